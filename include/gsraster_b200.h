@@ -1,0 +1,118 @@
+/*
+ * gsraster_b200 -- C ABI of the B200-native (sm_100a) differentiable Gaussian-splatting rasterizer.
+ *
+ * Drop-in boundary: these entry points sit exactly where the reference's
+ * CudaRasterizer::Rasterizer static API sits
+ *   (submodules/diff-gaussian-rasterization/cuda_rasterizer/rasterizer.h:20-94)
+ * and where SimpleKNN::knn sits (submodules/simple-knn/simple_knn.h:15-19).
+ * Plain pointers and sizes only; no torch / STL types; no exceptions cross this boundary.
+ * All data pointers are DEVICE pointers unless stated otherwise. fp32, contiguous, same layouts
+ * as the reference (means3D (P,3), shs (P,M,3), sh_objs (P,F), rotations (P,4) xyzw, matrices
+ * column-major flat, images CHW).
+ *
+ * Status codes: 0 = ok, negative = error; gsr_last_error() returns a thread-local message.
+ * Threading: no global mutable state besides the thread-local error string; safe to call from one
+ * host thread per device/stream concurrently. Every call is stream-ordered on params->stream.
+ */
+#ifndef GSRASTER_B200_H_
+#define GSRASTER_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GSR_OK 0
+#define GSR_ERR_INVALID_ARGUMENT (-1)
+#define GSR_ERR_CUDA (-2)
+#define GSR_ERR_UNSUPPORTED (-3)
+#define GSR_ERR_ALLOC (-4)
+
+/* Scratch allocator: replaces the three std::function<char*(size_t)> callbacks of
+ * Rasterizer::forward (rasterizer.h:32-34; torch side: rasterize_points.cu:27-33).
+ * Must return a device pointer to at least `bytes` bytes (256-byte aligned), valid until the
+ * matching backward call has completed. */
+typedef char* (*gsr_alloc_fn)(void* ctx, size_t bytes);
+
+typedef struct gsr_params {
+  int P;              /* number of Gaussians */
+  int D;              /* active SH degree (0..3) */
+  int M;              /* SH coefficients per colour channel stored per Gaussian (sh.size(1)), 0 if no SH */
+  int F;              /* feature ("objects") channels: 16 (reference NUM_OBJECTS, config.h:16) or 32 */
+  int width, height;
+  float tan_fovx, tan_fovy;
+  float scale_modifier;
+  int prefiltered;    /* reference traps if a prefiltered Gaussian is culled (auxiliary.h:161-165); here: error flag */
+  int debug;          /* !=0: synchronise + check after every stage (CHECK_CUDA, auxiliary.h:171-178) */
+  void* stream;       /* cudaStream_t; NULL = legacy default stream like the reference */
+} gsr_params;
+
+/* Replaces CudaRasterizer::Rasterizer::forward (rasterizer.h:31-59, rasterizer_impl.cu:201-352).
+ * Nullable exactly as the reference: shs / colors_precomp (exactly one), scales+rotations /
+ * cov3D_precomp (exactly one), radii, is_used. Outputs: out_depth (1,H,W), out_color (3,H,W),
+ * out_objects (F,H,W) are fully written (no pre-zeroing needed); radii (P) int32, is_used (P) bool.
+ * *num_rendered receives R = sum of tiles touched (needed by gsr_backward). */
+int gsr_forward(const gsr_params* params,
+                gsr_alloc_fn geom_alloc, void* geom_ctx,
+                gsr_alloc_fn binning_alloc, void* binning_ctx,
+                gsr_alloc_fn image_alloc, void* image_ctx,
+                const float* background, const float* means3D, const float* shs, const float* sh_objs,
+                const float* colors_precomp, const float* opacities, const float* scales,
+                const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                const float* projmatrix, const float* cam_pos,
+                float* out_depth, float* out_color, float* out_objects, int* radii, uint8_t* is_used,
+                int* num_rendered);
+
+/* Replaces CudaRasterizer::Rasterizer::backward (rasterizer.h:61-93, rasterizer_impl.cu:356-466).
+ * All 11 gradient outputs are fully written (culled Gaussians get exact zeros; the reference
+ * needs them pre-zeroed, rasterize_points.cu:164-174). dL_dmean2D is (P,3) with .z = 0,
+ * dL_dconic is (P,6) float6 {x,y,z=0,w,i,j} like the reference (backward.cu:670-674).
+ * dL_dsh / dL_dscale+dL_drot may be NULL when shs / scales are NULL. */
+int gsr_backward(const gsr_params* params, int num_rendered,
+                 const float* background, const float* means3D, const float* shs, const float* sh_objs,
+                 const float* colors_precomp, const float* scales, const float* rotations,
+                 const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                 const float* cam_pos, const int* radii,
+                 char* geom_buffer, char* binning_buffer, char* image_buffer,
+                 const float* dL_dpix_depth, const float* dL_dpix, const float* dL_dpix_obj,
+                 float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_ddepths,
+                 float* dL_dcolor, float* dL_dobjects, float* dL_dmean3D, float* dL_dcov3D,
+                 float* dL_dsh, float* dL_dscale, float* dL_drot);
+
+/* Replaces Rasterizer::markVisible (rasterizer.h:24-29, rasterizer_impl.cu:141-153). */
+int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                     uint8_t* present, void* stream);
+
+/* Replaces SimpleKNN::knn (simple-knn/simple_knn.h:18, simple_knn.cu:185-221): mean of the three
+ * smallest squared distances to other points. `scratch` must hold gsr_knn_scratch_bytes(P). */
+size_t gsr_knn_scratch_bytes(int P);
+int gsr_knn(int P, const float* points, float* mean_dists, char* scratch, void* stream);
+
+/* Parity/diagnostic export (no reference equivalent; the reference's private scratch layout is
+ * rasterizer_impl.h:30-70). Any output may be NULL. All device pointers:
+ * tiles_touched u32[P], depths f32[P], means2D f32[2P], conic_opacity f32[6P] (float6 order),
+ * rgb f32[3P], clamped u8[3P], point_list u32[R], sorted_keys u64[R] (tile<<32 | depth bits),
+ * ranges u32[2T], n_contrib u32[W*H], final_T f32[W*H]. */
+int gsr_export_state(const gsr_params* params, int num_rendered, const char* geom_buffer,
+                     const char* binning_buffer, const char* image_buffer,
+                     uint32_t* tiles_touched, float* depths, float* means2D, float* conic_opacity,
+                     float* rgb, uint8_t* clamped, uint32_t* point_list, uint64_t* sorted_keys,
+                     uint32_t* ranges, uint32_t* n_contrib, float* final_T);
+
+/* Sizes of the three scratch buffers (what the allocators will be asked for). */
+size_t gsr_geom_bytes(int P);
+size_t gsr_image_bytes(int width, int height);
+size_t gsr_binning_bytes(int64_t num_rendered);
+
+/* Kernel launches issued by the last forward/backward/knn call on this thread (for bench.py). */
+int gsr_last_launch_count(void);
+
+const char* gsr_last_error(void);
+const char* gsr_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSRASTER_B200_H_ */

@@ -1,0 +1,30 @@
+#!/usr/bin/env bash
+# TEST INFRASTRUCTURE. Compiles the UNMODIFIED reference CUDA rasterizer + simple-knn from the
+# sources where they lie under /root/reference into oracle/_ref/*.so (git-ignored, travels to
+# the GPU box). Does not run the reference's own build system (setup.py/CMake need torch); only
+# its cuda_rasterizer/*.cu + vendored glm are needed. No reference source is copied.
+set -euo pipefail
+HERE="$(cd "$(dirname "$0")" && pwd)"
+REF="${REF_ROOT:-/root/reference}/submodules"
+OUT="$HERE/_ref"
+mkdir -p "$OUT"
+if [ ! -d "$REF/diff-gaussian-rasterization/cuda_rasterizer" ]; then
+  echo "[build_ref] $REF not present (GPU box?) - keeping prebuilt $OUT" >&2
+  exit 0
+fi
+NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
+ARCH="-gencode arch=compute_100a,code=sm_100a"
+DGR="$REF/diff-gaussian-rasterization"
+KNN="$REF/simple-knn"
+if [ ! -f "$OUT/libref_rasterizer.so" ] || [ "${FORCE:-0}" = 1 ]; then
+  "$NVCC" -O3 -std=c++17 $ARCH -lineinfo -Xcompiler -fPIC -shared -w \
+    -I "$DGR/third_party/glm" -I "$DGR/cuda_rasterizer" \
+    "$DGR/cuda_rasterizer/forward.cu" "$DGR/cuda_rasterizer/backward.cu" \
+    "$DGR/cuda_rasterizer/rasterizer_impl.cu" "$HERE/ref_shim.cu" \
+    -o "$OUT/libref_rasterizer.so"
+fi
+if [ ! -f "$OUT/libref_knn.so" ] || [ "${FORCE:-0}" = 1 ]; then
+  "$NVCC" -O3 -std=c++17 $ARCH -lineinfo -Xcompiler -fPIC -shared -w -include cfloat \
+    -I "$KNN" "$KNN/simple_knn.cu" "$HERE/ref_knn_shim.cu" -o "$OUT/libref_knn.so"
+fi
+echo "[build_ref] ok: $(ls "$OUT")"

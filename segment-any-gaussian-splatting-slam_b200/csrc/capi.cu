@@ -1,0 +1,266 @@
+// C ABI of the B200-native rasterizer (include/gsraster_b200.h). Orchestration only: the stage
+// order mirrors Rasterizer::forward / ::backward of the reference (rasterizer_impl.cu:201-352,
+// 356-466); every stage is one of our sm_100a kernels. There is NO CPU fallback: any CUDA failure
+// is reported through the status code + gsr_last_error().
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+#include "../../include/gsraster_b200.h"
+#include "common.cuh"
+
+namespace gsr {
+void launch_export_keys(int T, const uint2* ranges, const uint32_t* point_list, const float4* rec, uint64_t* keys,
+                        cudaStream_t s);
+}
+
+namespace {
+thread_local std::string g_err;
+thread_local int g_launches = 0;
+thread_local int* g_pinned = nullptr;  // 8 ints of pinned host memory for the num_rendered read-back
+
+int fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+#define CUDA_TRY(expr)                                                                                  \
+  do {                                                                                                  \
+    cudaError_t e__ = (expr);                                                                           \
+    if (e__ != cudaSuccess) return fail(GSR_ERR_CUDA, "%s failed: %s", #expr, cudaGetErrorString(e__)); \
+  } while (0)
+#define STAGE_CHECK(name)                                                                                        \
+  do {                                                                                                           \
+    cudaError_t e__ = cudaGetLastError();                                                                        \
+    if (e__ == cudaSuccess && p->debug) e__ = cudaStreamSynchronize(stream);                                     \
+    if (e__ != cudaSuccess) return fail(GSR_ERR_CUDA, "stage %s failed: %s", name, cudaGetErrorString(e__));    \
+  } while (0)
+
+int check_params(const gsr_params* p) {
+  if (!p) return fail(GSR_ERR_INVALID_ARGUMENT, "params is NULL");
+  if (p->P < 0 || p->width <= 0 || p->height <= 0) return fail(GSR_ERR_INVALID_ARGUMENT, "bad sizes");
+  if (p->F != 16 && p->F != 32) return fail(GSR_ERR_UNSUPPORTED, "F must be 16 or 32 (got %d)", p->F);
+  if ((p->width + 15) / 16 > 255 || (p->height + 15) / 16 > 255)
+    return fail(GSR_ERR_UNSUPPORTED, "image larger than 4080x4080 tiles-per-axis limit");
+  if (p->D < 0 || p->D > 3) return fail(GSR_ERR_INVALID_ARGUMENT, "SH degree must be 0..3");
+  return GSR_OK;
+}
+gsr::Cam make_cam(const gsr_params* p, const float* view, const float* proj, const float* campos, const float* bg) {
+  gsr::Cam c;
+  c.V = view; c.PV = proj; c.campos = campos; c.bg = bg;
+  c.tan_fovx = p->tan_fovx; c.tan_fovy = p->tan_fovy;
+  c.focal_y = p->height / (2.0f * p->tan_fovy);  // rasterizer_impl.cu:229-230
+  c.focal_x = p->width / (2.0f * p->tan_fovx);
+  c.scale_modifier = p->scale_modifier;
+  c.W = p->width; c.H = p->height;
+  c.gx = (p->width + gsr::TILE_X - 1) / gsr::TILE_X;
+  c.gy = (p->height + gsr::TILE_Y - 1) / gsr::TILE_Y;
+  return c;
+}
+gsr::FwdInputs make_inputs(const gsr_params* p, const float* means3D, const float* shs, const float* colors_precomp,
+                           const float* opacities, const float* scales, const float* rotations,
+                           const float* cov3D_precomp) {
+  gsr::FwdInputs in;
+  in.P = p->P; in.D = p->D; in.M = p->M; in.F = p->F;
+  in.means3D = means3D; in.shs = shs; in.colors_precomp = colors_precomp; in.opacities = opacities;
+  in.scales = scales; in.rotations = rotations; in.cov3D_precomp = cov3D_precomp;
+  in.prefiltered = p->prefiltered != 0;
+  return in;
+}
+}  // namespace
+
+extern "C" {
+
+const char* gsr_last_error(void) { return g_err.c_str(); }
+const char* gsr_version(void) { return "gsraster_b200 0.1 (sm_100a)"; }
+int gsr_last_launch_count(void) { return g_launches; }
+
+size_t gsr_geom_bytes(int P) {
+  gsr::GeomState g;
+  return gsr::geom_from_chunk(nullptr, (size_t)(P > 0 ? P : 1), g);
+}
+size_t gsr_image_bytes(int width, int height) {
+  gsr::ImageState s;
+  size_t T = (size_t)((width + 15) / 16) * ((height + 15) / 16);
+  return gsr::image_from_chunk(nullptr, (size_t)width * height, T, s);
+}
+size_t gsr_binning_bytes(int64_t R) {
+  gsr::BinState b;
+  return gsr::bin_from_chunk(nullptr, (size_t)(R > 0 ? R : 1), b);
+}
+
+int gsr_forward(const gsr_params* p, gsr_alloc_fn geom_alloc, void* geom_ctx, gsr_alloc_fn binning_alloc,
+                void* binning_ctx, gsr_alloc_fn image_alloc, void* image_ctx, const float* background,
+                const float* means3D, const float* shs, const float* sh_objs, const float* colors_precomp,
+                const float* opacities, const float* scales, const float* rotations, const float* cov3D_precomp,
+                const float* viewmatrix, const float* projmatrix, const float* cam_pos, float* out_depth,
+                float* out_color, float* out_objects, int* radii, uint8_t* is_used, int* num_rendered) {
+  g_launches = 0;
+  if (int rc = check_params(p)) return rc;
+  if (num_rendered) *num_rendered = 0;
+  if (!geom_alloc || !binning_alloc || !image_alloc) return fail(GSR_ERR_INVALID_ARGUMENT, "allocator is NULL");
+  if (!background || !viewmatrix || !projmatrix || !out_depth || !out_color || !out_objects)
+    return fail(GSR_ERR_INVALID_ARGUMENT, "required pointer is NULL");
+  if (p->P == 0) return fail(GSR_ERR_INVALID_ARGUMENT, "P == 0: caller skips the op (rasterize_points.cu:86)");
+  if (!means3D || !opacities || !sh_objs)
+    return fail(GSR_ERR_INVALID_ARGUMENT, "means3D / opacities / sh_objs must be provided");
+  if ((shs == nullptr) == (colors_precomp == nullptr))
+    return fail(GSR_ERR_INVALID_ARGUMENT, "provide exactly one of shs / colors_precomp");
+  if (((scales == nullptr) || (rotations == nullptr)) == (cov3D_precomp == nullptr))
+    return fail(GSR_ERR_INVALID_ARGUMENT, "provide exactly one of scales+rotations / cov3D_precomp");
+  if (shs && p->M < (p->D + 1) * (p->D + 1)) return fail(GSR_ERR_INVALID_ARGUMENT, "M < (D+1)^2");
+  if (((uintptr_t)sh_objs & 15) || (rotations && ((uintptr_t)rotations & 15)))
+    return fail(GSR_ERR_INVALID_ARGUMENT, "sh_objs / rotations must be 16-byte aligned");
+  cudaStream_t stream = (cudaStream_t)p->stream;
+  const int P = p->P;
+  const gsr::Cam cam = make_cam(p, viewmatrix, projmatrix, cam_pos, background);
+  const int T = cam.gx * cam.gy;
+
+  gsr::GeomState g;
+  char* geom_chunk = geom_alloc(geom_ctx, gsr::geom_from_chunk(nullptr, (size_t)P, g, p->F));
+  if (!geom_chunk) return fail(GSR_ERR_ALLOC, "geometry allocator returned NULL");
+  gsr::geom_from_chunk(geom_chunk, (size_t)P, g, p->F);
+  gsr::ImageState img;
+  char* img_chunk = image_alloc(image_ctx, gsr_image_bytes(p->width, p->height));
+  if (!img_chunk) return fail(GSR_ERR_ALLOC, "image allocator returned NULL");
+  gsr::image_from_chunk(img_chunk, (size_t)p->width * p->height, (size_t)T, img);
+  if (!radii) radii = g.radii_internal;
+
+  CUDA_TRY(cudaMemsetAsync(g.flags, 0, 8 * sizeof(int), stream));
+  const gsr::FwdInputs in = make_inputs(p, means3D, shs, colors_precomp, opacities, scales, rotations, cov3D_precomp);
+  gsr::launch_preprocess(in, cam, g, radii, is_used, stream);
+  g_launches += 1;
+  STAGE_CHECK("preprocess");
+  gsr::launch_depth_sort_and_count(P, g, stream, g_launches);
+  STAGE_CHECK("depth_sort");
+
+  // the one data-dependent host sync of the path (reference: rasterizer_impl.cu:289-290)
+  if (!g_pinned) CUDA_TRY(cudaHostAlloc(&g_pinned, 8 * sizeof(int), cudaHostAllocDefault));
+  CUDA_TRY(cudaMemcpyAsync(g_pinned, g.flags, 2 * sizeof(int), cudaMemcpyDeviceToHost, stream));
+  CUDA_TRY(cudaStreamSynchronize(stream));
+  const int64_t R = (int64_t)(uint32_t)g_pinned[0];
+  if (g_pinned[1]) return fail(GSR_ERR_INVALID_ARGUMENT, "Point is filtered although prefiltered is set");
+  if (R > 0x7fffffffLL) return fail(GSR_ERR_UNSUPPORTED, "num_rendered exceeds int32");
+  if (num_rendered) *num_rendered = (int)R;
+
+  char* bin_chunk = binning_alloc(binning_ctx, gsr_binning_bytes(R));
+  if (!bin_chunk) return fail(GSR_ERR_ALLOC, "binning allocator returned NULL");
+  gsr::BinState b;
+  gsr::bin_from_chunk(bin_chunk, (size_t)R, b);
+  gsr::launch_binning(P, R, cam, g, b, img, stream, g_launches);
+  STAGE_CHECK("binning");
+  gsr::launch_render_forward(p->F, cam, g, b, img, sh_objs, out_depth, out_color, out_objects, stream);
+  g_launches += 1;
+  STAGE_CHECK("render_forward");
+  return GSR_OK;
+}
+
+int gsr_backward(const gsr_params* p, int num_rendered, const float* background, const float* means3D,
+                 const float* shs, const float* sh_objs, const float* colors_precomp, const float* scales,
+                 const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                 const float* projmatrix, const float* cam_pos, const int* radii, char* geom_buffer,
+                 char* binning_buffer, char* image_buffer, const float* dL_dpix_depth, const float* dL_dpix,
+                 const float* dL_dpix_obj, float* dL_dmean2D, float* dL_dconic, float* dL_dopacity,
+                 float* dL_ddepths, float* dL_dcolor, float* dL_dobjects, float* dL_dmean3D, float* dL_dcov3D,
+                 float* dL_dsh, float* dL_dscale, float* dL_drot) {
+  g_launches = 0;
+  if (int rc = check_params(p)) return rc;
+  if (p->P == 0) return GSR_OK;
+  if (!geom_buffer || !binning_buffer || !image_buffer) return fail(GSR_ERR_INVALID_ARGUMENT, "scratch buffer is NULL");
+  if (!dL_dpix_depth || !dL_dpix || !dL_dpix_obj) return fail(GSR_ERR_INVALID_ARGUMENT, "upstream gradient is NULL");
+  if (!dL_dmean2D || !dL_dconic || !dL_dopacity || !dL_ddepths || !dL_dcolor || !dL_dobjects || !dL_dmean3D ||
+      !dL_dcov3D)
+    return fail(GSR_ERR_INVALID_ARGUMENT, "gradient output is NULL");
+  if (shs && !dL_dsh) return fail(GSR_ERR_INVALID_ARGUMENT, "dL_dsh is NULL although shs given");
+  if (((uintptr_t)dL_dobjects & 15) || (dL_drot && ((uintptr_t)dL_drot & 15)))
+    return fail(GSR_ERR_INVALID_ARGUMENT, "dL_dobjects / dL_drot must be 16-byte aligned");
+  cudaStream_t stream = (cudaStream_t)p->stream;
+  const int P = p->P;
+  const gsr::Cam cam = make_cam(p, viewmatrix, projmatrix, cam_pos, background);
+  const int T = cam.gx * cam.gy;
+  gsr::GeomState g;
+  gsr::geom_from_chunk(geom_buffer, (size_t)P, g, p->F);
+  gsr::ImageState img;
+  gsr::image_from_chunk(image_buffer, (size_t)p->width * p->height, (size_t)T, img);
+  gsr::BinState b;
+  gsr::bin_from_chunk(binning_buffer, (size_t)(num_rendered > 0 ? num_rendered : 0), b);
+  if (!radii) radii = g.radii_internal;
+
+  CUDA_TRY(cudaMemsetAsync(g.grad_rows, 0, (size_t)P * gsr::grad_row_floats(p->F) * sizeof(float), stream));
+  if (num_rendered > 0) {
+    gsr::launch_render_backward(p->F, cam, g, b, img, sh_objs, dL_dpix_depth, dL_dpix, dL_dpix_obj, stream);
+    g_launches += 1;
+    STAGE_CHECK("render_backward");
+  }
+  const gsr::FwdInputs in = make_inputs(p, means3D, shs, colors_precomp, nullptr, scales, rotations, cov3D_precomp);
+  gsr::BwdOutputs out{dL_dmean2D, dL_dconic, dL_dopacity, dL_ddepths, dL_dcolor, dL_dobjects,
+                      dL_dmean3D, dL_dcov3D, dL_dsh,      dL_dscale,  dL_drot};
+  gsr::launch_preprocess_backward(in, cam, g, radii, out, stream);
+  g_launches += 1;
+  STAGE_CHECK("preprocess_backward");
+  return GSR_OK;
+}
+
+int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix, uint8_t* present,
+                     void* stream_) {
+  (void)projmatrix;  // unused by the reference as well (auxiliary.h:153-157 is commented out)
+  g_launches = 0;
+  if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) return fail(GSR_ERR_INVALID_ARGUMENT, "bad argument");
+  if (P == 0) return GSR_OK;
+  gsr::launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream_);
+  g_launches = 1;
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "mark_visible: %s", cudaGetErrorString(e));
+  return GSR_OK;
+}
+
+size_t gsr_knn_scratch_bytes(int P) { return gsr::knn_scratch_bytes(P); }
+
+int gsr_knn(int P, const float* points, float* mean_dists, char* scratch, void* stream_) {
+  g_launches = 0;
+  if (P < 0 || (P > 0 && (!points || !mean_dists || !scratch))) return fail(GSR_ERR_INVALID_ARGUMENT, "bad argument");
+  if (P == 0) return GSR_OK;
+  gsr::launch_knn(P, points, mean_dists, scratch, (cudaStream_t)stream_, g_launches);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "knn: %s", cudaGetErrorString(e));
+  return GSR_OK;
+}
+
+int gsr_export_state(const gsr_params* p, int num_rendered, const char* geom_buffer, const char* binning_buffer,
+                     const char* image_buffer, uint32_t* tiles_touched, float* depths, float* means2D,
+                     float* conic_opacity, float* rgb, uint8_t* clamped, uint32_t* point_list, uint64_t* sorted_keys,
+                     uint32_t* ranges, uint32_t* n_contrib, float* final_T) {
+  if (int rc = check_params(p)) return rc;
+  if (!geom_buffer || !image_buffer) return fail(GSR_ERR_INVALID_ARGUMENT, "scratch buffer is NULL");
+  cudaStream_t stream = (cudaStream_t)p->stream;
+  const int P = p->P;
+  const gsr::Cam cam = make_cam(p, nullptr, nullptr, nullptr, nullptr);
+  const int T = cam.gx * cam.gy;
+  const size_t N = (size_t)p->width * p->height;
+  gsr::GeomState g;
+  gsr::geom_from_chunk(const_cast<char*>(geom_buffer), (size_t)P, g, p->F);
+  gsr::ImageState img;
+  gsr::image_from_chunk(const_cast<char*>(image_buffer), N, (size_t)T, img);
+  gsr::BinState b{};
+  if (binning_buffer) gsr::bin_from_chunk(const_cast<char*>(binning_buffer), (size_t)(num_rendered > 0 ? num_rendered : 0), b);
+  gsr::launch_export(P, num_rendered, cam, g, b, tiles_touched, depths, means2D, conic_opacity, rgb, clamped,
+                     sorted_keys, stream);
+  if (num_rendered > 0 && binning_buffer) {
+    if (point_list)
+      CUDA_TRY(cudaMemcpyAsync(point_list, b.point_list, (size_t)num_rendered * 4, cudaMemcpyDeviceToDevice, stream));
+    if (sorted_keys) gsr::launch_export_keys(T, img.ranges, b.point_list, g.rec, sorted_keys, stream);
+  }
+  if (ranges) CUDA_TRY(cudaMemcpyAsync(ranges, img.ranges, (size_t)T * 8, cudaMemcpyDeviceToDevice, stream));
+  if (n_contrib) CUDA_TRY(cudaMemcpyAsync(n_contrib, img.n_contrib, N * 4, cudaMemcpyDeviceToDevice, stream));
+  if (final_T) CUDA_TRY(cudaMemcpyAsync(final_T, img.final_T, N * 4, cudaMemcpyDeviceToDevice, stream));
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "export: %s", cudaGetErrorString(e));
+  return GSR_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,144 @@
+// K0 (visibility) and K1 (forward preprocess) for sm_100a.
+// Behaviour follows reference forward.cu:171-275 / auxiliary.h:144-169;
+// layout, fusion and outputs are ours: one 48-byte record per visible Gaussian (what the blend
+// kernels stage with TMA bulk copies), the packed tile rect, and the depth-sort key.
+#include "common.cuh"
+#include "math.cuh"
+
+namespace gsr {
+
+__global__ void __launch_bounds__(256) mark_visible_kernel(int P, const float* __restrict__ means,
+                                                          const float* __restrict__ view,
+                                                          uint8_t* __restrict__ present) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= P) return;
+  float3 p = {means[3 * idx], means[3 * idx + 1], means[3 * idx + 2]};
+  float3 pv = xform4x3(p, view);
+  present[idx] = !(pv.z <= 0.2f);
+}
+
+void launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t s) {
+  mark_visible_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, means3D, view, present);
+}
+
+// SH -> RGB for one Gaussian (reference forward.cu:20-71). sh points at this Gaussian's M*3 floats.
+__device__ __forceinline__ void sh_to_rgb(int deg, const float3 pos, const float* campos,
+                                          const float* __restrict__ sh, float* rgb, unsigned& clamped_bits) {
+  float3 dir = {pos.x - campos[0], pos.y - campos[1], pos.z - campos[2]};
+  float len = sqrtf(dir.x * dir.x + dir.y * dir.y + dir.z * dir.z);
+  dir.x = dir.x / len; dir.y = dir.y / len; dir.z = dir.z / len;
+  float x = dir.x, y = dir.y, z = dir.z;
+  float xx = x * x, yy = y * y, zz = z * z;
+  float xy = x * y, yz = y * z, xz = x * z;
+  clamped_bits = 0;
+#pragma unroll
+  for (int c = 0; c < 3; c++) {
+#define SH(k) sh[3 * (k) + c]
+    float result = SH_C0 * SH(0);
+    if (deg > 0) {
+      result = result - SH_C1 * y * SH(1) + SH_C1 * z * SH(2) - SH_C1 * x * SH(3);
+      if (deg > 1) {
+        result = result + SH_C2_0 * xy * SH(4) + SH_C2_1 * yz * SH(5) + SH_C2_2 * (2.0f * zz - xx - yy) * SH(6) +
+                 SH_C2_3 * xz * SH(7) + SH_C2_4 * (xx - yy) * SH(8);
+        if (deg > 2) {
+          result = result + SH_C3_0 * y * (3.0f * xx - yy) * SH(9) + SH_C3_1 * xy * z * SH(10) +
+                   SH_C3_2 * y * (4.0f * zz - xx - yy) * SH(11) +
+                   SH_C3_3 * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * SH(12) +
+                   SH_C3_4 * x * (4.0f * zz - xx - yy) * SH(13) + SH_C3_5 * z * (xx - yy) * SH(14) +
+                   SH_C3_6 * x * (xx - 3.0f * yy) * SH(15);
+        }
+      }
+    }
+#undef SH
+    result += 0.5f;
+    if (result < 0) clamped_bits |= 1u << c;
+    rgb[c] = fmaxf(result, 0.0f);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+preprocess_kernel(const FwdInputs in, const Cam cam, float4* __restrict__ rec, uint32_t* __restrict__ tiles_touched,
+                  uint32_t* __restrict__ rect, uint8_t* __restrict__ clamped, uint64_t* __restrict__ dkeys,
+                  int* __restrict__ radii, uint8_t* __restrict__ is_used, int* __restrict__ flags) {
+  __shared__ CamS cs;
+  load_cam(cam, cs);
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= in.P) return;
+
+  int my_radius_i = 0;
+  uint32_t touched = 0;
+  uint64_t key = (0xFFFFFFFFull << 32) | (uint32_t)idx;  // culled Gaussians sort last
+
+  const float3 p_orig = {in.means3D[3 * idx], in.means3D[3 * idx + 1], in.means3D[3 * idx + 2]};
+  const float3 p_view = xform4x3(p_orig, cs.V);
+  do {
+    if (p_view.z <= 0.2f) {  // auxiliary.h:159 -- near plane only, no lateral test
+      if (in.prefiltered) flags[1] = 1;
+      break;
+    }
+    float4 p_hom = xform4x4(p_orig, cs.PV);
+    float p_w = 1.0f / (p_hom.w + 0.0000001f);
+    float3 p_proj = {p_hom.x * p_w, p_hom.y * p_w, p_hom.z * p_w};
+
+    float cov3D[6];
+    if (in.cov3D_precomp != nullptr) {
+#pragma unroll
+      for (int k = 0; k < 6; k++) cov3D[k] = in.cov3D_precomp[6 * (size_t)idx + k];
+    } else {
+      const float* sc = in.scales + 3 * (size_t)idx;
+      const float4 q = reinterpret_cast<const float4*>(in.rotations)[idx];
+      cov3d_from_scale_rot(sc[0], sc[1], sc[2], cam.scale_modifier, q.x, q.y, q.z, q.w, cov3D);
+    }
+    Cov2D c2 = project_cov(p_orig, cam.focal_x, cam.focal_y, cam.tan_fovx, cam.tan_fovy, cov3D, cs.V);
+    // low-pass filter, forward.cu:114-115
+    c2.cov.c[0][0] += 0.3f;
+    c2.cov.c[1][1] += 0.3f;
+    const float cxx = c2.cov.c[0][0], cxy = c2.cov.c[0][1], czx = c2.cov.c[0][2];
+    const float cyy = c2.cov.c[1][1], cyz = c2.cov.c[1][2];
+
+    float det = (cxx * cyy - cxy * cxy);
+    if (det == 0.0f) break;
+    float det_inv = 1.f / det;
+    float3 conic = {cyy * det_inv, -cxy * det_inv, cxx * det_inv};
+
+    float mid = 0.5f * (cxx + cyy);
+    float lambda1 = mid + sqrtf(max(0.1f, mid * mid - det));
+    float lambda2 = mid - sqrtf(max(0.1f, mid * mid - det));
+    float my_radius = ceilf(3.f * sqrtf(max(lambda1, lambda2)));
+    float2 point_image = {ndc2pix(p_proj.x, cam.W), ndc2pix(p_proj.y, cam.H)};
+    int x0, y0, x1, y1;
+    tile_rect(point_image.x, point_image.y, (int)my_radius, cam.gx, cam.gy, x0, y0, x1, y1);
+    if ((x1 - x0) * (y1 - y0) == 0) break;
+
+    float rgb[3];
+    unsigned cbits = 0;
+    if (in.colors_precomp == nullptr) {
+      sh_to_rgb(in.D, p_orig, cs.campos, in.shs + (size_t)idx * in.M * 3, rgb, cbits);
+    } else {
+      rgb[0] = in.colors_precomp[3 * (size_t)idx];
+      rgb[1] = in.colors_precomp[3 * (size_t)idx + 1];
+      rgb[2] = in.colors_precomp[3 * (size_t)idx + 2];
+    }
+    clamped[idx] = (uint8_t)cbits;
+    rec[3 * (size_t)idx + 0] = make_float4(point_image.x, point_image.y, conic.x, conic.y);
+    rec[3 * (size_t)idx + 1] = make_float4(conic.z, in.opacities[idx], czx, cyz);
+    rec[3 * (size_t)idx + 2] = make_float4(p_view.z, rgb[0], rgb[1], rgb[2]);
+    my_radius_i = (int)my_radius;
+    touched = (uint32_t)((y1 - y0) * (x1 - x0));
+    rect[idx] = (uint32_t)x0 | ((uint32_t)y0 << 8) | ((uint32_t)x1 << 16) | ((uint32_t)y1 << 24);
+    key = ((uint64_t)__float_as_uint(p_view.z) << 32) | (uint32_t)idx;
+  } while (false);
+
+  radii[idx] = my_radius_i;
+  tiles_touched[idx] = touched;
+  dkeys[idx] = key;
+  if (is_used) is_used[idx] = touched > 0;
+}
+
+void launch_preprocess(const FwdInputs& in, const Cam& cam, GeomState& g, int* radii, uint8_t* is_used,
+                       cudaStream_t s) {
+  preprocess_kernel<<<(in.P + 255) / 256, 256, 0, s>>>(in, cam, g.rec, g.tiles_touched, g.rect, g.clamped, g.dkeys_a,
+                                                      radii, is_used, g.flags);
+}
+
+}  // namespace gsr

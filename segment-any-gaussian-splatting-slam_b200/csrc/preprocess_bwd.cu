@@ -1,0 +1,271 @@
+// K6 + K7 fused: per-Gaussian backward for sm_100a. Behaviour: reference backward.cu:144-294
+// (computeCov2DCUDA), 369-426 (preprocessCUDA), 20-139 (SH), 298-364 (cov3D); SURVEY 8a a21-a22,
+// checklist 16-20, including the reference's missing dL_dcovyz terms in dL_dT11/dL_dT12.
+// One pass: reads the packed gradient row written by K5, recomputes cov3D from scale/rotation
+// (no 24 B/Gaussian round trip), writes all eleven gradient tensors -- zeros for culled
+// Gaussians, so no pre-zeroing memset of 376 B/Gaussian (rasterize_points.cu:164-174) is needed.
+#include "common.cuh"
+#include "math.cuh"
+
+namespace gsr {
+
+template <int F>
+__global__ void __launch_bounds__(256)
+preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restrict__ tiles_touched,
+                      const uint8_t* __restrict__ clampedb, const int* __restrict__ radii,
+                      const float* __restrict__ grad_rows, const BwdOutputs out) {
+  constexpr int ROW = (F == 16) ? 32 : 64;
+  __shared__ CamS cs;
+  load_cam(cam, cs);
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= in.P) return;
+  const int M = in.M, D = in.D;
+  const bool visible = radii[idx] > 0;
+
+  float g[12 + F];
+#pragma unroll
+  for (int k = 0; k < 12 + F; k++) g[k] = 0.f;
+  if (visible) {
+    const float4* row = reinterpret_cast<const float4*>(grad_rows + (size_t)idx * ROW);
+#pragma unroll
+    for (int q = 0; q < (12 + F) / 4; q++) {
+      float4 t = row[q];
+      g[4 * q] = t.x; g[4 * q + 1] = t.y; g[4 * q + 2] = t.z; g[4 * q + 3] = t.w;
+    }
+  }
+  // unpacked per-Gaussian outputs of K5 (API tensors)
+  out.dL_dmean2D[3 * (size_t)idx] = g[0];
+  out.dL_dmean2D[3 * (size_t)idx + 1] = g[1];
+  out.dL_dmean2D[3 * (size_t)idx + 2] = 0.f;
+  {
+    float* c = out.dL_dconic + 6 * (size_t)idx;
+    c[0] = g[2]; c[1] = g[3]; c[2] = 0.f; c[3] = g[4]; c[4] = g[5]; c[5] = g[6];
+  }
+  out.dL_dopacity[idx] = g[7];
+  out.dL_ddepths[idx] = g[8];
+  out.dL_dcolor[3 * (size_t)idx] = g[9];
+  out.dL_dcolor[3 * (size_t)idx + 1] = g[10];
+  out.dL_dcolor[3 * (size_t)idx + 2] = g[11];
+  {
+    float4* o = reinterpret_cast<float4*>(out.dL_dobjects + (size_t)idx * F);
+#pragma unroll
+    for (int q = 0; q < F / 4; q++) o[q] = make_float4(g[12 + 4 * q], g[13 + 4 * q], g[14 + 4 * q], g[15 + 4 * q]);
+  }
+
+  float dmean[3] = {0.f, 0.f, 0.f};
+  float dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  float dscale[3] = {0.f, 0.f, 0.f};
+  float drot[4] = {0.f, 0.f, 0.f, 0.f};
+
+  if (!visible) {
+    if (out.dL_dsh)
+      for (int k = 0; k < 3 * M; k++) out.dL_dsh[(size_t)idx * 3 * M + k] = 0.f;
+  } else {
+    const float3 mean = {in.means3D[3 * idx], in.means3D[3 * idx + 1], in.means3D[3 * idx + 2]};
+    float cov3D[6];
+    float sx = 0, sy = 0, sz = 0;
+    float4 q = make_float4(0, 0, 0, 1);
+    if (in.cov3D_precomp != nullptr) {
+#pragma unroll
+      for (int k = 0; k < 6; k++) cov3D[k] = in.cov3D_precomp[6 * (size_t)idx + k];
+    } else {
+      sx = in.scales[3 * (size_t)idx]; sy = in.scales[3 * (size_t)idx + 1]; sz = in.scales[3 * (size_t)idx + 2];
+      q = reinterpret_cast<const float4*>(in.rotations)[idx];
+      cov3d_from_scale_rot(sx, sy, sz, cam.scale_modifier, q.x, q.y, q.z, q.w, cov3D);
+    }
+    // ---------------- K6: conic / cov_zx / cov_yz -> cov3D and mean (backward.cu:144-294) ----------------
+    const float h_x = cam.focal_x, h_y = cam.focal_y;
+    const float3 dL_dconic = {g[2], g[3], g[4]};
+    const float dL_dcovzx = g[5], dL_dcovyz = g[6];
+    Cov2D c2 = project_cov(mean, h_x, h_y, cam.tan_fovx, cam.tan_fovy, cov3D, cs.V);
+    const float limx = 1.3f * cam.tan_fovx, limy = 1.3f * cam.tan_fovy;
+    const float x_grad_mul = c2.txtz < -limx || c2.txtz > limx ? 0 : 1;
+    const float y_grad_mul = c2.tytz < -limy || c2.tytz > limy ? 0 : 1;
+    const M3& T = c2.T;
+    const M3 Vrk = m3(cov3D[0], cov3D[1], cov3D[2], cov3D[1], cov3D[3], cov3D[4], cov3D[2], cov3D[4], cov3D[5]);
+    const float a = c2.cov.c[0][0] + 0.3f, b = c2.cov.c[0][1], c = c2.cov.c[1][1] + 0.3f;
+    const float denom = a * c - b * b;
+    float dL_da = 0, dL_db = 0, dL_dc = 0;
+    const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+#define TT(i, j) T.c[i][j]
+    if (denom2inv != 0) {
+      dL_da = denom2inv * (-c * c * dL_dconic.x + 2 * b * c * dL_dconic.y + (denom - a * c) * dL_dconic.z);
+      dL_dc = denom2inv * (-a * a * dL_dconic.z + 2 * a * b * dL_dconic.y + (denom - a * c) * dL_dconic.x);
+      dL_db = denom2inv * 2 * (b * c * dL_dconic.x - (denom + 2 * b * b) * dL_dconic.y + a * b * dL_dconic.z);
+      dcov[0] = (TT(0, 0) * TT(0, 0) * dL_da + TT(0, 0) * TT(1, 0) * dL_db + TT(0, 0) * TT(2, 0) * dL_dcovzx +
+                 TT(1, 0) * TT(1, 0) * dL_dc + TT(1, 0) * TT(2, 0) * dL_dcovyz);
+      dcov[3] = (TT(0, 1) * TT(0, 1) * dL_da + TT(0, 1) * TT(1, 1) * dL_db + TT(0, 1) * TT(2, 1) * dL_dcovzx +
+                 TT(1, 1) * TT(1, 1) * dL_dc + TT(1, 1) * TT(2, 1) * dL_dcovyz);
+      dcov[5] = (TT(0, 2) * TT(0, 2) * dL_da + TT(0, 2) * TT(1, 2) * dL_db + TT(0, 2) * TT(2, 2) * dL_dcovzx +
+                 TT(1, 2) * TT(1, 2) * dL_dc + TT(1, 2) * TT(2, 2) * dL_dcovyz);
+      dcov[1] = 2 * TT(0, 0) * TT(0, 1) * dL_da + (TT(0, 0) * TT(1, 1) + TT(0, 1) * TT(1, 0)) * dL_db +
+                (TT(0, 1) * TT(2, 0) + TT(0, 0) * TT(2, 1)) * dL_dcovzx +
+                (TT(1, 1) * TT(2, 0) + TT(1, 0) * TT(2, 1)) * dL_dcovyz + 2 * TT(1, 0) * TT(1, 1) * dL_dc;
+      dcov[2] = 2 * TT(0, 0) * TT(0, 2) * dL_da + (TT(0, 0) * TT(1, 2) + TT(0, 2) * TT(1, 0)) * dL_db +
+                (TT(0, 2) * TT(2, 0) + TT(0, 0) * TT(2, 2)) * dL_dcovzx +
+                (TT(1, 2) * TT(2, 0) + TT(1, 0) * TT(2, 2)) * dL_dcovyz + 2 * TT(1, 0) * TT(1, 2) * dL_dc;
+      dcov[4] = 2 * TT(0, 2) * TT(0, 1) * dL_da + (TT(0, 1) * TT(1, 2) + TT(0, 2) * TT(1, 1)) * dL_db +
+                (TT(0, 2) * TT(2, 1) + TT(0, 1) * TT(2, 2)) * dL_dcovzx +
+                (TT(1, 2) * TT(2, 1) + TT(1, 1) * TT(2, 2)) * dL_dcovyz + 2 * TT(1, 1) * TT(1, 2) * dL_dc;
+    }
+#define TV(r, cc) (TT(r, 0) * Vrk.c[cc][0] + TT(r, 1) * Vrk.c[cc][1] + TT(r, 2) * Vrk.c[cc][2])
+    const float dL_dT00 = 2 * TV(0, 0) * dL_da + TV(1, 0) * dL_db + TV(2, 0) * dL_dcovzx;
+    const float dL_dT01 = 2 * TV(0, 1) * dL_da + TV(1, 1) * dL_db + TV(2, 1) * dL_dcovzx;
+    const float dL_dT02 = 2 * TV(0, 2) * dL_da + TV(1, 2) * dL_db + TV(2, 2) * dL_dcovzx;
+    const float dL_dT10 = 2 * TV(1, 0) * dL_dc + TV(0, 0) * dL_db + TV(2, 0) * dL_dcovyz;
+    const float dL_dT11 = 2 * TV(1, 1) * dL_dc + TV(0, 1) * dL_db;  // reference drops the dL_dcovyz term (backward.cu:263-265)
+    const float dL_dT12 = 2 * TV(1, 2) * dL_dc + TV(0, 2) * dL_db;  // idem (backward.cu:266-268)
+#undef TV
+#undef TT
+    const float* V = cs.V;
+    // glm W[c][r]: W[0] = (V0,V4,V8), W[1] = (V1,V5,V9), W[2] = (V2,V6,V10)
+    const float dL_dJ00 = V[0] * dL_dT00 + V[4] * dL_dT01 + V[8] * dL_dT02;
+    const float dL_dJ02 = V[2] * dL_dT00 + V[6] * dL_dT01 + V[10] * dL_dT02;
+    const float dL_dJ11 = V[1] * dL_dT10 + V[5] * dL_dT11 + V[9] * dL_dT12;
+    const float dL_dJ12 = V[2] * dL_dT10 + V[6] * dL_dT11 + V[10] * dL_dT12;
+    const float tz = 1.f / c2.tz, tz2 = tz * tz, tz3 = tz2 * tz;
+    const float dL_dtx = x_grad_mul * -h_x * tz2 * dL_dJ02;
+    const float dL_dty = y_grad_mul * -h_y * tz2 * dL_dJ12;
+    const float dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * c2.tx) * tz3 * dL_dJ02 +
+                         (2 * h_y * c2.ty) * tz3 * dL_dJ12;
+    dmean[0] = V[0] * dL_dtx + V[1] * dL_dty + V[2] * dL_dtz;
+    dmean[1] = V[4] * dL_dtx + V[5] * dL_dty + V[6] * dL_dtz;
+    dmean[2] = V[8] * dL_dtx + V[9] * dL_dty + V[10] * dL_dtz;
+
+    // ---------------- K7 (backward.cu:369-426) ----------------
+    const float* proj = cs.PV;
+    const float3 m = mean;
+    const float4 m_hom = xform4x4(m, proj);
+    const float m_w = 1.0f / (m_hom.w + 0.0000001f);
+    const float mulz = V[2] * m.x + V[6] * m.y + V[10] * m.z + V[14];
+    const float ddep = g[8];
+    dmean[0] += ddep * (V[2] - V[3] * mulz);
+    dmean[1] += ddep * (V[6] - V[7] * mulz);
+    dmean[2] += ddep * (V[10] - V[11] * mulz);
+    const float mul1 = (proj[0] * m.x + proj[4] * m.y + proj[8] * m.z + proj[12]) * m_w * m_w;
+    const float mul2 = (proj[1] * m.x + proj[5] * m.y + proj[9] * m.z + proj[13]) * m_w * m_w;
+    dmean[0] += (proj[0] * m_w - proj[3] * mul1) * g[0] + (proj[1] * m_w - proj[3] * mul2) * g[1];
+    dmean[1] += (proj[4] * m_w - proj[7] * mul1) * g[0] + (proj[5] * m_w - proj[7] * mul2) * g[1];
+    dmean[2] += (proj[8] * m_w - proj[11] * mul1) * g[0] + (proj[9] * m_w - proj[11] * mul2) * g[1];
+
+    if (in.shs != nullptr) {
+      // SH backward (backward.cu:20-139)
+      const float3 dir_orig = {m.x - cs.campos[0], m.y - cs.campos[1], m.z - cs.campos[2]};
+      const float len = sqrtf(dir_orig.x * dir_orig.x + dir_orig.y * dir_orig.y + dir_orig.z * dir_orig.z);
+      const float x = dir_orig.x / len, y = dir_orig.y / len, z = dir_orig.z / len;
+      const float* sh = in.shs + (size_t)idx * M * 3;
+      float* dsh = out.dL_dsh + (size_t)idx * M * 3;
+      const uint8_t cb = clampedb[idx];
+      const float dRGB[3] = {g[9] * ((cb & 1) ? 0.f : 1.f), g[10] * ((cb & 2) ? 0.f : 1.f), g[11] * ((cb & 4) ? 0.f : 1.f)};
+      float ddx = 0.f, ddy = 0.f, ddz = 0.f;  // dL_ddir
+      const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+      float basis[16];
+      basis[0] = SH_C0;
+      basis[1] = -SH_C1 * y; basis[2] = SH_C1 * z; basis[3] = -SH_C1 * x;
+      basis[4] = SH_C2_0 * xy; basis[5] = SH_C2_1 * yz; basis[6] = SH_C2_2 * (2.f * zz - xx - yy);
+      basis[7] = SH_C2_3 * xz; basis[8] = SH_C2_4 * (xx - yy);
+      basis[9] = SH_C3_0 * y * (3.f * xx - yy); basis[10] = SH_C3_1 * xy * z;
+      basis[11] = SH_C3_2 * y * (4.f * zz - xx - yy); basis[12] = SH_C3_3 * z * (2.f * zz - 3.f * xx - 3.f * yy);
+      basis[13] = SH_C3_4 * x * (4.f * zz - xx - yy); basis[14] = SH_C3_5 * z * (xx - yy);
+      basis[15] = SH_C3_6 * x * (xx - 3.f * yy);
+      const int ncoef = (D + 1) * (D + 1);
+#pragma unroll
+      for (int k = 0; k < 16; k++) {
+        if (k < M) {
+          const float bk = k < ncoef ? basis[k] : 0.f;  // coefficients above the active degree get zero
+          dsh[3 * k] = bk * dRGB[0]; dsh[3 * k + 1] = bk * dRGB[1]; dsh[3 * k + 2] = bk * dRGB[2];
+        }
+      }
+      for (int k = 16; k < M; k++) { dsh[3 * k] = 0.f; dsh[3 * k + 1] = 0.f; dsh[3 * k + 2] = 0.f; }
+#pragma unroll
+      for (int ch = 0; ch < 3; ch++) {
+#define S(k) sh[3 * (k) + ch]
+        float dRGBdx = 0.f, dRGBdy = 0.f, dRGBdz = 0.f;
+        if (D > 0) {
+          dRGBdx = -SH_C1 * S(3); dRGBdy = -SH_C1 * S(1); dRGBdz = SH_C1 * S(2);
+          if (D > 1) {
+            dRGBdx += SH_C2_0 * y * S(4) + SH_C2_2 * 2.f * -x * S(6) + SH_C2_3 * z * S(7) + SH_C2_4 * 2.f * x * S(8);
+            dRGBdy += SH_C2_0 * x * S(4) + SH_C2_1 * z * S(5) + SH_C2_2 * 2.f * -y * S(6) + SH_C2_4 * 2.f * -y * S(8);
+            dRGBdz += SH_C2_1 * y * S(5) + SH_C2_2 * 2.f * 2.f * z * S(6) + SH_C2_3 * x * S(7);
+            if (D > 2) {
+              dRGBdx += (SH_C3_0 * S(9) * 3.f * 2.f * xy + SH_C3_1 * S(10) * yz + SH_C3_2 * S(11) * -2.f * xy +
+                         SH_C3_3 * S(12) * -3.f * 2.f * xz + SH_C3_4 * S(13) * (-3.f * xx + 4.f * zz - yy) +
+                         SH_C3_5 * S(14) * 2.f * xz + SH_C3_6 * S(15) * 3.f * (xx - yy));
+              dRGBdy += (SH_C3_0 * S(9) * 3.f * (xx - yy) + SH_C3_1 * S(10) * xz +
+                         SH_C3_2 * S(11) * (-3.f * yy + 4.f * zz - xx) + SH_C3_3 * S(12) * -3.f * 2.f * yz +
+                         SH_C3_4 * S(13) * -2.f * xy + SH_C3_5 * S(14) * -2.f * yz + SH_C3_6 * S(15) * -3.f * 2.f * xy);
+              dRGBdz += (SH_C3_1 * S(10) * xy + SH_C3_2 * S(11) * 4.f * 2.f * yz +
+                         SH_C3_3 * S(12) * 3.f * (2.f * zz - xx - yy) + SH_C3_4 * S(13) * 4.f * 2.f * xz +
+                         SH_C3_5 * S(14) * (xx - yy));
+            }
+          }
+        }
+#undef S
+        ddx += dRGBdx * dRGB[ch]; ddy += dRGBdy * dRGB[ch]; ddz += dRGBdz * dRGB[ch];
+      }
+      // dnormvdv (auxiliary.h:112-122)
+      const float3 v = dir_orig;
+      const float sum2 = v.x * v.x + v.y * v.y + v.z * v.z;
+      const float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
+      dmean[0] += ((+sum2 - v.x * v.x) * ddx - v.y * v.x * ddy - v.z * v.x * ddz) * invsum32;
+      dmean[1] += (-v.x * v.y * ddx + (sum2 - v.y * v.y) * ddy - v.z * v.y * ddz) * invsum32;
+      dmean[2] += (-v.x * v.z * ddx - v.y * v.z * ddy + (sum2 - v.z * v.z) * ddz) * invsum32;
+    }
+
+    if (in.scales != nullptr) {
+      // cov3D -> scale / quaternion (backward.cu:298-364); no normalisation Jacobian
+      const float x = q.x, y = q.y, z = q.z, w = q.w;
+      const M3 R = quat_to_R(x, y, z, w);
+      const float s3[3] = {cam.scale_modifier * sx, cam.scale_modifier * sy, cam.scale_modifier * sz};
+      M3 S = m3(1.0f, 0.0f, 0.0f, 0.0f, 1.0f, 0.0f, 0.0f, 0.0f, 1.0f);
+      S.c[0][0] = s3[0]; S.c[1][1] = s3[1]; S.c[2][2] = s3[2];
+      const M3 Mm = mul(S, R);
+      const M3 dL_dSigma = m3(dcov[0], 0.5f * dcov[1], 0.5f * dcov[2], 0.5f * dcov[1], dcov[3], 0.5f * dcov[4],
+                              0.5f * dcov[2], 0.5f * dcov[4], dcov[5]);
+      M3 M2;
+#pragma unroll
+      for (int cc = 0; cc < 3; cc++)
+#pragma unroll
+        for (int r = 0; r < 3; r++) M2.c[cc][r] = 2.0f * Mm.c[cc][r];
+      const M3 dL_dM = mul(M2, dL_dSigma);
+      const M3 Rt = transpose(R);
+      M3 dL_dMt = transpose(dL_dM);
+#pragma unroll
+      for (int k = 0; k < 3; k++)
+        dscale[k] = Rt.c[k][0] * dL_dMt.c[k][0] + Rt.c[k][1] * dL_dMt.c[k][1] + Rt.c[k][2] * dL_dMt.c[k][2];
+#pragma unroll
+      for (int k = 0; k < 3; k++)
+#pragma unroll
+        for (int r = 0; r < 3; r++) dL_dMt.c[k][r] *= s3[k];
+#define MT(i, j) dL_dMt.c[i][j]
+      drot[0] = 2 * y * (MT(1, 0) + MT(0, 1)) + 2 * z * (MT(2, 0) + MT(0, 2)) + 2 * w * (MT(1, 2) - MT(2, 1)) - 4 * x * (MT(2, 2) + MT(1, 1));
+      drot[1] = 2 * x * (MT(1, 0) + MT(0, 1)) + 2 * w * (MT(2, 0) - MT(0, 2)) + 2 * z * (MT(1, 2) + MT(2, 1)) - 4 * y * (MT(2, 2) + MT(0, 0));
+      drot[2] = 2 * w * (MT(0, 1) - MT(1, 0)) + 2 * x * (MT(2, 0) + MT(0, 2)) + 2 * y * (MT(1, 2) + MT(2, 1)) - 4 * z * (MT(1, 1) + MT(0, 0));
+      drot[3] = 2 * z * (MT(0, 1) - MT(1, 0)) + 2 * y * (MT(2, 0) - MT(0, 2)) + 2 * x * (MT(1, 2) - MT(2, 1));
+#undef MT
+    }
+  }
+
+  out.dL_dmean3D[3 * (size_t)idx] = dmean[0];
+  out.dL_dmean3D[3 * (size_t)idx + 1] = dmean[1];
+  out.dL_dmean3D[3 * (size_t)idx + 2] = dmean[2];
+#pragma unroll
+  for (int k = 0; k < 6; k++) out.dL_dcov3D[6 * (size_t)idx + k] = dcov[k];
+  if (out.dL_dscale) {
+    out.dL_dscale[3 * (size_t)idx] = dscale[0];
+    out.dL_dscale[3 * (size_t)idx + 1] = dscale[1];
+    out.dL_dscale[3 * (size_t)idx + 2] = dscale[2];
+  }
+  if (out.dL_drot) reinterpret_cast<float4*>(out.dL_drot)[idx] = make_float4(drot[0], drot[1], drot[2], drot[3]);
+}
+
+void launch_preprocess_backward(const FwdInputs& in, const Cam& cam, const GeomState& g, const int* radii,
+                                const BwdOutputs& out, cudaStream_t s) {
+  const int nb = (in.P + 255) / 256;
+  if (in.F == 16)
+    preprocess_bwd_kernel<16><<<nb, 256, 0, s>>>(in, cam, g.tiles_touched, g.clamped, radii, g.grad_rows, out);
+  else
+    preprocess_bwd_kernel<32><<<nb, 256, 0, s>>>(in, cam, g.tiles_touched, g.clamped, radii, g.grad_rows, out);
+}
+
+}  // namespace gsr

@@ -1,0 +1,149 @@
+// K4: forward alpha blending for sm_100a. Behaviour: reference forward.cu:280-436 (SURVEY 8a a19,
+// checklist 11-14). One CTA per 16x16 tile (fixed by parity), one pixel per thread, warps cover
+// 8x4 pixel blocks so that whole-warp rejection (ballot) is frequent.
+//
+// Per batch of 128 sorted instances every operand the inner loop needs -- the 48-byte geometry
+// record and the 4F-byte feature row -- is staged into shared memory by one 1-D TMA bulk copy per
+// row (UBLKCP) completing on an mbarrier, double-buffered; the inner loop touches no global memory
+// (the reference issues 19+1 scattered LDG per contributing pair, forward.cu:377-381,403).
+#include "common.cuh"
+#include "tma.cuh"
+
+namespace gsr {
+
+constexpr int RB = 128;  // instances per staged batch
+
+template <int F>
+struct FwdSmem {
+  float4 rec[2][RB][3];
+  float4 feat[2][RB][F / 4];
+  uint64_t bar[2];
+};
+
+template <int F>
+__global__ void __launch_bounds__(256)
+render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+                  const float4* __restrict__ rec, const float* __restrict__ feats, int W, int H,
+                  const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
+                  float* __restrict__ out_depth, float* __restrict__ out_color, float* __restrict__ out_objects) {
+  __shared__ __align__(128) FwdSmem<F> sm;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int px = blockIdx.x * TILE_X + (warp & 1) * 8 + (lane & 7);
+  const int py = blockIdx.y * TILE_Y + (warp >> 1) * 4 + (lane >> 3);
+  const bool inside = px < W && py < H;
+  const float pixx = (float)px, pixy = (float)py;
+  const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
+  const int todo = (int)(range.y - range.x);
+  const int nbatch = (todo + RB - 1) / RB;
+
+  if (tid == 0) {
+    mbar_init(&sm.bar[0], 1);
+    mbar_init(&sm.bar[1], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  constexpr uint32_t ROW_BYTES = 48 + 4 * F;
+  auto issue = [&](int b) {
+    const int st = b & 1;
+    const int cnt = min(RB, todo - b * RB);
+    if (tid == 0) mbar_arrive_expect_tx(&sm.bar[st], (uint32_t)cnt * ROW_BYTES);
+    if (tid < cnt) {
+      const uint32_t id = point_list[range.x + b * RB + tid];
+      tma_load_1d(&sm.rec[st][tid][0], rec + 3 * (size_t)id, 48, &sm.bar[st]);
+      tma_load_1d(&sm.feat[st][tid][0], feats + (size_t)id * F, 4 * F, &sm.bar[st]);
+    }
+  };
+
+  float T = 1.0f, D = 0.f;
+  float C[3] = {0.f, 0.f, 0.f};
+  float O[F];
+#pragma unroll
+  for (int ch = 0; ch < F; ch++) O[ch] = 0.f;
+  uint32_t last_contributor = 0;
+  bool done = !inside;
+
+  if (nbatch > 0) issue(0);
+  for (int b = 0; b < nbatch; b++) {
+    const int st = b & 1;
+    if (b + 1 < nbatch) issue(b + 1);  // stage (b+1)&1 was released by the barrier ending iteration b-1
+    mbar_wait(&sm.bar[st], (uint32_t)(b >> 1) & 1u);
+    const int cnt = min(RB, todo - b * RB);
+    if (!__all_sync(0xffffffffu, done)) {
+      for (int j = 0; j < cnt; j++) {
+        const float4 r0 = sm.rec[st][j][0];  // px, py, conic a, conic b
+        const float4 r1 = sm.rec[st][j][1];  // conic c, opacity, cov_zx, cov_yz
+        const float dx = r0.x - pixx, dy = r0.y - pixy;
+        const float power = -0.5f * (r0.z * dx * dx + r1.x * dy * dy) - r0.w * dx * dy;
+        bool hit = !done && power <= 0.0f;
+        float alpha = 0.f, test_T = 0.f;
+        if (hit) {
+          alpha = min(0.99f, r1.y * expf(power));
+          hit = alpha >= 1.0f / 255.0f;
+          if (hit) {
+            test_T = T * (1 - alpha);
+            if (test_T < 0.0001f) { done = true; hit = false; }
+          }
+        }
+        if (__any_sync(0xffffffffu, hit)) {
+          const float4 r2 = sm.rec[st][j][2];  // depth, r, g, b
+          float4 f[F / 4];
+#pragma unroll
+          for (int q = 0; q < F / 4; q++) f[q] = sm.feat[st][j][q];
+          if (hit) {
+            C[0] += r2.y * alpha * T;
+            C[1] += r2.z * alpha * T;
+            C[2] += r2.w * alpha * T;
+#pragma unroll
+            for (int q = 0; q < F / 4; q++) {
+              O[4 * q + 0] += f[q].x * alpha * T;
+              O[4 * q + 1] += f[q].y * alpha * T;
+              O[4 * q + 2] += f[q].z * alpha * T;
+              O[4 * q + 3] += f[q].w * alpha * T;
+            }
+            const float covzx = r1.z, covyz = r1.w;
+            const float depth_c = r2.x - (covzx * r0.z + covyz * r0.w) * dx - (covzx * r0.w + covyz * r1.x) * dy;
+            D += depth_c * alpha * T;
+            T = test_T;
+            last_contributor = (uint32_t)(b * RB + j + 1);
+          }
+        } else if (__all_sync(0xffffffffu, done)) {
+          break;
+        }
+      }
+    }
+    // block vote (reference forward.cu:339-341) + release of stage st for the copy issued next iteration
+    const int num_done = __syncthreads_count(done);
+    if (num_done == 256) {
+      if (b + 1 < nbatch) mbar_wait(&sm.bar[(b + 1) & 1], (uint32_t)((b + 1) >> 1) & 1u);  // drain in-flight TMA
+      break;
+    }
+  }
+
+  if (inside) {
+    const size_t pix_id = (size_t)W * py + px;
+    const size_t HW = (size_t)H * W;
+    final_T[pix_id] = T;
+    n_contrib[pix_id] = last_contributor;
+    out_depth[pix_id] = (D + T * 15.f);
+    out_color[0 * HW + pix_id] = C[0] + T * bg[0];
+    out_color[1 * HW + pix_id] = C[1] + T * bg[1];
+    out_color[2 * HW + pix_id] = C[2] + T * bg[2];
+#pragma unroll
+    for (int ch = 0; ch < F; ch++) out_objects[ch * HW + pix_id] = O[ch];
+  }
+}
+
+void launch_render_forward(int F, const Cam& cam, const GeomState& g, const BinState& b,
+                           ImageState& img, const float* sh_objs, float* out_depth, float* out_color,
+                           float* out_objects, cudaStream_t s) {
+  dim3 grid(cam.gx, cam.gy), block(256);
+  if (F == 16)
+    render_fwd_kernel<16><<<grid, block, 0, s>>>(img.ranges, b.point_list, g.rec, sh_objs, cam.W, cam.H, cam.bg,
+                                                 img.final_T, img.n_contrib, out_depth, out_color, out_objects);
+  else
+    render_fwd_kernel<32><<<grid, block, 0, s>>>(img.ranges, b.point_list, g.rec, sh_objs, cam.W, cam.H, cam.bg,
+                                                 img.final_T, img.n_contrib, out_depth, out_color, out_objects);
+}
+
+}  // namespace gsr

@@ -1,0 +1,207 @@
+"""ctypes binding of include/gsraster_b200.h for torch CUDA tensors.
+
+Mirrors RasterizeGaussiansCUDA / RasterizeGaussiansBackwardCUDA / markVisible of the reference's
+LibTorch binding (submodules/diff-gaussian-rasterization/rasterize_points.cu:35-237) and distCUDA2
+(submodules/simple-knn/spatial.cu:15-26): same argument order, same returned tuples. There is no
+CPU fallback: a missing library or a non-CUDA tensor raises.
+"""
+import ctypes as C
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libgsraster_b200.so")
+
+ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_size_t)
+
+
+class Params(C.Structure):
+    _fields_ = [("P", C.c_int), ("D", C.c_int), ("M", C.c_int), ("F", C.c_int), ("width", C.c_int),
+                ("height", C.c_int), ("tan_fovx", C.c_float), ("tan_fovy", C.c_float),
+                ("scale_modifier", C.c_float), ("prefiltered", C.c_int), ("debug", C.c_int),
+                ("stream", C.c_void_p)]
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(f"{LIB_PATH} not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                               "(there is no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        L.gsr_last_error.restype = C.c_char_p
+        L.gsr_version.restype = C.c_char_p
+        for n in ("gsr_geom_bytes", "gsr_image_bytes", "gsr_binning_bytes", "gsr_knn_scratch_bytes"):
+            getattr(L, n).restype = C.c_size_t
+        L.gsr_binning_bytes.argtypes = [C.c_int64]
+        L.gsr_forward.argtypes = [C.POINTER(Params), ALLOC_FN, C.c_void_p, ALLOC_FN, C.c_void_p, ALLOC_FN,
+                                  C.c_void_p] + [C.c_void_p] * 17 + [C.POINTER(C.c_int)]
+        L.gsr_backward.argtypes = [C.POINTER(Params), C.c_int] + [C.c_void_p] * 29
+        L.gsr_mark_visible.argtypes = [C.c_int] + [C.c_void_p] * 5
+        L.gsr_knn.argtypes = [C.c_int] + [C.c_void_p] * 4
+        L.gsr_export_state.argtypes = [C.POINTER(Params), C.c_int] + [C.c_void_p] * 14
+        _lib = L
+    return _lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise RuntimeError(f"gsraster_b200 error {rc}: {lib().gsr_last_error().decode()}")
+
+
+def _ptr(t):
+    """Device pointer of a tensor, NULL for empty tensors (reference: 0-element tensor == absent)."""
+    if t is None or t.numel() == 0:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError("gsraster_b200: expected a CUDA tensor (no CPU fallback)")
+    return t.data_ptr()
+
+
+def _f32c(t):
+    if t is None or t.numel() == 0:
+        return t
+    if t.dtype != torch.float32:
+        raise RuntimeError("gsraster_b200: expected float32")
+    return t.contiguous()
+
+
+class _Resizer:
+    """torch-backed scratch allocator (reference: resizeFunctional, rasterize_points.cu:27-33)."""
+
+    def __init__(self, device):
+        self.t = torch.empty(0, dtype=torch.uint8, device=device)
+        self.cb = ALLOC_FN(self._alloc)
+
+    def _alloc(self, _ctx, n):
+        self.t = torch.empty(int(n) + 256, dtype=torch.uint8, device=self.t.device)
+        return self.t.data_ptr()
+
+
+def _stream_ptr():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                        viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, sh_objs, degree,
+                        campos, prefiltered, debug):
+    """-> (num_rendered, depth, color, objects, radii, is_used, geomBuffer, binningBuffer, imgBuffer)."""
+    if means3D.dim() != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    dev = means3D.device
+    P, H, W = means3D.size(0), int(image_height), int(image_width)
+    if sh_objs is None or sh_objs.numel() == 0:
+        raise RuntimeError("sh_objs must be provided (the reference dereferences it unconditionally)")
+    F = sh_objs.numel() // max(P, 1)
+    out_depth = torch.empty((1, H, W), dtype=torch.float32, device=dev)
+    out_color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+    out_objects = torch.empty((F, H, W), dtype=torch.float32, device=dev)
+    radii = torch.empty((P,), dtype=torch.int32, device=dev)
+    is_used = torch.empty((P,), dtype=torch.bool, device=dev)
+    geo, binb, img = _Resizer(dev), _Resizer(dev), _Resizer(dev)
+    rendered = C.c_int(0)
+    if P == 0:
+        for t in (out_depth, out_color, out_objects):
+            t.zero_()
+        return 0, out_depth, out_color, out_objects, radii, is_used, geo.t, binb.t, img.t
+    M = sh.size(1) if (sh is not None and sh.numel() != 0) else 0
+    prm = Params(P, int(degree), int(M), int(F), W, H, float(tan_fovx), float(tan_fovy), float(scale_modifier),
+                 int(bool(prefiltered)), int(bool(debug)), _stream_ptr())
+    keep = [_f32c(t) for t in (background, means3D, sh, sh_objs, colors, opacity, scales, rotations, cov3D_precomp,
+                               viewmatrix, projmatrix, campos)]
+    with torch.cuda.device(dev):
+        rc = lib().gsr_forward(C.byref(prm), geo.cb, None, binb.cb, None, img.cb, None, *[_ptr(t) for t in keep],
+                               _ptr(out_depth), _ptr(out_color), _ptr(out_objects), _ptr(radii), _ptr(is_used),
+                               C.byref(rendered))
+    _check(rc)
+    return rendered.value, out_depth, out_color, out_objects, radii, is_used, geo.t, binb.t, img.t
+
+
+def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier,
+                                 cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_depth,
+                                 dL_dout_color, sh, dL_dout_objects, sh_objs, degree, campos, geomBuffer, R,
+                                 binningBuffer, imageBuffer, debug):
+    """-> (dL_dmeans2D, dL_dcolors, dL_dobjects, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
+    dL_drotations), exactly the reference's 9-tuple (rasterize_points.cu:215)."""
+    dev = means3D.device
+    P = means3D.size(0)
+    H, W = dL_dout_color.size(1), dL_dout_color.size(2)
+    M = sh.size(1) if (sh is not None and sh.numel() != 0) else 0
+    F = sh_objs.numel() // max(P, 1)
+    o = dict(device=dev, dtype=torch.float32)
+    g = dict(means3D=torch.empty((P, 3), **o), means2D=torch.empty((P, 3), **o), depths=torch.empty((P, 1), **o),
+             colors=torch.empty((P, 3), **o), objects=torch.empty((P, F), **o), conic=torch.empty((P, 6), **o),
+             opacity=torch.empty((P, 1), **o), cov3D=torch.empty((P, 6), **o), sh=torch.empty((P, M, 3), **o),
+             scales=torch.empty((P, 3), **o), rotations=torch.empty((P, 4), **o))
+    if P != 0:
+        prm = Params(P, int(degree), int(M), int(F), W, H, float(tan_fovx), float(tan_fovy), float(scale_modifier),
+                     0, int(bool(debug)), _stream_ptr())
+        keep = [_f32c(t) for t in (background, means3D, sh, sh_objs, colors, scales, rotations, cov3D_precomp,
+                                   viewmatrix, projmatrix, campos)]
+        ups = [_f32c(t) for t in (dL_dout_depth, dL_dout_color, dL_dout_objects)]
+        with torch.cuda.device(dev):
+            rc = lib().gsr_backward(C.byref(prm), int(R), *[_ptr(t) for t in keep], _ptr(radii), _ptr(geomBuffer),
+                                    _ptr(binningBuffer), _ptr(imageBuffer), *[_ptr(t) for t in ups],
+                                    _ptr(g["means2D"]), _ptr(g["conic"]), _ptr(g["opacity"]), _ptr(g["depths"]),
+                                    _ptr(g["colors"]), _ptr(g["objects"]), _ptr(g["means3D"]), _ptr(g["cov3D"]),
+                                    _ptr(g["sh"]), _ptr(g["scales"]), _ptr(g["rotations"]))
+        _check(rc)
+        if scales is None or scales.numel() == 0:
+            g["scales"].zero_()
+            g["rotations"].zero_()
+    rasterize_gaussians_backward.last_internal = (g["conic"], g["depths"])
+    return (g["means2D"], g["colors"], g["objects"], g["opacity"], g["means3D"], g["cov3D"], g["sh"], g["scales"],
+            g["rotations"])
+
+
+def mark_visible(means3D, viewmatrix, projmatrix):
+    P = means3D.size(0)
+    present = torch.zeros((P,), dtype=torch.bool, device=means3D.device)
+    if P:
+        m, v, pj = _f32c(means3D), _f32c(viewmatrix), _f32c(projmatrix)
+        with torch.cuda.device(means3D.device):
+            _check(lib().gsr_mark_visible(P, _ptr(m), _ptr(v), _ptr(pj), _ptr(present), _stream_ptr()))
+    return present
+
+
+def distCUDA2(points):
+    P = points.size(0)
+    pts = _f32c(points)
+    out = torch.zeros((P,), dtype=torch.float32, device=points.device)
+    if P:
+        scratch = torch.empty(lib().gsr_knn_scratch_bytes(P) + 256, dtype=torch.uint8, device=points.device)
+        with torch.cuda.device(points.device):
+            _check(lib().gsr_knn(P, _ptr(pts), _ptr(out), _ptr(scratch), _stream_ptr()))
+    return out
+
+
+def export_state(P, D, M, F, W, H, R, geomBuffer, binningBuffer, imageBuffer):
+    """Parity/diagnostic dump (see gsr_export_state)."""
+    dev = geomBuffer.device
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    o = dict(device=dev)
+    st = dict(tiles_touched=torch.zeros(P, dtype=torch.int32, **o), depths=torch.zeros(P, dtype=torch.float32, **o),
+              means2D=torch.zeros((P, 2), dtype=torch.float32, **o),
+              conic_opacity=torch.zeros((P, 6), dtype=torch.float32, **o),
+              rgb=torch.zeros((P, 3), dtype=torch.float32, **o), clamped=torch.zeros((P, 3), dtype=torch.uint8, **o),
+              point_list=torch.zeros(max(R, 1), dtype=torch.int32, **o),
+              sorted_keys=torch.zeros(max(R, 1), dtype=torch.int64, **o),
+              ranges=torch.zeros((T, 2), dtype=torch.int32, **o), n_contrib=torch.zeros(H * W, dtype=torch.int32, **o),
+              final_T=torch.zeros(H * W, dtype=torch.float32, **o))
+    prm = Params(P, D, M, F, W, H, 1.0, 1.0, 1.0, 0, 0, _stream_ptr())
+    with torch.cuda.device(dev):
+        _check(lib().gsr_export_state(C.byref(prm), int(R), _ptr(geomBuffer), _ptr(binningBuffer), _ptr(imageBuffer),
+                                      *[_ptr(st[k]) for k in ("tiles_touched", "depths", "means2D", "conic_opacity",
+                                                              "rgb", "clamped", "point_list", "sorted_keys", "ranges",
+                                                              "n_contrib", "final_T")]))
+    st["point_list"] = st["point_list"][:R]
+    st["sorted_keys"] = st["sorted_keys"][:R]
+    return st
+
+
+def last_launch_count():
+    return int(lib().gsr_last_launch_count())

@@ -1,0 +1,197 @@
+"""Shared test plumbing: run the product (C-ABI via ctypes), the unmodified reference CUDA build
+(oracle/_ref) and the CPU oracle on the same seeded scene. Test infrastructure only."""
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG = os.path.join(ROOT, "segment-any-gaussian-splatting-slam_b200")
+for p in (ROOT, PKG):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+from gsraster_b200 import scenes  # noqa: E402
+
+REF_LIB = os.path.join(ROOT, "oracle", "_ref", "libref_rasterizer.so")
+REF_KNN_LIB = os.path.join(ROOT, "oracle", "_ref", "libref_knn.so")
+ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_size_t)
+
+
+def to_torch(scene, cam, device="cuda"):
+    import torch
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(device)
+    return dict(bg=t(scene.bg), means3D=t(scene.means3D), scales=t(scene.scales), rotations=t(scene.rotations),
+                opacities=t(scene.opacities), shs=t(scene.shs), sh_objs=t(scene.sh_objs),
+                viewmatrix=t(cam.viewmatrix), projmatrix=t(cam.projmatrix), campos=t(cam.campos))
+
+
+def run_mine(scene, cam, grads=None, colors_precomp=None, cov3D_precomp=None, debug=False):
+    """Product path through the C ABI. Returns dict of torch tensors (+ exported state)."""
+    import torch
+    from gsraster_b200 import capi
+    d = to_torch(scene, cam)
+    e = torch.empty(0, device="cuda")
+    sh = d["shs"] if colors_precomp is None else e
+    col = e if colors_precomp is None else torch.from_numpy(colors_precomp).cuda()
+    sc, rot, cov = (d["scales"], d["rotations"], e) if cov3D_precomp is None else (e, e, torch.from_numpy(cov3D_precomp).cuda())
+    F = scene.sh_objs.shape[-1]
+    R, depth, color, objects, radii, is_used, gb, bb, ib = capi.rasterize_gaussians(
+        d["bg"], d["means3D"], col, d["opacities"], sc, rot, scene.scale_modifier, cov, d["viewmatrix"],
+        d["projmatrix"], cam.tanfovx, cam.tanfovy, cam.H, cam.W, sh, d["sh_objs"], scene.sh_degree, d["campos"],
+        False, debug)
+    M = sh.size(1) if sh.numel() else 0
+    out = dict(R=R, depth=depth, color=color, objects=objects, radii=radii, is_used=is_used,
+               launches_fwd=capi.last_launch_count())
+    out.update(capi.export_state(scene.P, scene.sh_degree, M, F, cam.W, cam.H, R, gb, bb, ib))
+    if grads is not None:
+        gd, gc, go = [torch.from_numpy(g).cuda() for g in grads]
+        res = capi.rasterize_gaussians_backward(
+            d["bg"], d["means3D"], radii, col, sc, rot, scene.scale_modifier, cov, d["viewmatrix"], d["projmatrix"],
+            cam.tanfovx, cam.tanfovy, gd, gc, sh, go, d["sh_objs"], scene.sh_degree, d["campos"], gb, R, bb, ib, debug)
+        names = ("dL_dmeans2D", "dL_dcolors", "dL_dobjects", "dL_dopacity", "dL_dmeans3D", "dL_dcov3D", "dL_dsh",
+                 "dL_dscales", "dL_drotations")
+        out.update(dict(zip(names, res)))
+        out["dL_dconic"], out["dL_ddepths"] = capi.rasterize_gaussians_backward.last_internal
+        out["launches_bwd"] = capi.last_launch_count()
+    torch.cuda.synchronize()
+    return out
+
+
+class _RefAlloc:
+    def __init__(self):
+        import torch
+        self.t = torch.empty(0, dtype=torch.uint8, device="cuda")
+        self.cb = ALLOC_FN(self._alloc)
+
+    def _alloc(self, _ctx, n):
+        import torch
+        self.t = torch.empty(int(n) + 256, dtype=torch.uint8, device="cuda")
+        return self.t.data_ptr()
+
+
+_ref = None
+
+
+def ref_lib():
+    global _ref
+    if _ref is None:
+        _ref = C.CDLL(REF_LIB)
+        _ref.ref_forward.argtypes = [ALLOC_FN, C.c_void_p] * 3 + [C.c_int] * 3 + [C.c_void_p, C.c_int, C.c_int] + \
+            [C.c_void_p] * 6 + [C.c_float] + [C.c_void_p] * 5 + [C.c_float, C.c_float, C.c_int] + [C.c_void_p] * 5 + [C.c_int]
+        _ref.ref_backward.argtypes = [C.c_int] * 4 + [C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 5 + [C.c_float] + \
+            [C.c_void_p] * 5 + [C.c_float, C.c_float] + [C.c_void_p] * 18 + [C.c_int]
+        _ref.ref_decode_geom.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p]
+        _ref.ref_decode_img.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p]
+        _ref.ref_decode_binning.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p]
+    return _ref
+
+
+def have_ref():
+    return os.path.exists(REF_LIB)
+
+
+def _view(base_tensor, addr, count, dtype):
+    """torch view (copy) of `count` elements of dtype at absolute device address inside base_tensor."""
+    import torch
+    off = addr - base_tensor.data_ptr()
+    nbytes = count * torch.empty(0, dtype=dtype).element_size()
+    return base_tensor[off:off + nbytes].clone().view(dtype)
+
+
+def run_ref(scene, cam, grads=None, colors_precomp=None, cov3D_precomp=None):
+    """Unmodified reference CUDA rasterizer (built by oracle/build_ref.sh) through oracle/ref_shim.cu."""
+    import torch
+    L = ref_lib()
+    d = to_torch(scene, cam)
+    P, W, H = scene.P, cam.W, cam.H
+    F = scene.sh_objs.shape[-1]
+    assert F == L.ref_num_objects(), "reference build has NUM_OBJECTS=%d" % L.ref_num_objects()
+    p = lambda t: None if t is None else t.data_ptr()
+    sh = d["shs"] if colors_precomp is None else None
+    col = None if colors_precomp is None else torch.from_numpy(colors_precomp).cuda()
+    sc, rot = (d["scales"], d["rotations"]) if cov3D_precomp is None else (None, None)
+    cov = None if cov3D_precomp is None else torch.from_numpy(cov3D_precomp).cuda()
+    M = scene.shs.shape[1] if sh is not None else 0
+    z = lambda *s, dt=torch.float32: torch.zeros(*s, dtype=dt, device="cuda")
+    depth, color, objects = z(1, H, W), z(3, H, W), z(F, H, W)
+    radii, is_used = z(P, dt=torch.int32), z(P, dt=torch.bool)
+    ga, ba, ia = _RefAlloc(), _RefAlloc(), _RefAlloc()
+    R = L.ref_forward(ga.cb, None, ba.cb, None, ia.cb, None, P, scene.sh_degree, M, p(d["bg"]), W, H,
+                      p(d["means3D"]), p(sh), p(d["sh_objs"]), p(col), p(d["opacities"]), p(sc),
+                      scene.scale_modifier, p(rot), p(cov), p(d["viewmatrix"]), p(d["projmatrix"]), p(d["campos"]),
+                      cam.tanfovx, cam.tanfovy, 0, p(depth), p(color), p(objects), p(radii), p(is_used), 0)
+    torch.cuda.synchronize()
+    assert R >= 0
+    out = dict(R=R, depth=depth, color=color, objects=objects, radii=radii, is_used=is_used)
+    ptrs = (C.c_void_p * 9)()
+    L.ref_decode_geom(ga.t.data_ptr(), P, ptrs)
+    out["depths"] = _view(ga.t, ptrs[0], P, torch.float32)
+    out["clamped"] = _view(ga.t, ptrs[1], 3 * P, torch.uint8).view(P, 3)
+    out["means2D"] = _view(ga.t, ptrs[3], 2 * P, torch.float32).view(P, 2)
+    out["conic_opacity"] = _view(ga.t, ptrs[5], 6 * P, torch.float32).view(P, 6)
+    out["rgb"] = _view(ga.t, ptrs[6], 3 * P, torch.float32).view(P, 3)
+    out["tiles_touched"] = _view(ga.t, ptrs[7], P, torch.int32)
+    ptrs = (C.c_void_p * 6)()
+    L.ref_decode_img(ia.t.data_ptr(), W * H, ptrs)
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    out["final_T"] = _view(ia.t, ptrs[0], W * H, torch.float32)
+    out["n_contrib"] = _view(ia.t, ptrs[3], W * H, torch.int32)
+    out["ranges"] = _view(ia.t, ptrs[5], 2 * T, torch.int32).view(T, 2)
+    if R > 0:
+        ptrs = (C.c_void_p * 4)()
+        L.ref_decode_binning(ba.t.data_ptr(), R, ptrs)
+        out["point_list"] = _view(ba.t, ptrs[0], R, torch.int32)
+        out["sorted_keys"] = _view(ba.t, ptrs[2], R, torch.int64)
+    if grads is not None:
+        gd, gc, go = [torch.from_numpy(g).cuda() for g in grads]
+        g = dict(dL_dmeans2D=z(P, 3), dL_dconic=z(P, 6), dL_dopacity=z(P, 1), dL_ddepths=z(P, 1), dL_dcolors=z(P, 3),
+                 dL_dobjects=z(P, F), dL_dmeans3D=z(P, 3), dL_dcov3D=z(P, 6), dL_dsh=z(P, M, 3), dL_dscales=z(P, 3),
+                 dL_drotations=z(P, 4))
+        rc = L.ref_backward(P, scene.sh_degree, M, R, p(d["bg"]), W, H, p(d["means3D"]), p(sh), p(d["sh_objs"]),
+                            p(col), p(sc), scene.scale_modifier, p(rot), p(cov), p(d["viewmatrix"]),
+                            p(d["projmatrix"]), p(d["campos"]), cam.tanfovx, cam.tanfovy, p(radii), ga.t.data_ptr(),
+                            ba.t.data_ptr(), ia.t.data_ptr(), p(gd), p(gc), p(go), p(g["dL_dmeans2D"]),
+                            p(g["dL_dconic"]), p(g["dL_dopacity"]), p(g["dL_ddepths"]), p(g["dL_dcolors"]),
+                            p(g["dL_dobjects"]), p(g["dL_dmeans3D"]), p(g["dL_dcov3D"]), p(g["dL_dsh"]),
+                            p(g["dL_dscales"]), p(g["dL_drotations"]), 0)
+        torch.cuda.synchronize()
+        assert rc == 0
+        out.update(g)
+    out["_keep"] = (ga, ba, ia, d)
+    return out
+
+
+def run_oracle(scene, cam, grads=None, colors_precomp=None, cov3D_precomp=None):
+    from oracle import pyoracle as po
+    pr = po.Problem(scene, cam, colors_precomp=colors_precomp, cov3D_precomp=cov3D_precomp)
+    st = po.forward(pr)
+    out = dict(R=st["R"], depth=st["out_depth"], color=st["out_color"], objects=st["out_objects"],
+               radii=st["radii"], is_used=st["is_used"].astype(bool), tiles_touched=st["tiles_touched"],
+               depths=st["depths"], means2D=st["means2D"], conic_opacity=st["conic_opacity"], rgb=st["rgb"],
+               point_list=st["point_list"], sorted_keys=st["keys"], ranges=st["ranges"], n_contrib=st["n_contrib"],
+               final_T=st["final_T"])
+    if grads is not None:
+        g = po.backward(pr, st, *grads)
+        out.update(dL_dmeans2D=g["dL_dmean2D"], dL_dconic=g["dL_dconic"], dL_dopacity=g["dL_dopacity"],
+                   dL_ddepths=g["dL_ddepths"], dL_dcolors=g["dL_dcolors"], dL_dobjects=g["dL_dobjects"],
+                   dL_dmeans3D=g["dL_dmean3D"], dL_dcov3D=g["dL_dcov3D"], dL_dsh=g["dL_dsh"],
+                   dL_dscales=g["dL_dscale"], dL_drotations=g["dL_drot"])
+    return out
+
+
+def npy(x):
+    return x.detach().cpu().numpy() if hasattr(x, "detach") else np.asarray(x)
+
+
+GRAD_KEYS = ("dL_dmeans2D", "dL_dconic", "dL_dopacity", "dL_ddepths", "dL_dcolors", "dL_dobjects", "dL_dmeans3D",
+             "dL_dcov3D", "dL_dsh", "dL_dscales", "dL_drotations")
+
+
+def grad_rel_err(a, b):
+    """Tensor-relative error used for the 'relative 1e-3' gradient bar: max|a-b| / max|b|
+    (float atomics make the reference itself non-deterministic in the last bits)."""
+    a, b = npy(a).astype(np.float64), npy(b).astype(np.float64)
+    den = np.abs(b).max()
+    return float(np.abs(a - b).max() / den) if den > 0 else float(np.abs(a).max())
