@@ -7,16 +7,17 @@
 
 namespace gsr {
 
-// SH constants: reference auxiliary.h:22-39
-__device__ constexpr float SH_C0 = 0.28209479177387814f;
-__device__ constexpr float SH_C1 = 0.4886025119029199f;
-__device__ constexpr float SH_C2_0 = 1.0925484305920792f, SH_C2_1 = -1.0925484305920792f,
-                           SH_C2_2 = 0.31539156525252005f, SH_C2_3 = -1.0925484305920792f,
-                           SH_C2_4 = 0.5462742152960396f;
-__device__ constexpr float SH_C3_0 = -0.5900435899266435f, SH_C3_1 = 2.890611442640554f,
-                           SH_C3_2 = -0.4570457994644658f, SH_C3_3 = 0.3731763325901154f,
-                           SH_C3_4 = -0.4570457994644658f, SH_C3_5 = 1.445305721320277f,
-                           SH_C3_6 = -0.5900435899266435f;
+// SH constants: reference auxiliary.h:22-39. Kept as __device__ const objects/arrays (not constexpr
+// immediates) on purpose: with immediates the compiler rewrites x + (-c)*y into x - c*y before FMA
+// contraction and the subtraction is then left unfused, which changes the rounding of the SH colour
+// relative to the reference build (observed: 11 % of rgb values off by 1 ulp).
+__device__ const float SH_C0 = 0.28209479177387814f;
+__device__ const float SH_C1 = 0.4886025119029199f;
+__device__ const float SH_C2[] = {1.0925484305920792f, -1.0925484305920792f, 0.31539156525252005f,
+                                  -1.0925484305920792f, 0.5462742152960396f};
+__device__ const float SH_C3[] = {-0.5900435899266435f, 2.890611442640554f, -0.4570457994644658f,
+                                  0.3731763325901154f, -0.4570457994644658f, 1.445305721320277f,
+                                  -0.5900435899266435f};
 
 // Column-major 3x3: c[col][row], product in the same term order as glm's mat3*mat3
 // (third_party/glm/glm/detail/type_mat3x3.inl:486-518): R[c][r] = A[0][r]B[c][0] + A[1][r]B[c][1] + A[2][r]B[c][2].

@@ -21,39 +21,49 @@ void launch_mark_visible(int P, const float* means3D, const float* view, uint8_t
   mark_visible_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, means3D, view, present);
 }
 
-// SH -> RGB for one Gaussian (reference forward.cu:20-71). sh points at this Gaussian's M*3 floats.
+// 3-vector with the operator set glm::vec3 offers; SH evaluation below is written on it so the
+// operation DAG (and with it nvcc's FMA contraction) matches the reference build bit for bit.
+struct V3 {
+  float x, y, z;
+};
+__device__ __forceinline__ V3 operator*(float s, const V3& v) { return {s * v.x, s * v.y, s * v.z}; }
+__device__ __forceinline__ V3 operator+(const V3& a, const V3& b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+__device__ __forceinline__ V3 operator-(const V3& a, const V3& b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+
+// SH -> RGB for one Gaussian (reference forward.cu:20-71). shp points at this Gaussian's M*3 floats.
 __device__ __forceinline__ void sh_to_rgb(int deg, const float3 pos, const float* campos,
-                                          const float* __restrict__ sh, float* rgb, unsigned& clamped_bits) {
-  float3 dir = {pos.x - campos[0], pos.y - campos[1], pos.z - campos[2]};
+                                          const float* __restrict__ shp, float* rgb, unsigned& clamped_bits) {
+  const V3* sh = reinterpret_cast<const V3*>(shp);
+  V3 dir = {pos.x - campos[0], pos.y - campos[1], pos.z - campos[2]};
   float len = sqrtf(dir.x * dir.x + dir.y * dir.y + dir.z * dir.z);
-  dir.x = dir.x / len; dir.y = dir.y / len; dir.z = dir.z / len;
-  float x = dir.x, y = dir.y, z = dir.z;
-  float xx = x * x, yy = y * y, zz = z * z;
-  float xy = x * y, yz = y * z, xz = x * z;
-  clamped_bits = 0;
-#pragma unroll
-  for (int c = 0; c < 3; c++) {
-#define SH(k) sh[3 * (k) + c]
-    float result = SH_C0 * SH(0);
-    if (deg > 0) {
-      result = result - SH_C1 * y * SH(1) + SH_C1 * z * SH(2) - SH_C1 * x * SH(3);
-      if (deg > 1) {
-        result = result + SH_C2_0 * xy * SH(4) + SH_C2_1 * yz * SH(5) + SH_C2_2 * (2.0f * zz - xx - yy) * SH(6) +
-                 SH_C2_3 * xz * SH(7) + SH_C2_4 * (xx - yy) * SH(8);
-        if (deg > 2) {
-          result = result + SH_C3_0 * y * (3.0f * xx - yy) * SH(9) + SH_C3_1 * xy * z * SH(10) +
-                   SH_C3_2 * y * (4.0f * zz - xx - yy) * SH(11) +
-                   SH_C3_3 * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * SH(12) +
-                   SH_C3_4 * x * (4.0f * zz - xx - yy) * SH(13) + SH_C3_5 * z * (xx - yy) * SH(14) +
-                   SH_C3_6 * x * (xx - 3.0f * yy) * SH(15);
-        }
+  dir = {dir.x / len, dir.y / len, dir.z / len};
+  V3 result = SH_C0 * sh[0];
+  if (deg > 0) {
+    float x = dir.x;
+    float y = dir.y;
+    float z = dir.z;
+    result = result - SH_C1 * y * sh[1] + SH_C1 * z * sh[2] - SH_C1 * x * sh[3];
+    if (deg > 1) {
+      float xx = x * x, yy = y * y, zz = z * z;
+      float xy = x * y, yz = y * z, xz = x * z;
+      result = result + SH_C2[0] * xy * sh[4] + SH_C2[1] * yz * sh[5] + SH_C2[2] * (2.0f * zz - xx - yy) * sh[6] +
+               SH_C2[3] * xz * sh[7] + SH_C2[4] * (xx - yy) * sh[8];
+      if (deg > 2) {
+        result = result + SH_C3[0] * y * (3.0f * xx - yy) * sh[9] + SH_C3[1] * xy * z * sh[10] +
+                 SH_C3[2] * y * (4.0f * zz - xx - yy) * sh[11] +
+                 SH_C3[3] * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * sh[12] +
+                 SH_C3[4] * x * (4.0f * zz - xx - yy) * sh[13] + SH_C3[5] * z * (xx - yy) * sh[14] +
+                 SH_C3[6] * x * (xx - 3.0f * yy) * sh[15];
       }
     }
-#undef SH
-    result += 0.5f;
-    if (result < 0) clamped_bits |= 1u << c;
-    rgb[c] = fmaxf(result, 0.0f);
   }
+  result.x += 0.5f;
+  result.y += 0.5f;
+  result.z += 0.5f;
+  clamped_bits = (result.x < 0 ? 1u : 0u) | (result.y < 0 ? 2u : 0u) | (result.z < 0 ? 4u : 0u);
+  rgb[0] = fmaxf(result.x, 0.0f);
+  rgb[1] = fmaxf(result.y, 0.0f);
+  rgb[2] = fmaxf(result.z, 0.0f);
 }
 
 __global__ void __launch_bounds__(256)

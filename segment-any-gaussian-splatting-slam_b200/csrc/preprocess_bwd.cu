@@ -162,12 +162,12 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
       float basis[16];
       basis[0] = SH_C0;
       basis[1] = -SH_C1 * y; basis[2] = SH_C1 * z; basis[3] = -SH_C1 * x;
-      basis[4] = SH_C2_0 * xy; basis[5] = SH_C2_1 * yz; basis[6] = SH_C2_2 * (2.f * zz - xx - yy);
-      basis[7] = SH_C2_3 * xz; basis[8] = SH_C2_4 * (xx - yy);
-      basis[9] = SH_C3_0 * y * (3.f * xx - yy); basis[10] = SH_C3_1 * xy * z;
-      basis[11] = SH_C3_2 * y * (4.f * zz - xx - yy); basis[12] = SH_C3_3 * z * (2.f * zz - 3.f * xx - 3.f * yy);
-      basis[13] = SH_C3_4 * x * (4.f * zz - xx - yy); basis[14] = SH_C3_5 * z * (xx - yy);
-      basis[15] = SH_C3_6 * x * (xx - 3.f * yy);
+      basis[4] = SH_C2[0] * xy; basis[5] = SH_C2[1] * yz; basis[6] = SH_C2[2] * (2.f * zz - xx - yy);
+      basis[7] = SH_C2[3] * xz; basis[8] = SH_C2[4] * (xx - yy);
+      basis[9] = SH_C3[0] * y * (3.f * xx - yy); basis[10] = SH_C3[1] * xy * z;
+      basis[11] = SH_C3[2] * y * (4.f * zz - xx - yy); basis[12] = SH_C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy);
+      basis[13] = SH_C3[4] * x * (4.f * zz - xx - yy); basis[14] = SH_C3[5] * z * (xx - yy);
+      basis[15] = SH_C3[6] * x * (xx - 3.f * yy);
       const int ncoef = (D + 1) * (D + 1);
 #pragma unroll
       for (int k = 0; k < 16; k++) {
@@ -184,19 +184,19 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
         if (D > 0) {
           dRGBdx = -SH_C1 * S(3); dRGBdy = -SH_C1 * S(1); dRGBdz = SH_C1 * S(2);
           if (D > 1) {
-            dRGBdx += SH_C2_0 * y * S(4) + SH_C2_2 * 2.f * -x * S(6) + SH_C2_3 * z * S(7) + SH_C2_4 * 2.f * x * S(8);
-            dRGBdy += SH_C2_0 * x * S(4) + SH_C2_1 * z * S(5) + SH_C2_2 * 2.f * -y * S(6) + SH_C2_4 * 2.f * -y * S(8);
-            dRGBdz += SH_C2_1 * y * S(5) + SH_C2_2 * 2.f * 2.f * z * S(6) + SH_C2_3 * x * S(7);
+            dRGBdx += SH_C2[0] * y * S(4) + SH_C2[2] * 2.f * -x * S(6) + SH_C2[3] * z * S(7) + SH_C2[4] * 2.f * x * S(8);
+            dRGBdy += SH_C2[0] * x * S(4) + SH_C2[1] * z * S(5) + SH_C2[2] * 2.f * -y * S(6) + SH_C2[4] * 2.f * -y * S(8);
+            dRGBdz += SH_C2[1] * y * S(5) + SH_C2[2] * 2.f * 2.f * z * S(6) + SH_C2[3] * x * S(7);
             if (D > 2) {
-              dRGBdx += (SH_C3_0 * S(9) * 3.f * 2.f * xy + SH_C3_1 * S(10) * yz + SH_C3_2 * S(11) * -2.f * xy +
-                         SH_C3_3 * S(12) * -3.f * 2.f * xz + SH_C3_4 * S(13) * (-3.f * xx + 4.f * zz - yy) +
-                         SH_C3_5 * S(14) * 2.f * xz + SH_C3_6 * S(15) * 3.f * (xx - yy));
-              dRGBdy += (SH_C3_0 * S(9) * 3.f * (xx - yy) + SH_C3_1 * S(10) * xz +
-                         SH_C3_2 * S(11) * (-3.f * yy + 4.f * zz - xx) + SH_C3_3 * S(12) * -3.f * 2.f * yz +
-                         SH_C3_4 * S(13) * -2.f * xy + SH_C3_5 * S(14) * -2.f * yz + SH_C3_6 * S(15) * -3.f * 2.f * xy);
-              dRGBdz += (SH_C3_1 * S(10) * xy + SH_C3_2 * S(11) * 4.f * 2.f * yz +
-                         SH_C3_3 * S(12) * 3.f * (2.f * zz - xx - yy) + SH_C3_4 * S(13) * 4.f * 2.f * xz +
-                         SH_C3_5 * S(14) * (xx - yy));
+              dRGBdx += (SH_C3[0] * S(9) * 3.f * 2.f * xy + SH_C3[1] * S(10) * yz + SH_C3[2] * S(11) * -2.f * xy +
+                         SH_C3[3] * S(12) * -3.f * 2.f * xz + SH_C3[4] * S(13) * (-3.f * xx + 4.f * zz - yy) +
+                         SH_C3[5] * S(14) * 2.f * xz + SH_C3[6] * S(15) * 3.f * (xx - yy));
+              dRGBdy += (SH_C3[0] * S(9) * 3.f * (xx - yy) + SH_C3[1] * S(10) * xz +
+                         SH_C3[2] * S(11) * (-3.f * yy + 4.f * zz - xx) + SH_C3[3] * S(12) * -3.f * 2.f * yz +
+                         SH_C3[4] * S(13) * -2.f * xy + SH_C3[5] * S(14) * -2.f * yz + SH_C3[6] * S(15) * -3.f * 2.f * xy);
+              dRGBdz += (SH_C3[1] * S(10) * xy + SH_C3[2] * S(11) * 4.f * 2.f * yz +
+                         SH_C3[3] * S(12) * 3.f * (2.f * zz - xx - yy) + SH_C3[4] * S(13) * 4.f * 2.f * xz +
+                         SH_C3[5] * S(14) * (xx - yy));
             }
           }
         }

@@ -195,3 +195,14 @@ def grad_rel_err(a, b):
     a, b = npy(a).astype(np.float64), npy(b).astype(np.float64)
     den = np.abs(b).max()
     return float(np.abs(a - b).max() / den) if den > 0 else float(np.abs(a).max())
+
+
+def run_ref_knn(points_np):
+    import torch
+    L = C.CDLL(REF_KNN_LIB)
+    L.ref_knn.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
+    pts = torch.from_numpy(np.ascontiguousarray(points_np, dtype=np.float32)).cuda()
+    out = torch.zeros(pts.shape[0], dtype=torch.float32, device="cuda")
+    L.ref_knn(pts.shape[0], pts.data_ptr(), out.data_ptr())
+    torch.cuda.synchronize()
+    return out
