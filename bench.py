@@ -1,0 +1,411 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the rasterizer hot path (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl mine|reference]
+
+A "step" is one mapping iteration of the hot path on one keyframe view: rasterizer forward +
+backward (rasterize_gaussians + rasterize_gaussians_backward through the C ABI) on the headline
+workload: 1M Gaussians, 1280x1024, SH degree 3 (M=16), 16-d feature. With N GPUs every rank
+rasterizes its own view per step against replicated Gaussians and the parameter gradients are
+summed with one NCCL all-reduce (weak scaling); value = view-iterations/s over all ranks.
+
+--impl reference times the UNMODIFIED reference CUDA rasterizer (oracle/_ref, built by
+oracle/build_ref.sh for sm_100a) on the same workload on GPU 0 (the reference has no CPU path and
+no multi-GPU path); if oracle/_ref is absent it falls back to timing the CPU oracle port.
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "segment-any-gaussian-splatting-slam_b200")
+for _p in (ROOT, PKG):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+METRIC = "mapping_iters_per_sec_fwd_bwd"
+UNIT = "iters/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="mine", choices=["mine", "reference"])
+    ap.add_argument("--P", type=int, default=1_000_000)
+    ap.add_argument("--width", type=int, default=1280)
+    ap.add_argument("--height", type=int, default=1024)
+    ap.add_argument("--F", type=int, default=16)
+    ap.add_argument("--deg", type=int, default=3)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        d = json.load(open(path))
+        return dict(hbm_gbs=float(d["hbm_gbs"]), sm_max_mhz=float(d.get("sm_max_mhz", 1965.0)), source="measured")
+    return dict(hbm_gbs=6650.0, sm_max_mhz=1965.0, source="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
+        self.proc.terminate()
+        self.th.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return dict(sm_mhz=sm[len(sm) // 2] if sm else None, sm_max_mhz=max(mx) if mx else None,
+                    reasons=sorted(reasons), samples=len(sm))
+
+
+def make_workload(args, view, device):
+    """Seeded synthetic scene of the headline shape, tensors resident on `device`."""
+    import numpy as np
+    import torch
+    from gsraster_b200 import scenes
+    sc = scenes.make_scene(args.P, sh_degree=args.deg, F=args.F, seed=1234, W=args.width, H=args.height)
+    cam = scenes.make_camera(args.width, args.height, view)
+    grads = scenes.make_upstream_grads(args.width, args.height, args.F)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(device)
+    d = dict(bg=t(sc.bg), means3D=t(sc.means3D), scales=t(sc.scales), rotations=t(sc.rotations),
+             opacities=t(sc.opacities), shs=t(sc.shs), sh_objs=t(sc.sh_objs), viewmatrix=t(cam.viewmatrix),
+             projmatrix=t(cam.projmatrix), campos=t(cam.campos))
+    g = [t(x) for x in grads]
+    return sc, cam, d, g
+
+
+def stage_model(args, stats):
+    """ALGORITHMIC bytes / flops per launch of each stage (restated in DESIGN.md).
+    stats: P, Pvis, R, Npix, n_eval_fwd, n_blend, n_eval_bwd."""
+    P, Pv, R, N = stats["P"], stats["Pvis"], stats["R"], stats["Npix"]
+    M, F = (args.deg + 1) ** 2, args.F
+    tile_passes = 2 if ((args.width + 15) // 16) * ((args.height + 15) // 16) > 256 else 1
+    return {
+        "preprocess": ("hbm", Pv * (44 + 12 * M + 84) + (P - Pv) * 20),
+        # 4 depth passes over P 8-byte items (hist read + scatter read + write) + count/scan of tiles_touched
+        "depth_sort_count": ("hbm", P * (4 * 24 + 12)),
+        # emission (20 B/Gaussian + 8 B/instance) + tile passes (24 B/instance each) + ranges/point list (12 B/instance)
+        "emit_tile_sort_ranges": ("hbm", P * 20 + R * (8 + 24 * tile_passes + 12)),
+        "render_fwd": ("fp32", 13 * stats["n_eval_fwd"] + (15 + 2 * (3 + F)) * stats["n_blend"]),
+        "render_bwd": ("fp32", 13 * stats["n_eval_bwd"] + (100 + 7 * (3 + F)) * stats["n_blend"]),
+        "preprocess_bwd": ("hbm", Pv * ((95 + 12 * M) + (64 + 12 * M)) + (P - Pv) * 4),
+    }
+
+
+def load_traffic():
+    path = os.path.join(ROOT, "profiles", "traffic.json")
+    return json.load(open(path)) if os.path.exists(path) else {}
+
+
+def run_mine(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from gsraster_b200 import capi, mapping
+    dev = torch.device("cuda", local_rank)
+    sc, cam, d, g = make_workload(args, view=rank, device=dev)
+    P, W, H, F, deg = args.P, args.width, args.height, args.F, args.deg
+    M = (deg + 1) ** 2
+    e = torch.empty(0, device=dev)
+    bucket = mapping.GradBucket(P, M, F, dev)
+    launches = [0]
+
+    def fwd(dd):
+        return capi.rasterize_gaussians(dd["bg"], dd["means3D"], e, dd["opacities"], dd["scales"], dd["rotations"],
+                                        1.0, e, dd["viewmatrix"], dd["projmatrix"], cam.tanfovx, cam.tanfovy, H, W,
+                                        dd["shs"], dd["sh_objs"], deg, dd["campos"], False, False)
+
+    def bwd(dd, res, gd, gc, go):
+        R, depth, color, objects, radii, is_used, gb, bb, ib = res
+        return capi.rasterize_gaussians_backward(dd["bg"], dd["means3D"], radii, e, dd["scales"], dd["rotations"], 1.0,
+                                                 e, dd["viewmatrix"], dd["projmatrix"], cam.tanfovx, cam.tanfovy, gd,
+                                                 gc, dd["shs"], go, dd["sh_objs"], deg, dd["campos"], gb, R, bb, ib,
+                                                 False, out=bucket.views)
+
+    def step():
+        res = fwd(d)
+        launches[0] += capi.last_launch_count()
+        bwd(d, res, g[0], g[1], g[2])
+        launches[0] += capi.last_launch_count()
+        if world > 1:
+            dist.all_reduce(bucket.flat)
+        return res
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        res = step()
+    sync_all()
+    # workload statistics for the roofline model (outside the timed region)
+    R = res[0]
+    st = capi.export_state(P, deg, M, F, W, H, R, res[6], res[7], res[8])
+    cp = capi.count_pairs(P, deg, M, F, W, H, R, res[6], res[7], res[8])
+    stats = dict(P=P, Pvis=int((res[4] > 0).sum()), R=int(R), Npix=W * H, n_eval_fwd=cp["evaluated"],
+                 n_blend=cp["blended"], n_eval_bwd=int(st["n_contrib"].to(torch.int64).sum()),
+                 warp_blended=cp["warp_blended"])
+    del st
+
+    # ---- timed region 1: inputs resident in HBM ----
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    capi.set_stage_timing(True)
+    capi.get_stage_times()
+    launches[0] = 0
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sync_all()
+    ev0.record()
+    for _ in range(args.steps):
+        step()
+    ev1.record()
+    sync_all()
+    ms = ev0.elapsed_time(ev1)
+    stage_ms = capi.get_stage_times()
+    capi.set_stage_timing(False)
+    n_launch = launches[0]
+
+    # ---- timed region 2: end to end with host buffers ----
+    e2e = None
+    if not args.no_e2e:
+        e2e = run_e2e(args, cam, d, g, fwd, bwd, bucket, world, dev, sync_all)
+    clk = clocks.stop()
+    if world > 1:
+        t = torch.tensor([ms, e2e["ms"] if e2e else 0.0], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t[0])
+        if e2e:
+            e2e["ms"] = float(t[1])
+    return dict(ms=ms, stage_ms=stage_ms, stats=stats, launches=n_launch, e2e=e2e, clocks=clk,
+                bucket_bytes=bucket.nbytes)
+
+
+def run_e2e(args, cam, d, g, fwd, bwd, bucket, world, dev, sync_all):
+    """Same step through the public API with HOST buffers: per step the keyframe (view matrix,
+    projection matrix, camera centre, ground-truth RGB image) is copied from pinned host memory, an
+    L1 photometric loss on the rendered colour produces dL/dcolour on the device, and the loss
+    scalar is read back. Gaussian parameters stay resident (they are the optimiser's state)."""
+    import torch
+    import torch.distributed as dist
+    W, H = args.width, args.height
+    pin = lambda t: t.detach().cpu().pin_memory()
+    h_view, h_proj, h_campos = pin(d["viewmatrix"]), pin(d["projmatrix"]), pin(d["campos"])
+    torch.manual_seed(7)
+    h_gt = torch.rand(3, H, W).pin_memory()
+    dd = dict(d)
+    dd["viewmatrix"], dd["projmatrix"], dd["campos"] = (torch.empty_like(d["viewmatrix"]),
+                                                         torch.empty_like(d["projmatrix"]),
+                                                         torch.empty_like(d["campos"]))
+    gt = torch.empty(3, H, W, device=dev)
+    h2d = sum(t.numel() * 4 for t in (h_view, h_proj, h_campos, h_gt))
+    inv_n = 1.0 / (3 * H * W)
+
+    def step():
+        dd["viewmatrix"].copy_(h_view, non_blocking=True)
+        dd["projmatrix"].copy_(h_proj, non_blocking=True)
+        dd["campos"].copy_(h_campos, non_blocking=True)
+        gt.copy_(h_gt, non_blocking=True)
+        res = fwd(dd)
+        diff = res[2] - gt
+        loss = diff.abs().sum() * inv_n
+        bwd(dd, res, g[0], torch.sign(diff) * inv_n, g[2])
+        if world > 1:
+            dist.all_reduce(bucket.flat)
+        return float(loss.item())  # 4-byte D2H of the step's result
+
+    for _ in range(3):
+        step()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sync_all()
+    ev0.record()
+    for _ in range(args.steps):
+        loss = step()
+    ev1.record()
+    sync_all()
+    return dict(ms=ev0.elapsed_time(ev1), h2d=h2d, d2h=4, loss=loss)
+
+
+def cpu_baseline(args, threads=None):
+    """CPU oracle port (oracle/oracle.cpp, OpenMP) timed on the host cores on a bounded sample."""
+    import numpy as np
+    from gsraster_b200 import scenes
+    from oracle import pyoracle as po
+    po.build()
+    cores = po.num_threads()
+    # bounded sample: the full camera/resolution with P scaled so the sample stays in the 10-30 s range
+    Ps = args.P if cores >= 32 else min(args.P, 250_000)
+    sc = scenes.make_scene(Ps, sh_degree=args.deg, F=args.F, seed=1234, W=args.width, H=args.height)
+    cam = scenes.make_camera(args.width, args.height, 0)
+    grads = scenes.make_upstream_grads(args.width, args.height, args.F)
+    pr = po.Problem(sc, cam)
+    t0 = time.time()
+    st = po.forward(pr)
+    po.backward(pr, st, *grads)
+    dt = time.time() - t0
+    sample = "1 fwd+bwd iteration, %d Gaussians (of %d), %dx%d, deg %d, F=%d, R=%d" % (
+        Ps, args.P, args.width, args.height, args.deg, args.F, st["R"])
+    return dict(value=1.0 / dt, unit=UNIT, cores=cores, kind="port", sample=sample, seconds=dt)
+
+
+def run_reference(args):
+    """Reference arm: unmodified reference CUDA rasterizer (oracle/_ref) on GPU 0, same workload."""
+    import torch
+    from oracle import refcuda
+    cfg = dict(workload="headline: 1 view fwd+bwd, %d Gaussians, %dx%d, SH deg %d, F=%d" % (
+        args.P, args.width, args.height, args.deg, args.F), l2="inputs (>=300 MB) larger than the 126 MB L2")
+    if not (torch.cuda.is_available() and refcuda.available(args.F)):
+        cb = cpu_baseline(args)
+        ms = 1e3 * cb["seconds"]
+        return dict(metric=METRIC, value=cb["value"], unit=UNIT, n_gpus=0, steps=1, warmup=0, ms_per_step=ms,
+                    higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
+                    config=cfg, impl="reference", cpu_baseline={k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+                    e2e=dict(value=cb["value"], unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0),
+                    note="oracle/_ref (reference CUDA build) not available: CPU oracle port timed instead")
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    sc, cam, d, g = make_workload(args, view=0, device=dev)
+    ref = refcuda.RefRasterizer(args.F)
+    W, H = args.width, args.height
+
+    def step():
+        R, depth, color, objects, radii, is_used, bufs = ref.forward(d, W, H, cam.tanfovx, cam.tanfovy, args.deg)
+        ref.backward(d, W, H, cam.tanfovx, cam.tanfovy, args.deg, R, radii, bufs, g[0], g[1], g[2])
+        return R
+
+    for _ in range(max(args.warmup, 3)):
+        R = step()
+    torch.cuda.synchronize()
+    clocks = ClockSampler(0)
+    clocks.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(args.steps):
+        step()
+    ev1.record()
+    torch.cuda.synchronize()
+    ms = ev0.elapsed_time(ev1)
+    clk = clocks.stop()
+    value = args.steps / (ms * 1e-3)
+    return dict(metric=METRIC, value=value, unit=UNIT, n_gpus=1, steps=args.steps, warmup=max(args.warmup, 3),
+                ms_per_step=ms / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32",
+                data="synthetic", config=dict(cfg, R=int(R)), impl="reference", clocks=clk,
+                cpu_baseline=dict(value=value, unit=UNIT, cores=0, kind="reference",
+                                  sample="unmodified reference CUDA rasterizer built for sm_100a (oracle/_ref), "
+                                         "run on GPU 0: the reference has no CPU implementation of this path"),
+                e2e=dict(value=value, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0))
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        if rank == 0:
+            print(json.dumps(run_reference(args)), flush=True)
+        return 0
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    r = run_mine(args, rank, world, local_rank)
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    if rank != 0:
+        if world > 1:
+            torch.distributed.destroy_process_group()
+        return 0
+    pk = peaks()
+    K = args.steps
+    ms = r["ms"]
+    value = world * K / (ms * 1e-3)
+    # per-stage roofline (events recorded inside the timed region, per launch = per step)
+    model = stage_model(args, r["stats"])
+    fp32_peak = 148 * 128 * 2 * pk["sm_max_mhz"] * 1e6 / 1e12  # TFLOP/s at clocks.max.sm, non-tensor FMA pipes
+    traffic = load_traffic()
+    stages = {}
+    for name, (bound, work) in model.items():
+        t = r["stage_ms"][name] / K * 1e-3
+        if bound == "hbm":
+            ach, peak, unit = work / t / 1e9, pk["hbm_gbs"], "GB/s"
+        else:
+            ach, peak, unit = work / t / 1e12, fp32_peak, "TFLOP/s"
+        stages[name] = dict(ms=round(t * 1e3, 4), bound=bound, achieved=round(ach, 3), peak=round(peak, 1), unit=unit,
+                            frac=round(ach / peak, 4), work=int(work), traffic=traffic.get(name))
+    top = max(stages, key=lambda k: stages[k]["ms"])
+    roof = dict(kernel=top, **{k: stages[top][k] for k in ("bound", "achieved", "peak", "unit", "frac", "traffic")},
+                peak_source=("MEASURED_PEAKS.json hbm_gbs" if stages[top]["bound"] == "hbm" else
+                             "148 SM x 128 FMA lanes x 2 x clocks.max.sm (no fp32 figure in MEASURED_PEAKS.json)") +
+                            " (%s)" % pk["source"])
+    out = dict(metric=METRIC, value=round(value, 4), unit=UNIT, n_gpus=world, steps=K, warmup=max(args.warmup, 3),
+               ms_per_step=round(ms / K, 4), higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32",
+               data="synthetic",
+               config=dict(workload="headline: 1 view fwd+bwd per GPU per step, %d Gaussians, %dx%d, SH deg %d (M=%d), "
+                                    "F=%d feature channels" % (args.P, args.width, args.height, args.deg,
+                                                               (args.deg + 1) ** 2, args.F),
+                           parallelism="view-data-parallel x%d, replicated Gaussians, 1 all-reduce of %d MB/step" % (
+                               world, r["bucket_bytes"] // 1000000) if world > 1 else "single GPU",
+                           l2="inputs (>=300 MB of Gaussian parameters) larger than the 126 MB L2; no flush needed",
+                           **{k: r["stats"][k] for k in ("Pvis", "R", "n_eval_fwd", "n_blend", "n_eval_bwd")}),
+               gpu_launches=r["launches"], clocks=r["clocks"], roofline=roof, stages=stages)
+    if r["e2e"]:
+        e = r["e2e"]
+        out["e2e"] = dict(value=round(world * K / (e["ms"] * 1e-3), 4), unit=UNIT, h2d_bytes_per_step=e["h2d"],
+                          d2h_bytes_per_step=e["d2h"], ms_per_step=round(e["ms"] / K, 4))
+    if world == 1 and not args.no_cpu_baseline:
+        cb = cpu_baseline(args)
+        out["cpu_baseline"] = {k: (round(cb[k], 5) if k == "value" else cb[k]) for k in ("value", "unit", "cores", "kind", "sample")}
+    print(json.dumps(out), flush=True)
+    if world > 1:
+        torch.distributed.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

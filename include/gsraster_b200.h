@@ -106,6 +106,25 @@ size_t gsr_geom_bytes(int P);
 size_t gsr_image_bytes(int width, int height);
 size_t gsr_binning_bytes(int64_t num_rendered);
 
+/* Per-stage device timing for the roofline report (bench.py): when enabled, every forward /
+ * backward call brackets each stage with CUDA events on params->stream. gsr_get_stage_times
+ * synchronises those events, ADDS the elapsed milliseconds since the last call of
+ * gsr_get_stage_times into ms[GSR_NUM_STAGES] (caller zero-initialises) and forgets them.
+ * Stages: 0 preprocess (K1), 1 depth sort + tile count/scan, 2 emission + tile sort + ranges,
+ * 3 forward blend (K4), 4 backward blend (K5), 5 backward preprocess (K6+K7). No reference
+ * equivalent (the reference has no timers). */
+#define GSR_NUM_STAGES 6
+int gsr_set_stage_timing(int enable);
+int gsr_get_stage_times(float* ms);
+
+/* Work counters of a finished forward pass, for the FP32 roofline of the blend kernels
+ * (SURVEY.md 8d "N_eval / N_contrib"): replays the blend tests (no blending) and returns on the
+ * HOST counts[0] = (pixel, Gaussian) pairs evaluated by a per-pixel early-exit walk,
+ * counts[1] = pairs blended (alpha >= 1/255 and T kept above 1e-4), counts[2] = (warp, Gaussian)
+ * pairs with at least one blended lane, counts[3] = staged tile instances. Synchronises. */
+int gsr_count_pairs(const gsr_params* params, int num_rendered, const char* geom_buffer,
+                    const char* binning_buffer, const char* image_buffer, unsigned long long* counts);
+
 /* Kernel launches issued by the last forward/backward/knn call on this thread (for bench.py). */
 int gsr_last_launch_count(void);
 

@@ -23,6 +23,16 @@ if [ ! -f "$OUT/libref_rasterizer.so" ] || [ "${FORCE:-0}" = 1 ]; then
     "$DGR/cuda_rasterizer/rasterizer_impl.cu" "$HERE/ref_shim.cu" \
     -o "$OUT/libref_rasterizer.so"
 fi
+# NUM_OBJECTS=32 variant for config 4 (config.h:16 has no #ifndef guard: oracle/ref_config_f32.h is
+# force-included, pre-defines the include guard and supplies the four constants; sources stay untouched).
+if [ ! -f "$OUT/libref_rasterizer_f32.so" ] || [ "${FORCE:-0}" = 1 ]; then
+  "$NVCC" -O3 -std=c++17 $ARCH -lineinfo -Xcompiler -fPIC -shared -w \
+    -include "$HERE/ref_config_f32.h" \
+    -I "$DGR/third_party/glm" -I "$DGR/cuda_rasterizer" \
+    "$DGR/cuda_rasterizer/forward.cu" "$DGR/cuda_rasterizer/backward.cu" \
+    "$DGR/cuda_rasterizer/rasterizer_impl.cu" "$HERE/ref_shim.cu" \
+    -o "$OUT/libref_rasterizer_f32.so"
+fi
 if [ ! -f "$OUT/libref_knn.so" ] || [ "${FORCE:-0}" = 1 ]; then
   "$NVCC" -O3 -std=c++17 $ARCH -lineinfo -Xcompiler -fPIC -shared -w -include cfloat \
     -I "$KNN" "$KNN/simple_knn.cu" "$HERE/ref_knn_shim.cu" -o "$OUT/libref_knn.so"

@@ -6,6 +6,7 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <vector>
 
 #include "../../include/gsraster_b200.h"
 #include "common.cuh"
@@ -19,6 +20,27 @@ namespace {
 thread_local std::string g_err;
 thread_local int g_launches = 0;
 thread_local int* g_pinned = nullptr;  // 8 ints of pinned host memory for the num_rendered read-back
+
+// ---- optional per-stage event timing (gsr_set_stage_timing) ----
+struct StageSpan { int stage; cudaEvent_t a, b; };
+thread_local bool g_timing = false;
+thread_local std::vector<StageSpan> g_spans;
+thread_local std::vector<cudaEvent_t> g_free_events;
+cudaEvent_t take_event() {
+  cudaEvent_t e;
+  if (!g_free_events.empty()) { e = g_free_events.back(); g_free_events.pop_back(); return e; }
+  cudaEventCreate(&e);
+  return e;
+}
+struct StageTimer {
+  bool on; int stage; cudaStream_t s; cudaEvent_t a;
+  StageTimer(int stage_, cudaStream_t s_) : on(g_timing), stage(stage_), s(s_), a(nullptr) {
+    if (on) { a = take_event(); cudaEventRecord(a, s); }
+  }
+  ~StageTimer() {
+    if (on) { cudaEvent_t b = take_event(); cudaEventRecord(b, s); g_spans.push_back({stage, a, b}); }
+  }
+};
 
 int fail(int code, const char* fmt, ...) {
   char buf[512];
@@ -133,10 +155,16 @@ int gsr_forward(const gsr_params* p, gsr_alloc_fn geom_alloc, void* geom_ctx, gs
 
   CUDA_TRY(cudaMemsetAsync(g.flags, 0, 8 * sizeof(int), stream));
   const gsr::FwdInputs in = make_inputs(p, means3D, shs, colors_precomp, opacities, scales, rotations, cov3D_precomp);
-  gsr::launch_preprocess(in, cam, g, radii, is_used, stream);
+  {
+    StageTimer tm(0, stream);
+    gsr::launch_preprocess(in, cam, g, radii, is_used, stream);
+  }
   g_launches += 1;
   STAGE_CHECK("preprocess");
-  gsr::launch_depth_sort_and_count(P, g, stream, g_launches);
+  {
+    StageTimer tm(1, stream);
+    gsr::launch_depth_sort_and_count(P, g, stream, g_launches);
+  }
   STAGE_CHECK("depth_sort");
 
   // the one data-dependent host sync of the path (reference: rasterizer_impl.cu:289-290)
@@ -152,9 +180,15 @@ int gsr_forward(const gsr_params* p, gsr_alloc_fn geom_alloc, void* geom_ctx, gs
   if (!bin_chunk) return fail(GSR_ERR_ALLOC, "binning allocator returned NULL");
   gsr::BinState b;
   gsr::bin_from_chunk(bin_chunk, (size_t)R, b);
-  gsr::launch_binning(P, R, cam, g, b, img, stream, g_launches);
+  {
+    StageTimer tm(2, stream);
+    gsr::launch_binning(P, R, cam, g, b, img, stream, g_launches);
+  }
   STAGE_CHECK("binning");
-  gsr::launch_render_forward(p->F, cam, g, b, img, sh_objs, out_depth, out_color, out_objects, stream);
+  {
+    StageTimer tm(3, stream);
+    gsr::launch_render_forward(p->F, cam, g, b, img, sh_objs, out_depth, out_color, out_objects, stream);
+  }
   g_launches += 1;
   STAGE_CHECK("render_forward");
   return GSR_OK;
@@ -191,18 +225,66 @@ int gsr_backward(const gsr_params* p, int num_rendered, const float* background,
   gsr::bin_from_chunk(binning_buffer, (size_t)(num_rendered > 0 ? num_rendered : 0), b);
   if (!radii) radii = g.radii_internal;
 
-  CUDA_TRY(cudaMemsetAsync(g.grad_rows, 0, (size_t)P * gsr::grad_row_floats(p->F) * sizeof(float), stream));
-  if (num_rendered > 0) {
-    gsr::launch_render_backward(p->F, cam, g, b, img, sh_objs, dL_dpix_depth, dL_dpix, dL_dpix_obj, stream);
-    g_launches += 1;
-    STAGE_CHECK("render_backward");
+  {
+    StageTimer tm(4, stream);
+    CUDA_TRY(cudaMemsetAsync(g.grad_rows, 0, (size_t)P * gsr::grad_row_floats(p->F) * sizeof(float), stream));
+    if (num_rendered > 0) {
+      gsr::launch_render_backward(p->F, cam, g, b, img, sh_objs, dL_dpix_depth, dL_dpix, dL_dpix_obj, stream);
+      g_launches += 1;
+    }
   }
+  STAGE_CHECK("render_backward");
   const gsr::FwdInputs in = make_inputs(p, means3D, shs, colors_precomp, nullptr, scales, rotations, cov3D_precomp);
   gsr::BwdOutputs out{dL_dmean2D, dL_dconic, dL_dopacity, dL_ddepths, dL_dcolor, dL_dobjects,
                       dL_dmean3D, dL_dcov3D, dL_dsh,      dL_dscale,  dL_drot};
-  gsr::launch_preprocess_backward(in, cam, g, radii, out, stream);
+  {
+    StageTimer tm(5, stream);
+    gsr::launch_preprocess_backward(in, cam, g, radii, out, stream);
+  }
   g_launches += 1;
   STAGE_CHECK("preprocess_backward");
+  return GSR_OK;
+}
+
+int gsr_set_stage_timing(int enable) {
+  g_timing = enable != 0;
+  return GSR_OK;
+}
+int gsr_get_stage_times(float* ms) {
+  if (!ms) return fail(GSR_ERR_INVALID_ARGUMENT, "ms is NULL");
+  for (const StageSpan& sp : g_spans) {
+    CUDA_TRY(cudaEventSynchronize(sp.b));
+    float t = 0.f;
+    CUDA_TRY(cudaEventElapsedTime(&t, sp.a, sp.b));
+    if (sp.stage >= 0 && sp.stage < GSR_NUM_STAGES) ms[sp.stage] += t;
+    g_free_events.push_back(sp.a);
+    g_free_events.push_back(sp.b);
+  }
+  g_spans.clear();
+  return GSR_OK;
+}
+
+int gsr_count_pairs(const gsr_params* p, int num_rendered, const char* geom_buffer, const char* binning_buffer,
+                    const char* image_buffer, unsigned long long* counts) {
+  if (int rc = check_params(p)) return rc;
+  if (!geom_buffer || !binning_buffer || !image_buffer || !counts)
+    return fail(GSR_ERR_INVALID_ARGUMENT, "NULL argument");
+  cudaStream_t stream = (cudaStream_t)p->stream;
+  const gsr::Cam cam = make_cam(p, nullptr, nullptr, nullptr, nullptr);
+  gsr::GeomState g;
+  gsr::geom_from_chunk(const_cast<char*>(geom_buffer), (size_t)p->P, g, p->F);
+  gsr::ImageState img;
+  gsr::image_from_chunk(const_cast<char*>(image_buffer), (size_t)p->width * p->height, (size_t)cam.gx * cam.gy, img);
+  gsr::BinState b;
+  gsr::bin_from_chunk(const_cast<char*>(binning_buffer), (size_t)(num_rendered > 0 ? num_rendered : 0), b);
+  unsigned long long* d = nullptr;
+  CUDA_TRY(cudaMalloc(&d, 4 * sizeof(unsigned long long)));
+  CUDA_TRY(cudaMemsetAsync(d, 0, 4 * sizeof(unsigned long long), stream));
+  gsr::launch_count_pairs(cam, g, b, img, d, stream);
+  cudaError_t e = cudaMemcpyAsync(counts, d, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+  cudaFree(d);
+  if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "count_pairs: %s", cudaGetErrorString(e));
   return GSR_OK;
 }
 

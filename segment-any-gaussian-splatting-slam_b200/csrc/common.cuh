@@ -145,6 +145,8 @@ void launch_render_forward(int F, const Cam& cam, const GeomState& g, const BinS
 void launch_render_backward(int F, const Cam& cam, const GeomState& g, const BinState& b,
                             const ImageState& img, const float* sh_objs, const float* dL_dpix_depth,
                             const float* dL_dpix, const float* dL_dpix_obj, cudaStream_t s);
+void launch_count_pairs(const Cam& cam, const GeomState& g, const BinState& b, const ImageState& img,
+                        unsigned long long* counts, cudaStream_t s);
 struct BwdOutputs {
   float* dL_dmean2D; float* dL_dconic; float* dL_dopacity; float* dL_ddepths; float* dL_dcolor; float* dL_dobjects;
   float* dL_dmean3D; float* dL_dcov3D; float* dL_dsh; float* dL_dscale; float* dL_drot;

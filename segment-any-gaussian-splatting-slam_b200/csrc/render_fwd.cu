@@ -134,6 +134,58 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   }
 }
 
+// Diagnostic only (gsr_count_pairs): replays the blend tests of a finished forward pass and counts
+// evaluated / blended (pixel, Gaussian) pairs; used by bench.py for the FP32 roofline figures.
+__global__ void __launch_bounds__(256)
+count_pairs_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+                   const float4* __restrict__ rec, int W, int H, unsigned long long* __restrict__ counts) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int px = blockIdx.x * TILE_X + (warp & 1) * 8 + (lane & 7);
+  const int py = blockIdx.y * TILE_Y + (warp >> 1) * 4 + (lane >> 3);
+  const bool inside = px < W && py < H;
+  const float pixx = (float)px, pixy = (float)py;
+  const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
+  float T = 1.0f;
+  bool done = !inside;
+  unsigned long long n_eval = 0, n_blend = 0, n_warp = 0;
+  for (uint32_t i = range.x; i < range.y; i++) {
+    if (__all_sync(0xffffffffu, done)) break;
+    const uint32_t id = point_list[i];
+    const float4 r0 = rec[3 * (size_t)id], r1 = rec[3 * (size_t)id + 1];
+    bool hit = false;
+    if (!done) {
+      n_eval++;
+      const float dx = r0.x - pixx, dy = r0.y - pixy;
+      const float power = -0.5f * (r0.z * dx * dx + r1.x * dy * dy) - r0.w * dx * dy;
+      if (power <= 0.0f) {
+        const float alpha = min(0.99f, r1.y * expf(power));
+        if (alpha >= 1.0f / 255.0f) {
+          const float test_T = T * (1 - alpha);
+          if (test_T < 0.0001f) done = true;
+          else { T = test_T; hit = true; n_blend++; }
+        }
+      }
+    }
+    if (__any_sync(0xffffffffu, hit) && lane == 0) n_warp++;
+  }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) {
+    n_eval += __shfl_xor_sync(0xffffffffu, n_eval, o);
+    n_blend += __shfl_xor_sync(0xffffffffu, n_blend, o);
+  }
+  if (lane == 0) {
+    atomicAdd(&counts[0], n_eval);
+    atomicAdd(&counts[1], n_blend);
+    atomicAdd(&counts[2], n_warp);
+    if (warp == 0) atomicAdd(&counts[3], (unsigned long long)(range.y - range.x));
+  }
+}
+void launch_count_pairs(const Cam& cam, const GeomState& g, const BinState& b, const ImageState& img,
+                        unsigned long long* counts, cudaStream_t s) {
+  dim3 grid(cam.gx, cam.gy), block(256);
+  count_pairs_kernel<<<grid, block, 0, s>>>(img.ranges, b.point_list, g.rec, cam.W, cam.H, counts);
+}
+
 void launch_render_forward(int F, const Cam& cam, const GeomState& g, const BinState& b,
                            ImageState& img, const float* sh_objs, float* out_depth, float* out_color,
                            float* out_objects, cudaStream_t s) {

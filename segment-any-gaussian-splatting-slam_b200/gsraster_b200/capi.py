@@ -44,6 +44,9 @@ def lib():
         L.gsr_mark_visible.argtypes = [C.c_int] + [C.c_void_p] * 5
         L.gsr_knn.argtypes = [C.c_int] + [C.c_void_p] * 4
         L.gsr_export_state.argtypes = [C.POINTER(Params), C.c_int] + [C.c_void_p] * 14
+        L.gsr_count_pairs.argtypes = [C.POINTER(Params), C.c_int] + [C.c_void_p] * 3 + [C.POINTER(C.c_ulonglong)]
+        L.gsr_get_stage_times.argtypes = [C.POINTER(C.c_float)]
+        L.gsr_set_stage_timing.argtypes = [C.c_int]
         _lib = L
     return _lib
 
@@ -92,6 +95,8 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
     """-> (num_rendered, depth, color, objects, radii, is_used, geomBuffer, binningBuffer, imgBuffer)."""
     if means3D.dim() != 2 or means3D.size(1) != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    if not means3D.is_cuda:
+        raise RuntimeError("gsraster_b200: expected CUDA tensors (there is no CPU fallback)")
     dev = means3D.device
     P, H, W = means3D.size(0), int(image_height), int(image_width)
     if sh_objs is None or sh_objs.numel() == 0:
@@ -124,8 +129,11 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier,
                                  cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_depth,
                                  dL_dout_color, sh, dL_dout_objects, sh_objs, degree, campos, geomBuffer, R,
-                                 binningBuffer, imageBuffer, debug):
-    """-> (dL_dmeans2D, dL_dcolors, dL_dobjects, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
+                                 binningBuffer, imageBuffer, debug, out=None):
+    """`out` (extension): dict of preallocated contiguous fp32 tensors keyed like the local `g` below
+    (e.g. views into one flat all-reduce bucket, see mapping.GradBucket) that the kernels write
+    directly; missing keys are allocated here.
+    -> (dL_dmeans2D, dL_dcolors, dL_dobjects, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
     dL_drotations), exactly the reference's 9-tuple (rasterize_points.cu:215)."""
     dev = means3D.device
     P = means3D.size(0)
@@ -137,6 +145,11 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
              colors=torch.empty((P, 3), **o), objects=torch.empty((P, F), **o), conic=torch.empty((P, 6), **o),
              opacity=torch.empty((P, 1), **o), cov3D=torch.empty((P, 6), **o), sh=torch.empty((P, M, 3), **o),
              scales=torch.empty((P, 3), **o), rotations=torch.empty((P, 4), **o))
+    if out:
+        for k, t in out.items():
+            if t.numel() != g[k].numel() or t.dtype != torch.float32 or not t.is_contiguous() or not t.is_cuda:
+                raise RuntimeError(f"out[{k!r}] must be a contiguous CUDA float32 tensor of {g[k].numel()} elements")
+            g[k] = t.view(g[k].shape)
     if P != 0:
         prm = Params(P, int(degree), int(M), int(F), W, H, float(tan_fovx), float(tan_fovy), float(scale_modifier),
                      0, int(bool(debug)), _stream_ptr())
@@ -201,6 +214,29 @@ def export_state(P, D, M, F, W, H, R, geomBuffer, binningBuffer, imageBuffer):
     st["point_list"] = st["point_list"][:R]
     st["sorted_keys"] = st["sorted_keys"][:R]
     return st
+
+
+STAGES = ("preprocess", "depth_sort_count", "emit_tile_sort_ranges", "render_fwd", "render_bwd", "preprocess_bwd")
+
+
+def set_stage_timing(enable):
+    _check(lib().gsr_set_stage_timing(int(bool(enable))))
+
+
+def get_stage_times():
+    """Milliseconds per stage accumulated since the previous call (synchronises)."""
+    ms = (C.c_float * len(STAGES))()
+    _check(lib().gsr_get_stage_times(ms))
+    return dict(zip(STAGES, [float(v) for v in ms]))
+
+
+def count_pairs(P, D, M, F, W, H, R, geomBuffer, binningBuffer, imageBuffer):
+    """-> dict(evaluated, blended, warp_blended, instances) of a finished forward pass."""
+    prm = Params(P, D, M, F, W, H, 1.0, 1.0, 1.0, 0, 0, _stream_ptr())
+    c = (C.c_ulonglong * 4)()
+    with torch.cuda.device(geomBuffer.device):
+        _check(lib().gsr_count_pairs(C.byref(prm), int(R), _ptr(geomBuffer), _ptr(binningBuffer), _ptr(imageBuffer), c))
+    return dict(evaluated=int(c[0]), blended=int(c[1]), warp_blended=int(c[2]), instances=int(c[3]))
 
 
 def last_launch_count():

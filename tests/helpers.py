@@ -71,13 +71,13 @@ class _RefAlloc:
         return self.t.data_ptr()
 
 
-_ref = None
+_refs = {}
 
 
-def ref_lib():
-    global _ref
+def ref_lib(F=16):
+    _ref = _refs.get(F)
     if _ref is None:
-        _ref = C.CDLL(REF_LIB)
+        _ref = _refs[F] = C.CDLL(REF_LIB if F == 16 else REF_LIB.replace(".so", "_f%d.so" % F))
         _ref.ref_forward.argtypes = [ALLOC_FN, C.c_void_p] * 3 + [C.c_int] * 3 + [C.c_void_p, C.c_int, C.c_int] + \
             [C.c_void_p] * 6 + [C.c_float] + [C.c_void_p] * 5 + [C.c_float, C.c_float, C.c_int] + [C.c_void_p] * 5 + [C.c_int]
         _ref.ref_backward.argtypes = [C.c_int] * 4 + [C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 5 + [C.c_float] + \
@@ -88,8 +88,8 @@ def ref_lib():
     return _ref
 
 
-def have_ref():
-    return os.path.exists(REF_LIB)
+def have_ref(F=16):
+    return os.path.exists(REF_LIB if F == 16 else REF_LIB.replace(".so", "_f%d.so" % F))
 
 
 def _view(base_tensor, addr, count, dtype):
@@ -103,10 +103,10 @@ def _view(base_tensor, addr, count, dtype):
 def run_ref(scene, cam, grads=None, colors_precomp=None, cov3D_precomp=None):
     """Unmodified reference CUDA rasterizer (built by oracle/build_ref.sh) through oracle/ref_shim.cu."""
     import torch
-    L = ref_lib()
+    F = scene.sh_objs.shape[-1]
+    L = ref_lib(F)
     d = to_torch(scene, cam)
     P, W, H = scene.P, cam.W, cam.H
-    F = scene.sh_objs.shape[-1]
     assert F == L.ref_num_objects(), "reference build has NUM_OBJECTS=%d" % L.ref_num_objects()
     p = lambda t: None if t is None else t.data_ptr()
     sh = d["shs"] if colors_precomp is None else None
