@@ -84,6 +84,10 @@ def main(outdir):
             a = h.npy(ref[k]).copy()
             if k in ("depths", "means2D", "conic_opacity", "rgb", "clamped"):
                 a[~vis] = 0  # the reference leaves culled entries uninitialised (forward.cu:211, 237, 252)
+            if colors is not None and k == "clamped":
+                a[:] = 0     # ... and never writes `clamped` / `rgb` when colours are precomputed
+            if colors is not None and k == "rgb":
+                a = colors * vis[:, None]  # (forward.cu:259-265); the blend reads colors_precomp instead
             d["ref_" + k] = a
         d["ref_R"] = np.array([ref["R"]], np.int64)
         np.savez_compressed(os.path.join(outdir, name + ".npz"), **d)

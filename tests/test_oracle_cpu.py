@@ -32,6 +32,8 @@ def test_oracle_vs_golden(name):
     assert (orc["tiles_touched"] != ref["tiles_touched"]).sum() <= max(1, P // 500)
     vis = (ref["radii"] > 0) & (orc["radii"] > 0)
     for k, tol in (("depths", 1e-5), ("means2D", 2e-3), ("rgb", 1e-5)):
+        if k == "rgb" and colors is not None:
+            continue  # neither the reference nor the oracle fills geomState.rgb for precomputed colours
         assert np.abs(orc[k][vis] - ref[k][vis]).max() <= tol, k
     co, cr = orc["conic_opacity"][vis], ref["conic_opacity"][vis]
     assert (np.abs(co - cr) / (np.abs(cr) + 1e-3)).max() < 2e-3
