@@ -146,36 +146,217 @@ void radix_pass(const uint64_t* in, uint64_t* out, int64_t n, int shift, int bit
   launches += 3;
 }
 
-// ---- tiles_touched in depth order: block sums, scan of block sums -----------------------------
-__global__ void __launch_bounds__(EMIT_THREADS)
-count_kernel(int P, const uint64_t* __restrict__ dkeys, const uint32_t* __restrict__ tiles_touched,
-             uint32_t* __restrict__ block_sums) {
-  __shared__ uint32_t ws[EMIT_THREADS / 32];
-  int i = blockIdx.x * EMIT_THREADS + threadIdx.x;
-  uint32_t v = 0;
-  if (i < P) v = tiles_touched[(uint32_t)dkeys[i]];
-#pragma unroll
-  for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = v;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    uint32_t t = 0;
-    for (int w = 0; w < EMIT_THREADS / 32; w++) t += ws[w];
-    block_sums[blockIdx.x] = t;
+// =================================================================================================
+// Tile binning without an instance sort.
+//
+// The reference duplicates every Gaussian into one (tile|depth, idx) pair per covered tile and
+// radix-sorts the R pairs (rasterizer_impl.cu:70-111, 286-327). With the Gaussians already in
+// depth order the per-tile lists can be PULLED instead: a tile's list is the depth-ordered
+// sub-sequence of Gaussians whose rect covers it, so an order-preserving filter per tile yields
+// exactly the reference's sorted order (tile, depth bits, index) without moving 12-byte pairs
+// through several scatter passes.
+//   1. preprocess splats the four corners of every rect into a (gy+1)x(gx+1) difference grid
+//      (and of the supertile rect into a coarse one): a 2-D prefix sum gives the list length of
+//      every tile -> offsets, ranges, R (offsets_kernel, one block).
+//   2. supertile lists (S x S tiles): order-preserving filter of the depth-ordered sequence into
+//      NS lists of {rect, idx}; warp granularity: ballot ranks inside a warp, a scan over
+//      per-(supertile, warp) counters between warps (l1_count / l1_scan / l1_write).
+//   3. tile pull: one warp per tile walks its supertile's list (staged through shared memory by
+//      the block's 8 tile-warps) and appends matching indices at its running offset
+//      (tile_pull_kernel). Sequential per tile, so stable by construction; no atomics.
+// =================================================================================================
+
+// Coverage difference grids: +1/-1 at the four corners of every visible Gaussian's tile rect (and
+// of its supertile rect). Privatised in shared memory per block (a few hundred blocks grid-stride
+// over the Gaussians), non-zero entries flushed with global atomics: integer adds, so exact and
+// order-independent. use_smem == 0 (grids above the shared-memory budget): direct global atomics.
+__global__ void __launch_bounds__(256)
+coverage_kernel(int P, int gx, int gy, SuperGrid sg, int use_smem, const uint32_t* __restrict__ tiles_touched,
+                const uint32_t* __restrict__ rect, int* __restrict__ sat, int* __restrict__ ssat) {
+  extern __shared__ int cov_s[];
+  const int n1 = (gx + 1) * (gy + 1), n2 = (sg.sgx + 1) * (sg.sgy + 1);
+  int* a = use_smem ? cov_s : sat;
+  int* b = use_smem ? cov_s + n1 : ssat;
+  if (use_smem) {
+    for (int i = threadIdx.x; i < n1 + n2; i += blockDim.x) cov_s[i] = 0;
+    __syncthreads();
+  }
+  const int w = gx + 1, sw = sg.sgx + 1, sh = sg.S == 8 ? 3 : 4;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < P; i += gridDim.x * blockDim.x) {
+    if (tiles_touched[i] == 0) continue;
+    const uint32_t rc = rect[i];
+    const int x0 = rc & 255u, y0 = (rc >> 8) & 255u, x1 = (rc >> 16) & 255u, y1 = rc >> 24;
+    atomicAdd(&a[y0 * w + x0], 1);
+    atomicAdd(&a[y0 * w + x1], -1);
+    atomicAdd(&a[y1 * w + x0], -1);
+    atomicAdd(&a[y1 * w + x1], 1);
+    const int sx0 = x0 >> sh, sy0 = y0 >> sh, sx1 = ((x1 - 1) >> sh) + 1, sy1 = ((y1 - 1) >> sh) + 1;
+    atomicAdd(&b[sy0 * sw + sx0], 1);
+    atomicAdd(&b[sy0 * sw + sx1], -1);
+    atomicAdd(&b[sy1 * sw + sx0], -1);
+    atomicAdd(&b[sy1 * sw + sx1], 1);
+  }
+  if (use_smem) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < n1 + n2; i += blockDim.x) {  // sat and ssat are contiguous in global memory too
+      const int v = cov_s[i];
+      if (v) atomicAdd(&sat[i], v);
+    }
   }
 }
 
-// single block: exclusive scan of block_sums[0..n), total -> flags[0]
-__global__ void __launch_bounds__(1024) scan_block_sums_kernel(uint32_t* __restrict__ block_sums, int n,
-                                                              int* __restrict__ flags) {
-  __shared__ uint32_t warp_sums[32];
+// single block: 2-D prefix sums of the coverage grids, then exclusive scans -> offsets
+__global__ void __launch_bounds__(1024)
+offsets_kernel(int gx, int gy, SuperGrid sg, int* __restrict__ sat, int* __restrict__ ssat, uint2* __restrict__ ranges,
+               uint32_t* __restrict__ tile_off, uint32_t* __restrict__ l1_off, int* __restrict__ flags) {
+  __shared__ unsigned long long warp_sums[32];
+  __shared__ unsigned long long carry_s;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  // row-wise then column-wise inclusive prefix (grids are small: <= 257 x 257)
+  for (int pass = 0; pass < 2; pass++) {
+    int* g = pass == 0 ? sat : ssat;
+    const int w = (pass == 0 ? gx : sg.sgx) + 1, h = (pass == 0 ? gy : sg.sgy) + 1;
+    for (int y = tid; y < h; y += blockDim.x) {
+      int run = 0;
+      for (int x = 0; x < w; x++) { run += g[y * w + x]; g[y * w + x] = run; }
+    }
+    __syncthreads();
+    for (int x = tid; x < w; x += blockDim.x) {
+      int run = 0;
+      for (int y = 0; y < h; y++) { run += g[y * w + x]; g[y * w + x] = run; }
+    }
+    __syncthreads();
+  }
+  // exclusive scans in tile-id / supertile-id order
+  for (int pass = 0; pass < 2; pass++) {
+    const int* g = pass == 0 ? sat : ssat;
+    const int w = (pass == 0 ? gx : sg.sgx), h = (pass == 0 ? gy : sg.sgy), n = w * h;
+    if (tid == 0) carry_s = 0;
+    __syncthreads();
+    for (int base = 0; base < n; base += 1024) {
+      const int i = base + tid;
+      unsigned long long v = 0;
+      if (i < n) v = (unsigned long long)(uint32_t)g[(i / w) * (w + 1) + (i % w)];
+      unsigned long long incl = v;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        unsigned long long t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+      }
+      if (lane == 31) warp_sums[warp] = incl;
+      __syncthreads();
+      unsigned long long woff = 0;
+      for (int k = 0; k < warp; k++) woff += warp_sums[k];
+      const unsigned long long carry = carry_s;
+      const unsigned long long excl = carry + woff + incl - v;
+      if (i < n) {
+        if (pass == 0) {
+          tile_off[i] = (uint32_t)excl;
+          ranges[i] = v ? make_uint2((uint32_t)excl, (uint32_t)(excl + v)) : make_uint2(0u, 0u);
+        } else {
+          l1_off[i] = (uint32_t)excl;
+        }
+      }
+      __syncthreads();
+      if (tid == 1023) carry_s = carry + woff + incl;
+      __syncthreads();
+    }
+    if (tid == 0) {
+      const unsigned long long total = carry_s;
+      if (pass == 0) {
+        flags[0] = total > 0x7fffffffull ? -1 : (int)total;  // num_rendered must fit an int (reference: :289)
+      } else {
+        l1_off[n] = (uint32_t)total;
+        flags[2] = (int)(uint32_t)total;
+        flags[3] = (int)(uint32_t)(total >> 32);
+      }
+    }
+    __syncthreads();
+  }
+}
+
+void launch_depth_sort_and_offsets(int P, const Cam& cam, GeomState& g, ImageState& img, cudaStream_t s,
+                                   int& launches) {
+  // 4 stable 8-bit passes over the depth bits (item bits 32..63); a -> b -> a -> b -> a
+  uint64_t* a = g.dkeys_a;
+  uint64_t* b = g.dkeys_b;
+  for (int pass = 0; pass < 4; pass++) {
+    radix_pass(a, b, P, 32 + 8 * pass, 8, g.block_hist, g.digit_total, s, launches);
+    uint64_t* t = a; a = b; b = t;
+  }
+  const SuperGrid sg = super_grid(cam.gx, cam.gy);
+  {
+    const size_t smem = sat_ints(cam.gx, cam.gy) * sizeof(int);
+    const int use_smem = smem <= 160 * 1024;
+    static bool attr_set = false;  // idempotent; a benign race at worst sets it twice
+    if (!attr_set) {
+      cudaFuncSetAttribute(coverage_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+      attr_set = true;
+    }
+    int nb = (P + 255) / 256;
+    if (use_smem && nb > 296) nb = 296;
+    coverage_kernel<<<nb, 256, use_smem ? smem : 0, s>>>(P, cam.gx, cam.gy, sg, use_smem, g.tiles_touched, g.rect,
+                                                         img.sat, img.ssat);
+  }
+  launches += 1;
+  offsets_kernel<<<1, 1024, 0, s>>>(cam.gx, cam.gy, sg, img.sat, img.ssat, img.ranges, img.tile_off, img.l1_off,
+                                   g.flags);
+  launches += 1;
+}
+
+// rect (x0 | y0<<8 | x1<<16 | y1<<24, x1/y1 exclusive) -> supertile rect, same packing
+__device__ __forceinline__ uint32_t super_rect(uint32_t rc, int shift) {
+  const uint32_t x0 = rc & 255u, y0 = (rc >> 8) & 255u, x1 = (rc >> 16) & 255u, y1 = rc >> 24;
+  return (x0 >> shift) | ((y0 >> shift) << 8) | ((((x1 - 1) >> shift) + 1) << 16) | ((((y1 - 1) >> shift) + 1) << 24);
+}
+// is point (x, y) (packed x | y<<8 | x<<16 | y<<24) inside rect? bytes 0,1: lo <= p ; bytes 2,3: !(hi <= p)
+__device__ __forceinline__ bool rect_has(uint32_t rc, uint32_t pxy) { return __vcmpleu4(rc, pxy) == 0x0000FFFFu; }
+
+// WRITE = false: per-(supertile, warp) counts; WRITE = true: ranked writes of {rect, idx}
+template <bool WRITE>
+__global__ void __launch_bounds__(256)
+l1_kernel(int P, SuperGrid sg, int shift, const uint64_t* __restrict__ dkeys, const uint32_t* __restrict__ tiles_touched,
+          const uint32_t* __restrict__ rect, uint32_t* __restrict__ warp_cnt, int NW, uint2* __restrict__ l1) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31, w = k >> 5;
+  uint32_t idx = 0, rc = 0, src = 0;
+  bool vis = false;
+  if (k < P) {
+    idx = (uint32_t)dkeys[k];
+    vis = tiles_touched[idx] != 0;
+    if (vis) { rc = rect[idx]; src = super_rect(rc, shift); }
+  }
+  if (!__any_sync(0xffffffffu, vis)) {
+    if (!WRITE && w < NW) for (int s = lane; s < sg.NS; s += 32) warp_cnt[(size_t)s * NW + w] = 0;
+    return;
+  }
+  for (int sy = 0; sy < sg.sgy; sy++) {
+    for (int sx = 0; sx < sg.sgx; sx++) {
+      const uint32_t pxy = (uint32_t)sx | ((uint32_t)sy << 8);
+      const bool in = vis && rect_has(src, pxy | (pxy << 16));
+      const unsigned m = __ballot_sync(0xffffffffu, in);
+      const int s = sy * sg.sgx + sx;
+      if (!WRITE) {
+        if (lane == 0) warp_cnt[(size_t)s * NW + w] = __popc(m);
+      } else if (in) {
+        l1[warp_cnt[(size_t)s * NW + w] + __popc(m & ((1u << lane) - 1))] = make_uint2(rc, idx);
+      }
+    }
+  }
+}
+
+// one block per supertile: exclusive scan of its row of warp counters, offset by the list base
+__global__ void __launch_bounds__(256)
+l1_scan_kernel(uint32_t* __restrict__ warp_cnt, int NW, const uint32_t* __restrict__ l1_off) {
+  __shared__ uint32_t warp_sums[8];
   __shared__ uint32_t carry_s;
+  uint32_t* row = warp_cnt + (size_t)blockIdx.x * NW;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (threadIdx.x == 0) carry_s = 0;
+  if (threadIdx.x == 0) carry_s = l1_off[blockIdx.x];
   __syncthreads();
-  for (int base = 0; base < n; base += 1024) {
-    int i = base + threadIdx.x;
-    uint32_t v = i < n ? block_sums[i] : 0;
+  for (int base = 0; base < NW; base += 256) {
+    const int i = base + threadIdx.x;
+    const uint32_t v = i < NW ? row[i] : 0;
     uint32_t incl = v;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -185,110 +366,74 @@ __global__ void __launch_bounds__(1024) scan_block_sums_kernel(uint32_t* __restr
     if (lane == 31) warp_sums[warp] = incl;
     __syncthreads();
     uint32_t woff = 0;
-    for (int w = 0; w < warp; w++) woff += warp_sums[w];
-    uint32_t carry = carry_s;
-    if (i < n) block_sums[i] = carry + woff + incl - v;
+    for (int k = 0; k < warp; k++) woff += warp_sums[k];
+    const uint32_t carry = carry_s;
+    if (i < NW) row[i] = carry + woff + incl - v;
     __syncthreads();
-    if (threadIdx.x == 1023) carry_s = carry + woff + incl;
+    if (threadIdx.x == 255) carry_s = carry + woff + incl;
     __syncthreads();
   }
-  if (threadIdx.x == 0) flags[0] = (int)carry_s;
 }
 
-void launch_depth_sort_and_count(int P, GeomState& g, cudaStream_t s, int& launches) {
-  // 4 stable 8-bit passes over the depth bits (item bits 32..63); a -> b -> a -> b -> a
-  uint64_t* a = g.dkeys_a;
-  uint64_t* b = g.dkeys_b;
-  for (int pass = 0; pass < 4; pass++) {
-    radix_pass(a, b, P, 32 + 8 * pass, 8, g.block_hist, g.digit_total, s, launches);
-    uint64_t* t = a; a = b; b = t;
-  }
-  const int nb = emit_blocks(P);
-  count_kernel<<<nb, EMIT_THREADS, 0, s>>>(P, g.dkeys_a, g.tiles_touched, g.block_sums);
-  scan_block_sums_kernel<<<1, 1024, 0, s>>>(g.block_sums, nb, g.flags);
-  launches += 2;
-}
-
-// ---- emission (replaces duplicateWithKeys): warp-cooperative, coalesced 8-byte stores ----------
-__global__ void __launch_bounds__(EMIT_THREADS)
-emit_kernel(int P, int gx, const uint64_t* __restrict__ dkeys, const uint32_t* __restrict__ tiles_touched,
-            const uint32_t* __restrict__ rect, const uint32_t* __restrict__ block_sums, uint64_t* __restrict__ items) {
-  __shared__ uint32_t ws[EMIT_THREADS / 32];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  int i = blockIdx.x * EMIT_THREADS + threadIdx.x;
-  uint32_t idx = 0, tt = 0, rc = 0;
-  if (i < P) {
-    idx = (uint32_t)dkeys[i];
-    tt = tiles_touched[idx];
-    if (tt) rc = rect[idx];
-  }
-  uint32_t incl = tt;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-    if (lane >= o) incl += t;
-  }
-  if (lane == 31) ws[warp] = incl;
-  __syncthreads();
-  uint32_t off = block_sums[blockIdx.x] + incl - tt;
-  for (int w = 0; w < warp; w++) off += ws[w];
-
-  unsigned todo = __ballot_sync(0xffffffffu, tt > 0);
-  while (todo) {
-    int src = __ffs(todo) - 1;
-    todo &= todo - 1;
-    uint32_t s_idx = __shfl_sync(0xffffffffu, idx, src);
-    uint32_t s_tt = __shfl_sync(0xffffffffu, tt, src);
-    uint32_t s_rc = __shfl_sync(0xffffffffu, rc, src);
-    uint32_t s_off = __shfl_sync(0xffffffffu, off, src);
-    const uint32_t x0 = s_rc & 255u, y0 = (s_rc >> 8) & 255u, x1 = (s_rc >> 16) & 255u;
-    const uint32_t w = x1 - x0;
-    for (uint32_t k = lane; k < s_tt; k += 32) {
-      uint32_t y = y0 + k / w, x = x0 + k % w;  // row-major inside the rect, like the reference
-      items[s_off + k] = ((uint64_t)(y * gx + x) << 32) | s_idx;
-    }
-  }
-}
-
-// ---- tile ranges + compact point list (replaces memset + identifyTileRanges) --------------------
+// 8 warps = 8 tiles of one supertile; the supertile's list is staged through shared memory in
+// chunks of PULL_CHUNK entries and every warp filters it for its own tile.
+constexpr int PULL_CHUNK = 1024;
 __global__ void __launch_bounds__(256)
-ranges_kernel(int64_t R, const uint64_t* __restrict__ items, uint32_t* __restrict__ point_list,
-              uint2* __restrict__ ranges) {
-  int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
-  if (i >= R) return;
-  uint64_t it = items[i];
-  uint32_t cur = (uint32_t)(it >> 32);
-  point_list[i] = (uint32_t)it;
-  if (i == 0) ranges[cur].x = 0;
-  else {
-    uint32_t prev = (uint32_t)(items[i - 1] >> 32);
-    if (cur != prev) {
-      ranges[prev].y = (uint32_t)i;
-      ranges[cur].x = (uint32_t)i;
+tile_pull_kernel(int gx, int gy, SuperGrid sg, const uint2* __restrict__ l1, const uint32_t* __restrict__ l1_off,
+                 const uint32_t* __restrict__ tile_off, uint32_t* __restrict__ point_list) {
+  __shared__ uint2 buf[2][PULL_CHUNK];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int per_super = sg.S * sg.S / 8;
+  const int s = blockIdx.x / per_super, sub = blockIdx.x % per_super;
+  const int tl = sub * 8 + warp;
+  const int tx = (s % sg.sgx) * sg.S + tl % sg.S, ty = (s / sg.sgx) * sg.S + tl / sg.S;
+  const bool live = tx < gx && ty < gy;
+  const uint32_t pxy1 = (uint32_t)tx | ((uint32_t)ty << 8), pxy = pxy1 | (pxy1 << 16);
+  uint32_t off = live ? tile_off[ty * gx + tx] : 0;
+  const uint32_t beg = l1_off[s], end = l1_off[s + 1];
+  const int n = (int)(end - beg);
+  const int nchunk = (n + PULL_CHUNK - 1) / PULL_CHUNK;
+  uint2 pre[PULL_CHUNK / 256];
+  auto fetch = [&](int c) {
+#pragma unroll
+    for (int q = 0; q < PULL_CHUNK / 256; q++) {
+      const int i = c * PULL_CHUNK + q * 256 + tid;
+      pre[q] = i < n ? l1[beg + i] : make_uint2(0u, 0u);  // rect 0 matches no tile (x1 = 0)
+    }
+  };
+  if (nchunk > 0) fetch(0);
+  for (int c = 0; c < nchunk; c++) {
+    const int st = c & 1;
+#pragma unroll
+    for (int q = 0; q < PULL_CHUNK / 256; q++) buf[st][q * 256 + tid] = pre[q];
+    __syncthreads();  // also orders reuse of buf[st] (read two iterations ago) against this write
+    if (c + 1 < nchunk) fetch(c + 1);
+    if (live) {
+      const int cnt = min(PULL_CHUNK, n - c * PULL_CHUNK);
+      for (int base = 0; base < cnt; base += 32) {  // warp-uniform trip count
+        const int i = base + lane;
+        const uint2 e = i < cnt ? buf[st][i] : make_uint2(0u, 0u);
+        const bool in = rect_has(e.x, pxy);
+        const unsigned m = __ballot_sync(0xffffffffu, in);
+        if (in) point_list[off + __popc(m & ((1u << lane) - 1))] = e.y;
+        off += __popc(m);
+      }
     }
   }
-  if (i == R - 1) ranges[cur].y = (uint32_t)R;
 }
 
 void launch_binning(int P, int64_t R, const Cam& cam, GeomState& g, BinState& b, ImageState& img, cudaStream_t s,
                     int& launches) {
-  const int T = cam.gx * cam.gy;
-  cudaMemsetAsync(img.ranges, 0, (size_t)T * sizeof(uint2), s);
   if (R <= 0) return;
-  emit_kernel<<<emit_blocks(P), EMIT_THREADS, 0, s>>>(P, cam.gx, g.dkeys_a, g.tiles_touched, g.rect, g.block_sums,
-                                                     b.items_a);
-  launches += 1;
-  int tile_bits = 1;
-  while ((1 << tile_bits) < T) tile_bits++;
-  uint64_t* a = b.items_a;
-  uint64_t* o = b.items_b;
-  for (int done = 0; done < tile_bits; done += 8) {
-    int bits = tile_bits - done < 8 ? tile_bits - done : 8;
-    radix_pass(a, o, R, 32 + done, bits, b.block_hist, b.digit_total, s, launches);
-    uint64_t* t = a; a = o; o = t;
-  }
-  ranges_kernel<<<(int)((R + 255) / 256), 256, 0, s>>>(R, a, b.point_list, img.ranges);
-  launches += 1;
+  const SuperGrid sg = super_grid(cam.gx, cam.gy);
+  const int shift = sg.S == 8 ? 3 : 4;
+  const int NW = (P + 31) / 32, nb = (P + 255) / 256;
+  l1_kernel<false><<<nb, 256, 0, s>>>(P, sg, shift, g.dkeys_a, g.tiles_touched, g.rect, b.warp_cnt, NW, b.l1);
+  l1_scan_kernel<<<sg.NS, 256, 0, s>>>(b.warp_cnt, NW, img.l1_off);
+  l1_kernel<true><<<nb, 256, 0, s>>>(P, sg, shift, g.dkeys_a, g.tiles_touched, g.rect, b.warp_cnt, NW, b.l1);
+  tile_pull_kernel<<<sg.NS * (sg.S * sg.S / 8), 256, 0, s>>>(cam.gx, cam.gy, sg, b.l1, img.l1_off, img.tile_off,
+                                                           b.point_list);
+  launches += 4;
 }
 
 // ---- parity export ------------------------------------------------------------------------------

@@ -108,12 +108,11 @@ size_t gsr_geom_bytes(int P) {
 }
 size_t gsr_image_bytes(int width, int height) {
   gsr::ImageState s;
-  size_t T = (size_t)((width + 15) / 16) * ((height + 15) / 16);
-  return gsr::image_from_chunk(nullptr, (size_t)width * height, T, s);
+  return gsr::image_from_chunk(nullptr, width, height, s);
 }
 size_t gsr_binning_bytes(int64_t R) {
   gsr::BinState b;
-  return gsr::bin_from_chunk(nullptr, (size_t)(R > 0 ? R : 1), b);
+  return gsr::bin_from_chunk(nullptr, (size_t)(R > 0 ? R : 1), 0, 0, b);
 }
 
 int gsr_forward(const gsr_params* p, gsr_alloc_fn geom_alloc, void* geom_ctx, gsr_alloc_fn binning_alloc,
@@ -150,36 +149,40 @@ int gsr_forward(const gsr_params* p, gsr_alloc_fn geom_alloc, void* geom_ctx, gs
   gsr::ImageState img;
   char* img_chunk = image_alloc(image_ctx, gsr_image_bytes(p->width, p->height));
   if (!img_chunk) return fail(GSR_ERR_ALLOC, "image allocator returned NULL");
-  gsr::image_from_chunk(img_chunk, (size_t)p->width * p->height, (size_t)T, img);
+  gsr::image_from_chunk(img_chunk, p->width, p->height, img);
   if (!radii) radii = g.radii_internal;
 
   CUDA_TRY(cudaMemsetAsync(g.flags, 0, 8 * sizeof(int), stream));
+  CUDA_TRY(cudaMemsetAsync(img.sat, 0, gsr::sat_ints(cam.gx, cam.gy) * sizeof(int), stream));
   const gsr::FwdInputs in = make_inputs(p, means3D, shs, colors_precomp, opacities, scales, rotations, cov3D_precomp);
   {
     StageTimer tm(0, stream);
-    gsr::launch_preprocess(in, cam, g, radii, is_used, stream);
+    gsr::launch_preprocess(in, cam, g, img, radii, is_used, stream);
   }
   g_launches += 1;
   STAGE_CHECK("preprocess");
   {
     StageTimer tm(1, stream);
-    gsr::launch_depth_sort_and_count(P, g, stream, g_launches);
+    gsr::launch_depth_sort_and_offsets(P, cam, g, img, stream, g_launches);
   }
   STAGE_CHECK("depth_sort");
 
   // the one data-dependent host sync of the path (reference: rasterizer_impl.cu:289-290)
   if (!g_pinned) CUDA_TRY(cudaHostAlloc(&g_pinned, 8 * sizeof(int), cudaHostAllocDefault));
-  CUDA_TRY(cudaMemcpyAsync(g_pinned, g.flags, 2 * sizeof(int), cudaMemcpyDeviceToHost, stream));
+  CUDA_TRY(cudaMemcpyAsync(g_pinned, g.flags, 4 * sizeof(int), cudaMemcpyDeviceToHost, stream));
   CUDA_TRY(cudaStreamSynchronize(stream));
   const int64_t R = (int64_t)(uint32_t)g_pinned[0];
+  const uint64_t l1_total = (uint64_t)(uint32_t)g_pinned[2] | ((uint64_t)(uint32_t)g_pinned[3] << 32);
   if (g_pinned[1]) return fail(GSR_ERR_INVALID_ARGUMENT, "Point is filtered although prefiltered is set");
   if (R > 0x7fffffffLL) return fail(GSR_ERR_UNSUPPORTED, "num_rendered exceeds int32");
+  if (l1_total > 0xffffffffull) return fail(GSR_ERR_UNSUPPORTED, "supertile list length exceeds uint32");
   if (num_rendered) *num_rendered = (int)R;
 
-  char* bin_chunk = binning_alloc(binning_ctx, gsr_binning_bytes(R));
-  if (!bin_chunk) return fail(GSR_ERR_ALLOC, "binning allocator returned NULL");
+  const size_t nw_ns = (size_t)((P + 31) / 32) * gsr::super_grid(cam.gx, cam.gy).NS;
   gsr::BinState b;
-  gsr::bin_from_chunk(bin_chunk, (size_t)R, b);
+  char* bin_chunk = binning_alloc(binning_ctx, gsr::bin_from_chunk(nullptr, (size_t)R, (size_t)l1_total, nw_ns, b));
+  if (!bin_chunk) return fail(GSR_ERR_ALLOC, "binning allocator returned NULL");
+  gsr::bin_from_chunk(bin_chunk, (size_t)R, (size_t)l1_total, nw_ns, b);
   {
     StageTimer tm(2, stream);
     gsr::launch_binning(P, R, cam, g, b, img, stream, g_launches);
@@ -220,9 +223,9 @@ int gsr_backward(const gsr_params* p, int num_rendered, const float* background,
   gsr::GeomState g;
   gsr::geom_from_chunk(geom_buffer, (size_t)P, g, p->F);
   gsr::ImageState img;
-  gsr::image_from_chunk(image_buffer, (size_t)p->width * p->height, (size_t)T, img);
+  gsr::image_from_chunk(image_buffer, p->width, p->height, img);
   gsr::BinState b;
-  gsr::bin_from_chunk(binning_buffer, (size_t)(num_rendered > 0 ? num_rendered : 0), b);
+  gsr::bin_from_chunk(binning_buffer, (size_t)(num_rendered > 0 ? num_rendered : 0), 0, 0, b);
   if (!radii) radii = g.radii_internal;
 
   {
@@ -274,9 +277,9 @@ int gsr_count_pairs(const gsr_params* p, int num_rendered, const char* geom_buff
   gsr::GeomState g;
   gsr::geom_from_chunk(const_cast<char*>(geom_buffer), (size_t)p->P, g, p->F);
   gsr::ImageState img;
-  gsr::image_from_chunk(const_cast<char*>(image_buffer), (size_t)p->width * p->height, (size_t)cam.gx * cam.gy, img);
+  gsr::image_from_chunk(const_cast<char*>(image_buffer), p->width, p->height, img);
   gsr::BinState b;
-  gsr::bin_from_chunk(const_cast<char*>(binning_buffer), (size_t)(num_rendered > 0 ? num_rendered : 0), b);
+  gsr::bin_from_chunk(const_cast<char*>(binning_buffer), (size_t)(num_rendered > 0 ? num_rendered : 0), 0, 0, b);
   unsigned long long* d = nullptr;
   CUDA_TRY(cudaMalloc(&d, 4 * sizeof(unsigned long long)));
   CUDA_TRY(cudaMemsetAsync(d, 0, 4 * sizeof(unsigned long long), stream));
@@ -327,9 +330,10 @@ int gsr_export_state(const gsr_params* p, int num_rendered, const char* geom_buf
   gsr::GeomState g;
   gsr::geom_from_chunk(const_cast<char*>(geom_buffer), (size_t)P, g, p->F);
   gsr::ImageState img;
-  gsr::image_from_chunk(const_cast<char*>(image_buffer), N, (size_t)T, img);
+  gsr::image_from_chunk(const_cast<char*>(image_buffer), p->width, p->height, img);
   gsr::BinState b{};
-  if (binning_buffer) gsr::bin_from_chunk(const_cast<char*>(binning_buffer), (size_t)(num_rendered > 0 ? num_rendered : 0), b);
+  if (binning_buffer)
+    gsr::bin_from_chunk(const_cast<char*>(binning_buffer), (size_t)(num_rendered > 0 ? num_rendered : 0), 0, 0, b);
   gsr::launch_export(P, num_rendered, cam, g, b, tiles_touched, depths, means2D, conic_opacity, rgb, clamped,
                      sorted_keys, stream);
   if (num_rendered > 0 && binning_buffer) {

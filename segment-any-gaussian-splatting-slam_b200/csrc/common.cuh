@@ -18,8 +18,11 @@ constexpr int TILE_X = 16, TILE_Y = 16;  // fixed by parity: reference config.h:
 //   tiles_touched u32, rect u32 (x0 | y0<<8 | x1<<16 | y1<<24), clamped u8 (bit c = channel c clamped)
 //   dkeys_a/b     u64 = depth_bits<<32 | idx   (ping-pong of the depth radix sort)
 //   sort scratch  u32[256 * nblk(P)] + u32[256]; scan scratch u32[nblk256(P) + 8]
-// image (per pixel / tile): final_T f32[N], n_contrib u32[N], ranges uint2[T]
-// binning (per instance): items_a/b u64 = tile<<32 | idx, point_list u32, sort scratch
+// image (per pixel / tile): final_T f32[N], n_contrib u32[N], ranges uint2[T], tile_off u32[T],
+//   sat i32[(gy+1)(gx+1)] / ssat i32[(sgy+1)(sgx+1)] (corner-splatted coverage counts, see binning.cu),
+//   l1_off u32[NS+1]
+// binning: point_list u32[R] (FIRST: all the backward pass needs), L1 supertile lists uint2[L1]
+//   {packed rect, Gaussian idx}, per-(supertile, warp) counters u32[NS * ceil(P/32)]
 // ---------------------------------------------------------------------------------------------
 constexpr int SORT_THREADS = 256;
 constexpr int SORT_IPT = 16;                           // items per thread
@@ -42,21 +45,35 @@ struct GeomState {
   uint32_t* block_hist;   // 256 * sort_blocks(P)
   uint32_t* digit_total;  // 256
   uint32_t* block_sums;   // emit_blocks(P) + 8
-  int* flags;             // [0] num_rendered, [1] prefiltered-cull error
+  int* flags;             // [0] num_rendered, [1] prefiltered-cull error, [2..3] L1 list total (u64)
   float* grad_rows;       // P * 32 (F=16) or P * 48 (F=32): backward intermediate, see render_bwd.cu
 };
 struct ImageState {
   float* final_T;
   uint32_t* n_contrib;
   uint2* ranges;
+  uint32_t* tile_off;  // T: start of every tile's list (ranges holds (0,0) for empty tiles, like the reference)
+  int* sat;            // (gy+1)*(gx+1), zeroed before preprocess
+  int* ssat;           // (sgy+1)*(sgx+1), contiguous with sat (one memset)
+  uint32_t* l1_off;    // NS+1
 };
 struct BinState {
-  uint64_t* items_a;
-  uint64_t* items_b;
   uint32_t* point_list;
-  uint32_t* block_hist;
-  uint32_t* digit_total;
+  uint2* l1;            // {rect, idx}
+  uint32_t* warp_cnt;   // [NS][NW]
 };
+// Supertiles: S x S tiles, S = 8 unless that gives more than 256 supertiles (then 16).
+struct SuperGrid {
+  int S, sgx, sgy, NS;
+};
+__host__ __device__ inline SuperGrid super_grid(int gx, int gy) {
+  SuperGrid g;
+  g.S = (((gx + 7) / 8) * ((gy + 7) / 8) <= 256) ? 8 : 16;
+  g.sgx = (gx + g.S - 1) / g.S;
+  g.sgy = (gy + g.S - 1) / g.S;
+  g.NS = g.sgx * g.sgy;
+  return g;
+}
 
 template <typename T>
 inline void carve(char*& p, T*& out, size_t count) {
@@ -82,21 +99,30 @@ inline size_t geom_from_chunk(char* chunk, size_t P, GeomState& g, int F = 32) {
   carve(p, g.grad_rows, P * (size_t)grad_row_floats(F));
   return (size_t)(p - chunk) + 256;
 }
-inline size_t image_from_chunk(char* chunk, size_t N, size_t T, ImageState& s) {
+inline size_t image_from_chunk(char* chunk, int W, int H, ImageState& s) {
   char* p = chunk;
+  const size_t N = (size_t)W * H;
+  const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
+  const SuperGrid sg = super_grid(gx, gy);
   carve(p, s.final_T, N);
   carve(p, s.n_contrib, N);
-  carve(p, s.ranges, T);
+  carve(p, s.ranges, (size_t)gx * gy);
+  carve(p, s.tile_off, (size_t)gx * gy);
+  carve(p, s.sat, (size_t)(gx + 1) * (gy + 1) + (size_t)(sg.sgx + 1) * (sg.sgy + 1));
+  s.ssat = s.sat + (size_t)(gx + 1) * (gy + 1);
+  carve(p, s.l1_off, (size_t)sg.NS + 1);
   return (size_t)(p - chunk) + 256;
 }
-inline size_t bin_from_chunk(char* chunk, size_t R, BinState& b) {
+inline size_t sat_ints(int gx, int gy) {
+  const SuperGrid sg = super_grid(gx, gy);
+  return (size_t)(gx + 1) * (gy + 1) + (size_t)(sg.sgx + 1) * (sg.sgy + 1);
+}
+// point_list comes first: the backward pass calls this with l1_total = nw_ns = 0.
+inline size_t bin_from_chunk(char* chunk, size_t R, size_t l1_total, size_t nw_ns, BinState& b) {
   char* p = chunk;
-  size_t Rp = R ? R : 1;
-  carve(p, b.items_a, Rp);
-  carve(p, b.items_b, Rp);
-  carve(p, b.point_list, Rp);
-  carve(p, b.block_hist, (size_t)RADIX * (sort_blocks((int64_t)Rp)));
-  carve(p, b.digit_total, RADIX);
+  carve(p, b.point_list, R ? R : 1);
+  carve(p, b.l1, l1_total ? l1_total : 1);
+  carve(p, b.warp_cnt, nw_ns ? nw_ns : 1);
   return (size_t)(p - chunk) + 256;
 }
 
@@ -133,10 +159,12 @@ struct FwdInputs {
   bool prefiltered;
 };
 void launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t s);
-void launch_preprocess(const FwdInputs& in, const Cam& cam, GeomState& g, int* radii, uint8_t* is_used, cudaStream_t s);
-// depth sort + scan; leaves depth-ordered keys in g.dkeys_a, block sums ready, total in g.flags[0]
-void launch_depth_sort_and_count(int P, GeomState& g, cudaStream_t s, int& launches);
-// emission + tile sort + ranges
+void launch_preprocess(const FwdInputs& in, const Cam& cam, GeomState& g, ImageState& img, int* radii,
+                       uint8_t* is_used, cudaStream_t s);
+// depth sort (leaves depth-ordered keys in g.dkeys_a) + tile / supertile offsets from the coverage
+// grids: ranges, tile_off, l1_off, R -> g.flags[0], L1 total -> g.flags[2..3]
+void launch_depth_sort_and_offsets(int P, const Cam& cam, GeomState& g, ImageState& img, cudaStream_t s, int& launches);
+// supertile lists + per-tile pull into point_list
 void launch_binning(int P, int64_t R, const Cam& cam, GeomState& g, BinState& b, ImageState& img, cudaStream_t s,
                     int& launches);
 void launch_render_forward(int F, const Cam& cam, const GeomState& g, const BinState& b,

@@ -145,10 +145,11 @@ preprocess_kernel(const FwdInputs in, const Cam cam, float4* __restrict__ rec, u
   if (is_used) is_used[idx] = touched > 0;
 }
 
-void launch_preprocess(const FwdInputs& in, const Cam& cam, GeomState& g, int* radii, uint8_t* is_used,
-                       cudaStream_t s) {
+void launch_preprocess(const FwdInputs& in, const Cam& cam, GeomState& g, ImageState& img, int* radii,
+                       uint8_t* is_used, cudaStream_t s) {
   preprocess_kernel<<<(in.P + 255) / 256, 256, 0, s>>>(in, cam, g.rec, g.tiles_touched, g.rect, g.clamped, g.dkeys_a,
                                                       radii, is_used, g.flags);
+  (void)img;
 }
 
 }  // namespace gsr
