@@ -1,11 +1,22 @@
 // K5: backward alpha blending for sm_100a. Behaviour: reference backward.cu:429-680 (SURVEY 8a a20,
 // checklist 13-16). The reference issues 12+F float atomicAdd per contributing (pixel, Gaussian)
 // pair, all 32 lanes of a warp hitting the same address. Here each warp (an 8x4 pixel block)
-// reduces its 12+F partial sums with a butterfly transpose-reduce (31 SHFL for 32 values: after
-// the reduce lane L holds the total of value L) and issues ONE coalesced red.global.add per
-// (warp, Gaussian) into a packed 128-byte gradient row; the per-Gaussian backward (K6+K7) then
-// consumes the rows. Staging is the same TMA bulk-copy pipeline as the forward kernel, walking
-// the tile's list back to front and starting at the tile's deepest contributor.
+// reduces its 12+F partial sums with shuffles and issues ONE coalesced red.global.add per
+// (warp, Gaussian) into a packed gradient row; the per-Gaussian backward (K6+K7) then consumes
+// the rows. Staging is the same TMA bulk-copy pipeline as the forward kernel, walking the tile's
+// list back to front and starting at the tile's deepest contributor.
+//
+// Arithmetic restructuring (same mathematics as the reference, different summation order; the
+// gradient bar is relative 1e-3):
+//  * The reference keeps one running "accum_rec" per channel (3 + F + depth recurrences,
+//    backward.cu:574-599, 614-640). Since T_i * accum_rec_i[ch] = sum_{j>i} w_j c_j[ch] / (1 - a_i)
+//    with w_j = a_j T_j, the alpha gradient only needs ONE scalar suffix sum
+//    S_i = sum_{j>i} w_j E_j,  E_j = <c_j, dL/dC> + <o_j, dL/dO> + depth_j dL/dD :
+//    dL/da_i = T_i E_i - (S_i + T_final (<bg, dL/dC> + 15 dL/dD)) / (1 - a_i).
+//    One 20-term dot product per pair replaces 20 three-instruction recurrences and 20 registers.
+//  * Feature-channel partial sums are produced directly in a lane-permuted register order
+//    (slot s of lane l holds channel s ^ (l & 15)), which makes the butterfly transpose-reduce
+//    select-free: v[s] += shfl_xor(v[s ^ B], B).
 //
 // Gradient row layout (float index): 0 dmean2D.x  1 dmean2D.y  2 dconic.x  3 dconic.y  4 dconic.w
 // 5 dcov_zx  6 dcov_yz  7 dopacity  8 ddepth  9..11 dcolor  12..12+F-1 dfeature.
@@ -25,74 +36,40 @@ struct BwdSmem {
   uint32_t max_contrib;
 };
 
-// Butterfly transpose-reduce: v[0..31] per lane -> lane L returns sum over lanes of v[L].
-__device__ __forceinline__ float warp_transpose_reduce32(float (&v)[32], int lane) {
+constexpr unsigned FULL = 0xffffffffu;
+
+// Select-free butterfly reduce over N = 16 or 32 slots. Precondition: slot s of lane l holds the
+// partial sum of logical index s ^ (l & (N-1)). Returns, in every lane l, the warp total of logical
+// index l & (N-1).
+template <int N>
+__device__ __forceinline__ float warp_permuted_reduce(float (&v)[N]) {
 #pragma unroll
-  for (int i = 0; i < 16; i++) {
-    const bool up = lane & 16;
-    float send = up ? v[i] : v[i + 16];
-    float keep = up ? v[i + 16] : v[i];
-    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
-  }
+  for (int B = N / 2; B >= 1; B >>= 1) {
 #pragma unroll
-  for (int i = 0; i < 8; i++) {
-    const bool up = lane & 8;
-    float send = up ? v[i] : v[i + 8];
-    float keep = up ? v[i + 8] : v[i];
-    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+    for (int s = 0; s < B; s++) v[s] += __shfl_xor_sync(FULL, v[s + B], B);
   }
-#pragma unroll
-  for (int i = 0; i < 4; i++) {
-    const bool up = lane & 4;
-    float send = up ? v[i] : v[i + 4];
-    float keep = up ? v[i + 4] : v[i];
-    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-  }
-#pragma unroll
-  for (int i = 0; i < 2; i++) {
-    const bool up = lane & 2;
-    float send = up ? v[i] : v[i + 2];
-    float keep = up ? v[i + 2] : v[i];
-    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
-  }
-  {
-    const bool up = lane & 1;
-    float send = up ? v[0] : v[1];
-    float keep = up ? v[1] : v[0];
-    v[0] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
-  }
+  if (N == 16) v[0] += __shfl_xor_sync(FULL, v[0], 16);
   return v[0];
 }
-// 16 values: lane L returns the total of v[L & 15] (both half-warps hold a copy).
+// Transpose-reduce with selects for values that cannot be produced in permuted order:
+// v[0..15] per lane -> every lane l returns the warp total of v[l & 15].
 __device__ __forceinline__ float warp_transpose_reduce16(float (&v)[16], int lane) {
 #pragma unroll
-  for (int i = 0; i < 8; i++) {
-    const bool up = lane & 8;
-    float send = up ? v[i] : v[i + 8];
-    float keep = up ? v[i + 8] : v[i];
-    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-  }
+  for (int B = 8; B >= 1; B >>= 1) {
+    const bool up = lane & B;
 #pragma unroll
-  for (int i = 0; i < 4; i++) {
-    const bool up = lane & 4;
-    float send = up ? v[i] : v[i + 4];
-    float keep = up ? v[i + 4] : v[i];
-    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+    for (int i = 0; i < B; i++) {
+      const float send = up ? v[i] : v[i + B];
+      const float keep = up ? v[i + B] : v[i];
+      v[i] = keep + __shfl_xor_sync(FULL, send, B);
+    }
   }
-#pragma unroll
-  for (int i = 0; i < 2; i++) {
-    const bool up = lane & 2;
-    float send = up ? v[i] : v[i + 2];
-    float keep = up ? v[i + 2] : v[i];
-    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
-  }
-  {
-    const bool up = lane & 1;
-    float send = up ? v[0] : v[1];
-    float keep = up ? v[1] : v[0];
-    v[0] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
-  }
-  return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 16);
+  return v[0] + __shfl_xor_sync(FULL, v[0], 16);
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
 }
 
 template <int F>
@@ -123,7 +100,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   }
   __syncthreads();
   {
-    uint32_t m = __reduce_max_sync(0xffffffffu, last_contributor);
+    uint32_t m = __reduce_max_sync(FULL, last_contributor);
     if (lane == 0 && m) atomicMax(&sm.max_contrib, m);
   }
   __syncthreads();
@@ -148,19 +125,18 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
 
   const float T_final = inside ? final_T[pix_id] : 0.f;
   float T = T_final;
-  float acc_c[3] = {0.f, 0.f, 0.f};  // accum_rec, updated eagerly (same arithmetic as the reference's lazy form)
-  float acc_o[F];
-  float acc_d = 0.f;
-  float dpx[3], dpo[F], dpd = 0.f;
+  float dpx[3], dpo[F], dpo_perm[F], dpd = 0.f;
 #pragma unroll
   for (int c = 0; c < 3; c++) dpx[c] = inside ? dL_dpix[c * HW + pix_id] : 0.f;
 #pragma unroll
   for (int c = 0; c < F; c++) {
     dpo[c] = inside ? dL_dpix_obj[c * HW + pix_id] : 0.f;
-    acc_o[c] = 0.f;
+    dpo_perm[c] = inside ? dL_dpix_obj[(size_t)(c ^ (lane & (F - 1))) * HW + pix_id] : 0.f;
   }
   if (inside) dpd = dL_dpix_depth[pix_id];
-  const float bg_dot_dpixel = bg[0] * dpx[0] + bg[1] * dpx[1] + bg[2] * dpx[2];
+  // suffix sum S, seeded with the background term T_final * (<bg, dL/dC> + 15 dL/dD)
+  // (backward.cu:607-610, 648): it always appears as (S + that) / (1 - alpha).
+  float S = T_final * (bg[0] * dpx[0] + bg[1] * dpx[1] + bg[2] * dpx[2] + 15.f * dpd);
   const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
 
   if (nbatch > 0) issue(0);
@@ -172,84 +148,76 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     const int cnt = min(BB, todo - b * BB);
     for (int j = 0; j < cnt; j++) {
       const uint32_t pos = (uint32_t)(todo - 1 - (b * BB + j));  // 0-based position in the tile's list
-      const float4 r0 = sm.rec[st][j][0];
-      const float4 r1 = sm.rec[st][j][1];
+      const float4 r0 = sm.rec[st][j][0];  // px, py, conic a, conic b
+      const float4 r1 = sm.rec[st][j][1];  // conic c, opacity, cov_zx, cov_yz
       const float dx = r0.x - pixx, dy = r0.y - pixy;
       const float power = -0.5f * (r0.z * dx * dx + r1.x * dy * dy) - r0.w * dx * dy;
-      bool hit = pos < last_contributor && power <= 0.0f;
-      float G = 0.f, alpha = 0.f;
-      if (hit) {
-        G = expf(power);
-        alpha = min(0.99f, r1.y * G);
-        hit = alpha >= 1.0f / 255.0f;
-      }
-      if (!__any_sync(0xffffffffu, hit)) continue;
+      const bool cand = pos < last_contributor && power <= 0.0f;
+      if (!__any_sync(FULL, cand)) continue;
+      float G = expf(power);
+      float alpha = min(0.99f, r1.y * G);
+      const bool hit = cand && alpha >= 1.0f / 255.0f;
+      if (!__any_sync(FULL, hit)) continue;
 
-      const float4 r2 = sm.rec[st][j][2];
-      float v[32];
-      float v2[16];
+      // Lanes without a hit run the same instructions with G = alpha = 0, which zeroes every
+      // partial sum below and leaves T and S unchanged (hit rate inside such a warp is ~95 %).
+      G = hit ? G : 0.f;
+      alpha = hit ? alpha : 0.f;
+      const float4 r2 = sm.rec[st][j][2];  // depth, r, g, b
+      const float inv1ma = rcp_approx(1.f - alpha);
+      T = T * inv1ma;
+      const float w = alpha * T;  // d(out channel) / d(channel value of this Gaussian)
+      const float a = r0.z, bq = r0.w, c = r1.x, covzx = r1.z, covyz = r1.w;
+      const float cza = covzx * a + covyz * bq;
+      const float czb = covzx * bq + covyz * c;
+      const float depth = r2.x - cza * dx - czb * dy;
+      float E = depth * dpd;
+      E = fmaf(r2.y, dpx[0], E);
+      E = fmaf(r2.z, dpx[1], E);
+      E = fmaf(r2.w, dpx[2], E);
+      float vf[F];
 #pragma unroll
-      for (int k = 0; k < 32; k++) v[k] = 0.f;
-#pragma unroll
-      for (int k = 0; k < 16; k++) v2[k] = 0.f;
-      if (hit) {
-        T = T / (1.f - alpha);
-        const float w = alpha * T;  // dchannel_dcolor
-        float dL_dalpha = 0.0f;
-        const float col[3] = {r2.y, r2.z, r2.w};
-#pragma unroll
-        for (int ch = 0; ch < 3; ch++) {
-          dL_dalpha += (col[ch] - acc_c[ch]) * dpx[ch];
-          v[9 + ch] = w * dpx[ch];
-          acc_c[ch] = alpha * col[ch] + (1.f - alpha) * acc_c[ch];
-        }
-#pragma unroll
-        for (int q = 0; q < F / 4; q++) {
-          const float4 f4 = sm.feat[st][j][q];
-          const float fo[4] = {f4.x, f4.y, f4.z, f4.w};
-#pragma unroll
-          for (int e = 0; e < 4; e++) {
-            const int ch = 4 * q + e;
-            dL_dalpha += (fo[e] - acc_o[ch]) * dpo[ch];
-            const float gv = w * dpo[ch];
-            if (12 + ch < 32) v[12 + ch] = gv; else v2[(12 + ch - 32) & 15] = gv;
-            acc_o[ch] = alpha * fo[e] + (1.f - alpha) * acc_o[ch];
-          }
-        }
-        dL_dalpha *= T;
-        const float inv1ma = 1.f / (1.f - alpha);
-        dL_dalpha += (-T_final * inv1ma) * bg_dot_dpixel;
-        // depth path (backward.cu:614-649); T_d == T, alpha_d == alpha, G_d == G
-        const float covzx = r1.z, covyz = r1.w;
-        const float cza = covzx * r0.z + covyz * r0.w;  // covzx*a + covyz*b
-        const float czb = covzx * r0.w + covyz * r1.x;  // covzx*b + covyz*c
-        const float depth = r2.x - cza * dx - czb * dy;
-        v[8] = w * dpd;
-        v[5] = dpd * ((-r0.z * dx - r0.w * dy) * w);  // d/dcov_zx
-        v[6] = dpd * ((-r0.w * dx) * w);              // d/dcov_yz (sic, backward.cu:629)
-        const float dL_dalpha_d = dpd * ((depth - acc_d) * T) + (-T_final * inv1ma) * (15.f * dpd);
-        acc_d = alpha * depth + (1.f - alpha) * acc_d;
-        const float dL_da_tot = dL_dalpha + dL_dalpha_d;
-        const float dL_dG = r1.y * dL_da_tot;
-        const float gdx = G * dx, gdy = G * dy;
-        const float dG_ddelx = -gdx * r0.z - gdy * r0.w;
-        const float dG_ddely = -gdy * r1.x - gdx * r0.w;
-        v[0] = (dL_dG * dG_ddelx + dpd * (-cza * w)) * ddelx_dx;
-        v[1] = (dL_dG * dG_ddely + dpd * (-czb * w)) * ddely_dy;
-        v[2] = -0.5f * gdx * dx * dL_dG + dpd * ((-covzx * dx) * w);
-        v[3] = -0.5f * gdx * dy * dL_dG + dpd * ((-covyz * dx - covzx * dy) * w);
-        v[4] = -0.5f * gdy * dy * dL_dG + dpd * ((-covyz * dy) * w);
-        v[7] = G * dL_da_tot;
+      for (int q = 0; q < F / 4; q++) {
+        const float4 f4 = sm.feat[st][j][q];
+        E = fmaf(f4.x, dpo[4 * q + 0], E);
+        E = fmaf(f4.y, dpo[4 * q + 1], E);
+        E = fmaf(f4.z, dpo[4 * q + 2], E);
+        E = fmaf(f4.w, dpo[4 * q + 3], E);
       }
+#pragma unroll
+      for (int k = 0; k < F; k++) vf[k] = w * dpo_perm[k];
+      const float dL_da = T * E - S * inv1ma;
+      S = fmaf(w, E, S);
+      const float wd = w * dpd;
+      const float dL_dG = r1.y * dL_da;
+      const float gdx = G * dx, gdy = G * dy;
+      const float dG_ddelx = -gdx * a - gdy * bq;
+      const float dG_ddely = -gdy * c - gdx * bq;
+      float v[16];
+      v[0] = (dL_dG * dG_ddelx - wd * cza) * ddelx_dx;
+      v[1] = (dL_dG * dG_ddely - wd * czb) * ddely_dy;
+      v[2] = -0.5f * gdx * dx * dL_dG - wd * covzx * dx;
+      v[3] = -0.5f * gdx * dy * dL_dG - wd * (covyz * dx + covzx * dy);
+      v[4] = -0.5f * gdy * dy * dL_dG - wd * covyz * dy;
+      v[5] = -wd * (a * dx + bq * dy);  // d/dcov_zx
+      v[6] = -wd * bq * dx;             // d/dcov_yz (sic, backward.cu:629)
+      v[7] = G * dL_da;
+      v[8] = wd;
+      v[9] = w * dpx[0];
+      v[10] = w * dpx[1];
+      v[11] = w * dpx[2];
+      v[12] = v[13] = v[14] = v[15] = 0.f;
+
       const uint32_t gid = sm.id[st][j];
       float* row = grad_rows + (size_t)gid * ROW;
-      const float s0 = warp_transpose_reduce32(v, lane);
+      const float sf = warp_permuted_reduce<F>(vf);        // lane l: feature channel l & (F-1)
+      const float ss = warp_transpose_reduce16(v, lane);   // lane l: special l & 15
       if constexpr (F == 16) {
-        if (lane < 28) atomicAdd(row + lane, s0);
+        // one RED: lanes 0..15 -> features, lanes 16..27 -> the 12 specials
+        if (lane < 28) atomicAdd(row + (lane < 16 ? 12 + lane : lane - 16), lane < 16 ? sf : ss);
       } else {
-        atomicAdd(row + lane, s0);
-        const float s1 = warp_transpose_reduce16(v2, lane);
-        if (lane < 12) atomicAdd(row + 32 + lane, s1);
+        atomicAdd(row + 12 + lane, sf);
+        if (lane < 12) atomicAdd(row + lane, ss);
       }
     }
     __syncthreads();  // release stage st for the copy issued at the top of the next iteration

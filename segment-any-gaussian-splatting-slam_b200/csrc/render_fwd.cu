@@ -70,46 +70,44 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     mbar_wait(&sm.bar[st], (uint32_t)(b >> 1) & 1u);
     const int cnt = min(RB, todo - b * RB);
     if (!__all_sync(0xffffffffu, done)) {
-      for (int j = 0; j < cnt; j++) {
-        const float4 r0 = sm.rec[st][j][0];  // px, py, conic a, conic b
-        const float4 r1 = sm.rec[st][j][1];  // conic c, opacity, cov_zx, cov_yz
+      const float4* rp = &sm.rec[st][0][0];
+      const float4* fp = &sm.feat[st][0][0];
+      for (int j = 0; j < cnt; j++, rp += 3, fp += F / 4) {
+        const float4 r0 = rp[0];  // px, py, conic a, conic b
+        const float4 r1 = rp[1];  // conic c, opacity, cov_zx, cov_yz
         const float dx = r0.x - pixx, dy = r0.y - pixy;
         const float power = -0.5f * (r0.z * dx * dx + r1.x * dy * dy) - r0.w * dx * dy;
-        bool hit = !done && power <= 0.0f;
-        float alpha = 0.f, test_T = 0.f;
-        if (hit) {
-          alpha = min(0.99f, r1.y * expf(power));
-          hit = alpha >= 1.0f / 255.0f;
-          if (hit) {
-            test_T = T * (1 - alpha);
-            if (test_T < 0.0001f) { done = true; hit = false; }
-          }
-        }
+        const bool cand = !done && power <= 0.0f;                  // forward.cu:365-366
+        if (!__any_sync(0xffffffffu, cand)) continue;
+        // T, alpha and the two thresholds use exactly the reference's operations (n_contrib and
+        // final_T are bit-exact); lanes that are not candidates compute values that are masked out.
+        const float alpha = min(0.99f, r1.y * expf(power));       // forward.cu:371
+        const bool ok = cand && alpha >= 1.0f / 255.0f;            // forward.cu:372-373
+        const float test_T = T * (1 - alpha);
+        const bool stop = ok && test_T < 0.0001f;                  // forward.cu:375-379: pixel done, not blended
+        const bool hit = ok && !stop;
+        done = done || stop;
         if (__any_sync(0xffffffffu, hit)) {
-          const float4 r2 = sm.rec[st][j][2];  // depth, r, g, b
-          float4 f[F / 4];
+          const float4 r2 = rp[2];  // depth, r, g, b
+          const float w = hit ? alpha * T : 0.f;  // colour/feature/depth sums need 1e-4, not bit-exactness
+          C[0] = fmaf(r2.y, w, C[0]);
+          C[1] = fmaf(r2.z, w, C[1]);
+          C[2] = fmaf(r2.w, w, C[2]);
 #pragma unroll
-          for (int q = 0; q < F / 4; q++) f[q] = sm.feat[st][j][q];
-          if (hit) {
-            C[0] += r2.y * alpha * T;
-            C[1] += r2.z * alpha * T;
-            C[2] += r2.w * alpha * T;
-#pragma unroll
-            for (int q = 0; q < F / 4; q++) {
-              O[4 * q + 0] += f[q].x * alpha * T;
-              O[4 * q + 1] += f[q].y * alpha * T;
-              O[4 * q + 2] += f[q].z * alpha * T;
-              O[4 * q + 3] += f[q].w * alpha * T;
-            }
-            const float covzx = r1.z, covyz = r1.w;
-            const float depth_c = r2.x - (covzx * r0.z + covyz * r0.w) * dx - (covzx * r0.w + covyz * r1.x) * dy;
-            D += depth_c * alpha * T;
-            T = test_T;
-            last_contributor = (uint32_t)(b * RB + j + 1);
+          for (int q = 0; q < F / 4; q++) {
+            const float4 f4 = fp[q];
+            O[4 * q + 0] = fmaf(f4.x, w, O[4 * q + 0]);
+            O[4 * q + 1] = fmaf(f4.y, w, O[4 * q + 1]);
+            O[4 * q + 2] = fmaf(f4.z, w, O[4 * q + 2]);
+            O[4 * q + 3] = fmaf(f4.w, w, O[4 * q + 3]);
           }
-        } else if (__all_sync(0xffffffffu, done)) {
-          break;
+          const float covzx = r1.z, covyz = r1.w;
+          const float depth_c = r2.x - (covzx * r0.z + covyz * r0.w) * dx - (covzx * r0.w + covyz * r1.x) * dy;
+          D = fmaf(depth_c, w, D);
+          T = hit ? test_T : T;
+          last_contributor = hit ? (uint32_t)(b * RB + j + 1) : last_contributor;
         }
+        if (__any_sync(0xffffffffu, stop) && __all_sync(0xffffffffu, done)) break;
       }
     }
     // block vote (reference forward.cu:339-341) + release of stage st for the copy issued next iteration
