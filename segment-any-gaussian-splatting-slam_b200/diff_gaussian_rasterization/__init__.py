@@ -1,0 +1,105 @@
+"""Drop-in for the reference's `diff_gaussian_rasterization` Python module
+(submodules/diff-gaussian-rasterization/diff_gaussian_rasterization/__init__.py): same names, same
+argument order, same outputs, so `render_4` (gaussian_renderer/__init__.py:325-480) runs unchanged.
+
+    GaussianRasterizationSettings   12-field NamedTuple            (reference :166-178)
+    GaussianRasterizer(settings)    .forward(...) -> (depth, color, radii, objects, is_used), .markVisible(positions)
+    rasterize_gaussians(...)        autograd entry point            (reference :21-44)
+
+Underneath sits gsraster_b200.capi -> lib/libgsraster_b200.so (hand-written sm_100a CUDA behind the C ABI of
+include/gsraster_b200.h). There is no CPU fallback: CPU tensors or a missing library raise.
+"""
+from typing import NamedTuple
+
+import torch
+import torch.nn as nn
+
+from gsraster_b200 import capi as _C
+
+
+def rasterize_gaussians(means3D, means2D, sh, sh_objs, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                        raster_settings):
+    return _RasterizeGaussians.apply(means3D, means2D, sh, sh_objs, colors_precomp, opacities, scales, rotations,
+                                     cov3Ds_precomp, raster_settings)
+
+
+class _RasterizeGaussians(torch.autograd.Function):
+    """Reference :46-164. Gradient slots: (means3D, means2D, sh, sh_objs, colors_precomp, opacities, scales,
+    rotations, cov3Ds_precomp, None)."""
+
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, sh_objs, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                raster_settings):
+        rs = raster_settings
+        num_rendered, depth, color, objects, radii, is_used, geomBuffer, binningBuffer, imgBuffer = \
+            _C.rasterize_gaussians(rs.bg, means3D, colors_precomp, opacities, scales, rotations, rs.scale_modifier,
+                                   cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
+                                   rs.image_height, rs.image_width, sh, sh_objs, rs.sh_degree, rs.campos,
+                                   rs.prefiltered, rs.debug)
+        ctx.raster_settings = rs
+        ctx.num_rendered = num_rendered
+        ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, sh_objs,
+                              geomBuffer, binningBuffer, imgBuffer)
+        ctx.mark_non_differentiable(radii, is_used)
+        return depth, color, radii, objects, is_used
+
+    @staticmethod
+    def backward(ctx, grad_depth, grad_out_color, grad_radii, grad_out_objects, grad_is_used):
+        rs = ctx.raster_settings
+        (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, sh_objs, geomBuffer, binningBuffer,
+         imgBuffer) = ctx.saved_tensors
+        H, W = rs.image_height, rs.image_width
+        z = lambda g, c: g if g is not None else torch.zeros((c, H, W), dtype=torch.float32, device=means3D.device)
+        F = sh_objs.numel() // max(means3D.size(0), 1)
+        grad_depth, grad_out_color, grad_out_objects = z(grad_depth, 1), z(grad_out_color, 3), z(grad_out_objects, F)
+        (grad_means2D, grad_colors_precomp, grad_objects, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh,
+         grad_scales, grad_rotations) = _C.rasterize_gaussians_backward(
+            rs.bg, means3D, radii, colors_precomp, scales, rotations, rs.scale_modifier, cov3Ds_precomp, rs.viewmatrix,
+            rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_depth, grad_out_color, sh, grad_out_objects, sh_objs,
+            rs.sh_degree, rs.campos, geomBuffer, ctx.num_rendered, binningBuffer, imgBuffer, rs.debug)
+        return (grad_means3D, grad_means2D, grad_sh, grad_objects.unsqueeze(1), grad_colors_precomp, grad_opacities,
+                grad_scales, grad_rotations, grad_cov3Ds_precomp, None)
+
+
+class GaussianRasterizationSettings(NamedTuple):
+    image_height: int
+    image_width: int
+    tanfovx: float
+    tanfovy: float
+    bg: torch.Tensor
+    scale_modifier: float
+    viewmatrix: torch.Tensor
+    projmatrix: torch.Tensor
+    sh_degree: int
+    campos: torch.Tensor
+    prefiltered: bool
+    debug: bool
+
+
+class GaussianRasterizer(nn.Module):
+    def __init__(self, raster_settings):
+        super().__init__()
+        self.raster_settings = raster_settings
+
+    def markVisible(self, positions):
+        with torch.no_grad():
+            rs = self.raster_settings
+            return _C.mark_visible(positions, rs.viewmatrix, rs.projmatrix)
+
+    def forward(self, means3D, means2D, opacities, shs=None, sh_objs=None, colors_precomp=None, scales=None,
+                rotations=None, cov3D_precomp=None):
+        # same two checks and messages as the reference (:200-204)
+        if (shs is None and colors_precomp is None) or (shs is not None and colors_precomp is not None):
+            raise Exception('Please provide excatly one of either SHs or precomputed colors!')
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or \
+                ((scales is not None or rotations is not None) and cov3D_precomp is not None):
+            raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
+        e = torch.Tensor([])  # "absent" == 0-element tensor -> NULL pointer (reference :206-219)
+        shs = e if shs is None else shs
+        colors_precomp = e if colors_precomp is None else colors_precomp
+        scales = e if scales is None else scales
+        rotations = e if rotations is None else rotations
+        cov3D_precomp = e if cov3D_precomp is None else cov3D_precomp
+        sh_objs = e if sh_objs is None else sh_objs
+        return rasterize_gaussians(means3D, means2D, shs, sh_objs, colors_precomp, opacities, scales, rotations,
+                                   cov3D_precomp, self.raster_settings)

@@ -141,3 +141,23 @@ def test_mapping_step_gloo_world2():
         for j, k in enumerate(("means3D", "sh", "objects", "opacity", "scales", "rotations")):
             assert first[k] == views_sum * (j + 1), (rank, k)
     assert res[0][2] == res[1][2]
+
+
+def test_dropin_modules_import_and_validate_like_the_reference():
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer, rasterize_gaussians  # noqa: F401
+    import simple_knn._C as knn
+    assert GaussianRasterizationSettings._fields == ("image_height", "image_width", "tanfovx", "tanfovy", "bg",
+                                                     "scale_modifier", "viewmatrix", "projmatrix", "sh_degree",
+                                                     "campos", "prefiltered", "debug")
+    assert callable(knn.distCUDA2)
+    rs = GaussianRasterizationSettings(48, 64, 0.5, 0.4, torch.zeros(3), 1.0, torch.eye(4), torch.eye(4), 0,
+                                       torch.zeros(3), False, False)
+    r = GaussianRasterizer(rs)
+    m = torch.zeros(4, 3)
+    with pytest.raises(Exception, match="excatly one of either SHs"):
+        r(means3D=m, means2D=m, opacities=torch.zeros(4, 1), scales=m, rotations=torch.zeros(4, 4))
+    with pytest.raises(Exception, match="scale/rotation pair"):
+        r(means3D=m, means2D=m, opacities=torch.zeros(4, 1), shs=torch.zeros(4, 1, 3), scales=m)
+    with pytest.raises(RuntimeError):  # CPU tensors: no CPU fallback
+        r(means3D=m, means2D=m, opacities=torch.zeros(4, 1), shs=torch.zeros(4, 1, 3), sh_objs=torch.zeros(4, 1, 16),
+          scales=m, rotations=torch.zeros(4, 4))

@@ -250,3 +250,43 @@ def test_forward_is_deterministic_and_backward_stable():
         assert (h.npy(a[k]) == h.npy(b[k])).all(), k
     for k in h.GRAD_KEYS:
         assert h.grad_rel_err(a[k], b[k]) < 1e-5, k
+
+
+# ---- drop-in Python surface (reference diff_gaussian_rasterization/__init__.py, simple_knn/_C) -----
+def test_dropin_module_autograd_matches_capi():
+    import torch
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    from simple_knn._C import distCUDA2
+    W, H, P = 320, 256, 20_000
+    sc = scenes.make_scene(P, sh_degree=2, F=16, seed=31, W=W, H=H, scale_mul=2.0)
+    cam = scenes.make_camera(W, H, 1)
+    grads = scenes.make_upstream_grads(W, H, 16)
+    d = h.to_torch(sc, cam)
+    prm = {k: d[k].clone().requires_grad_(True) for k in ("means3D", "shs", "sh_objs", "opacities", "scales", "rotations")}
+    means2D = torch.zeros_like(prm["means3D"], requires_grad=True)  # like render_4 (:356)
+    settings = GaussianRasterizationSettings(H, W, cam.tanfovx, cam.tanfovy, d["bg"], 1.0, d["viewmatrix"],
+                                             d["projmatrix"], sc.sh_degree, d["campos"], False, False)
+    rast = GaussianRasterizer(settings)
+    depth, color, radii, objects, is_used = rast(means3D=prm["means3D"], means2D=means2D, opacities=prm["opacities"],
+                                                 shs=prm["shs"], sh_objs=prm["sh_objs"], scales=prm["scales"],
+                                                 rotations=prm["rotations"])
+    gd, gc, go = [torch.from_numpy(g).cuda() for g in grads]
+    ((depth * gd).sum() + (color * gc).sum() + (objects * go).sum()).backward()
+    mine = h.run_mine(sc, cam, grads)
+    assert (radii == mine["radii"]).all() and (is_used == mine["is_used"]).all()
+    assert torch.equal(color, mine["color"]) and torch.equal(depth, mine["depth"]) and torch.equal(objects, mine["objects"])
+    pairs = (("means3D", "dL_dmeans3D"), ("shs", "dL_dsh"), ("sh_objs", "dL_dobjects"), ("opacities", "dL_dopacity"),
+             ("scales", "dL_dscales"), ("rotations", "dL_drotations"))
+    for k, gk in pairs:
+        assert prm[k].grad.shape == prm[k].shape
+        assert h.grad_rel_err(prm[k].grad.reshape(mine[gk].shape), mine[gk]) < 1e-5, k
+    assert h.grad_rel_err(means2D.grad, mine["dL_dmeans2D"]) < 1e-5
+    vis = rast.markVisible(d["means3D"])
+    assert vis.dtype == torch.bool and int(vis.sum()) >= int((radii > 0).sum())
+    assert distCUDA2(d["means3D"]).shape == (P,)
+    with pytest.raises(Exception, match="excatly one of either SHs"):
+        rast(means3D=prm["means3D"], means2D=means2D, opacities=prm["opacities"], sh_objs=prm["sh_objs"],
+             scales=prm["scales"], rotations=prm["rotations"])
+    with pytest.raises(Exception, match="scale/rotation pair"):
+        rast(means3D=prm["means3D"], means2D=means2D, opacities=prm["opacities"], shs=prm["shs"],
+             sh_objs=prm["sh_objs"], scales=prm["scales"])
