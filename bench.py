@@ -120,13 +120,14 @@ def stage_model(args, stats):
     stats: P, Pvis, R, Npix, n_eval_fwd, n_blend, n_eval_bwd."""
     P, Pv, R, N = stats["P"], stats["Pvis"], stats["R"], stats["Npix"]
     M, F = (args.deg + 1) ** 2, args.F
-    tile_passes = 2 if ((args.width + 15) // 16) * ((args.height + 15) // 16) > 256 else 1
+    L1 = stats["l1_total"]
     return {
         "preprocess": ("hbm", Pv * (44 + 12 * M + 84) + (P - Pv) * 20),
-        # 4 depth passes over P 8-byte items (hist read + scatter read + write) + count/scan of tiles_touched
-        "depth_sort_count": ("hbm", P * (4 * 24 + 12)),
-        # emission (20 B/Gaussian + 8 B/instance) + tile passes (24 B/instance each) + ranges/point list (12 B/instance)
-        "emit_tile_sort_ranges": ("hbm", P * 20 + R * (8 + 24 * tile_passes + 12)),
+        # 4 depth passes over P 8-byte items (histogram read + scatter read + write) + coverage grids (8 B/Gaussian)
+        "depth_sort_offsets": ("hbm", P * (4 * 24 + 8)),
+        # supertile lists: 2 sweeps over (depth key 8 + tiles_touched 4 + rect 4) B/Gaussian, 8 B/entry written;
+        # tile pull: 8 B/entry read (once from HBM, S*S/8 times from L2), 4 B/instance written
+        "binning": ("hbm", P * 32 + L1 * 16 + R * 4),
         "render_fwd": ("fp32", 13 * stats["n_eval_fwd"] + (15 + 2 * (3 + F)) * stats["n_blend"]),
         "render_bwd": ("fp32", 13 * stats["n_eval_bwd"] + (100 + 7 * (3 + F)) * stats["n_blend"]),
         "preprocess_bwd": ("hbm", Pv * ((95 + 12 * M) + (64 + 12 * M)) + (P - Pv) * 4),
@@ -181,11 +182,12 @@ def run_mine(args, rank, world, local_rank):
     sync_all()
     # workload statistics for the roofline model (outside the timed region)
     R = res[0]
+    l1_total = capi.last_forward_stats()["l1_total"]
     st = capi.export_state(P, deg, M, F, W, H, R, res[6], res[7], res[8])
     cp = capi.count_pairs(P, deg, M, F, W, H, R, res[6], res[7], res[8])
     stats = dict(P=P, Pvis=int((res[4] > 0).sum()), R=int(R), Npix=W * H, n_eval_fwd=cp["evaluated"],
                  n_blend=cp["blended"], n_eval_bwd=int(st["n_contrib"].to(torch.int64).sum()),
-                 warp_blended=cp["warp_blended"])
+                 warp_blended=cp["warp_blended"], l1_total=l1_total)
     del st
 
     # ---- timed region 1: inputs resident in HBM ----
@@ -392,7 +394,7 @@ def main():
                            parallelism="view-data-parallel x%d, replicated Gaussians, 1 all-reduce of %d MB/step" % (
                                world, r["bucket_bytes"] // 1000000) if world > 1 else "single GPU",
                            l2="inputs (>=300 MB of Gaussian parameters) larger than the 126 MB L2; no flush needed",
-                           **{k: r["stats"][k] for k in ("Pvis", "R", "n_eval_fwd", "n_blend", "n_eval_bwd")}),
+                           **{k: r["stats"][k] for k in ("Pvis", "R", "l1_total", "n_eval_fwd", "n_blend", "warp_blended", "n_eval_bwd")}),
                gpu_launches=r["launches"], clocks=r["clocks"], roofline=roof, stages=stages)
     if r["e2e"]:
         e = r["e2e"]

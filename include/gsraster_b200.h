@@ -110,8 +110,9 @@ size_t gsr_binning_bytes(int64_t num_rendered);
  * backward call brackets each stage with CUDA events on params->stream. gsr_get_stage_times
  * synchronises those events, ADDS the elapsed milliseconds since the last call of
  * gsr_get_stage_times into ms[GSR_NUM_STAGES] (caller zero-initialises) and forgets them.
- * Stages: 0 preprocess (K1), 1 depth sort + tile count/scan, 2 emission + tile sort + ranges,
- * 3 forward blend (K4), 4 backward blend (K5), 5 backward preprocess (K6+K7). No reference
+ * Stages: 0 preprocess (K1), 1 depth sort + coverage grids + tile offsets/ranges, 2 binning
+ * (supertile lists + per-tile pull into the point list), 3 forward blend (K4), 4 backward blend
+ * (K5), 5 backward preprocess (K6+K7). No reference
  * equivalent (the reference has no timers). */
 #define GSR_NUM_STAGES 6
 int gsr_set_stage_timing(int enable);
@@ -124,6 +125,10 @@ int gsr_get_stage_times(float* ms);
  * pairs with at least one blended lane, counts[3] = staged tile instances. Synchronises. */
 int gsr_count_pairs(const gsr_params* params, int num_rendered, const char* geom_buffer,
                     const char* binning_buffer, const char* image_buffer, unsigned long long* counts);
+
+/* Sizes seen by the last gsr_forward on this thread: out[0] = num_rendered R, out[1] = total length
+ * of the supertile lists (binning intermediate). For bench.py's algorithmic-bytes model. */
+int gsr_last_forward_stats(unsigned long long* out);
 
 /* Kernel launches issued by the last forward/backward/knn call on this thread (for bench.py). */
 int gsr_last_launch_count(void);

@@ -444,14 +444,17 @@ __global__ void export_gauss_kernel(int P, const float4* __restrict__ rec, const
   if (i >= P) return;
   uint32_t t = tt[i];
   if (tiles_touched) tiles_touched[i] = t;
-  float4 r0 = make_float4(0, 0, 0, 0), r1 = r0, r2 = r0;
+  float4 r0 = make_float4(0, 0, 0, 0), r1 = r0, r2 = r0, r3 = r0;
   uint8_t cb = 0;
-  if (t) { r0 = rec[3 * (size_t)i]; r1 = rec[3 * (size_t)i + 1]; r2 = rec[3 * (size_t)i + 2]; cb = clampedb[i]; }
+  if (t) {
+    r0 = rec[REC4 * (size_t)i]; r1 = rec[REC4 * (size_t)i + 1]; r2 = rec[REC4 * (size_t)i + 2];
+    r3 = rec[REC4 * (size_t)i + 3]; cb = clampedb[i];
+  }
   if (depths) depths[i] = r2.x;
   if (means2D) { means2D[2 * i] = r0.x; means2D[2 * i + 1] = r0.y; }
   if (conic_opacity) {
     float* c = conic_opacity + 6 * (size_t)i;
-    c[0] = r0.z; c[1] = r0.w; c[2] = r1.x; c[3] = r1.y; c[4] = r1.z; c[5] = r1.w;
+    c[0] = r0.z; c[1] = r0.w; c[2] = r1.x; c[3] = r1.y; c[4] = r3.x; c[5] = r3.y;
   }
   if (rgb) { rgb[3 * i] = r2.y; rgb[3 * i + 1] = r2.z; rgb[3 * i + 2] = r2.w; }
   if (clamped) { clamped[3 * i] = cb & 1; clamped[3 * i + 1] = (cb >> 1) & 1; clamped[3 * i + 2] = (cb >> 2) & 1; }
@@ -463,7 +466,7 @@ __global__ void export_keys_kernel(int T, const uint2* __restrict__ ranges, cons
   if (tile >= T) return;
   uint2 r = ranges[tile];
   for (uint32_t i = r.x + threadIdx.x; i < r.y; i += blockDim.x)
-    keys[i] = ((uint64_t)tile << 32) | __float_as_uint(rec[3 * (size_t)point_list[i] + 2].x);
+    keys[i] = ((uint64_t)tile << 32) | __float_as_uint(rec[REC4 * (size_t)point_list[i] + 2].x);
 }
 // needs ranges -> declared here, called from capi.cu with the image state
 void launch_export_keys(int T, const uint2* ranges, const uint32_t* point_list, const float4* rec, uint64_t* keys,

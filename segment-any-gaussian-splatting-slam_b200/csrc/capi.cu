@@ -19,6 +19,7 @@ void launch_export_keys(int T, const uint2* ranges, const uint32_t* point_list, 
 namespace {
 thread_local std::string g_err;
 thread_local int g_launches = 0;
+thread_local unsigned long long g_last_stats[2] = {0, 0};
 thread_local int* g_pinned = nullptr;  // 8 ints of pinned host memory for the num_rendered read-back
 
 // ---- optional per-stage event timing (gsr_set_stage_timing) ----
@@ -177,6 +178,8 @@ int gsr_forward(const gsr_params* p, gsr_alloc_fn geom_alloc, void* geom_ctx, gs
   if (R > 0x7fffffffLL) return fail(GSR_ERR_UNSUPPORTED, "num_rendered exceeds int32");
   if (l1_total > 0xffffffffull) return fail(GSR_ERR_UNSUPPORTED, "supertile list length exceeds uint32");
   if (num_rendered) *num_rendered = (int)R;
+  g_last_stats[0] = (unsigned long long)R;
+  g_last_stats[1] = l1_total;
 
   const size_t nw_ns = (size_t)((P + 31) / 32) * gsr::super_grid(cam.gx, cam.gy).NS;
   gsr::BinState b;
@@ -249,6 +252,12 @@ int gsr_backward(const gsr_params* p, int num_rendered, const float* background,
   return GSR_OK;
 }
 
+int gsr_last_forward_stats(unsigned long long* out) {
+  if (!out) return fail(GSR_ERR_INVALID_ARGUMENT, "out is NULL");
+  out[0] = g_last_stats[0];
+  out[1] = g_last_stats[1];
+  return GSR_OK;
+}
 int gsr_set_stage_timing(int enable) {
   g_timing = enable != 0;
   return GSR_OK;

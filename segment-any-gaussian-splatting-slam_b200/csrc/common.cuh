@@ -13,8 +13,10 @@ constexpr int TILE_X = 16, TILE_Y = 16;  // fixed by parity: reference config.h:
 // roles (geometry / binning / image) but the contents are ours:
 //
 // geometry (per Gaussian):
-//   rec           3 x float4 = 48 B   {px, py, conic.a, conic.b} {conic.c, opacity, cov_zx, cov_yz}
-//                                      {depth, r, g, b}   -- the record the blend kernels stage by TMA
+//   rec           4 x float4 = 64 B   {px, py, conic.a, conic.b} {conic.c, opacity, hx, hy}
+//                                      {depth, r, g, b} {cov_zx, cov_yz, 0, 0} -- the record the blend kernels
+//                                      stage by TMA; (hx, hy) = half extents of the axis-aligned box around the
+//                                      alpha >= 1/255 ellipse (conservative), negative if opacity can never reach it
 //   tiles_touched u32, rect u32 (x0 | y0<<8 | x1<<16 | y1<<24), clamped u8 (bit c = channel c clamped)
 //   dkeys_a/b     u64 = depth_bits<<32 | idx   (ping-pong of the depth radix sort)
 //   sort scratch  u32[256 * nblk(P)] + u32[256]; scan scratch u32[nblk256(P) + 8]
@@ -24,6 +26,7 @@ constexpr int TILE_X = 16, TILE_Y = 16;  // fixed by parity: reference config.h:
 // binning: point_list u32[R] (FIRST: all the backward pass needs), L1 supertile lists uint2[L1]
 //   {packed rect, Gaussian idx}, per-(supertile, warp) counters u32[NS * ceil(P/32)]
 // ---------------------------------------------------------------------------------------------
+constexpr int REC4 = 4;  // float4 per Gaussian record
 constexpr int SORT_THREADS = 256;
 constexpr int SORT_IPT = 16;                           // items per thread
 constexpr int SORT_TILE = SORT_THREADS * SORT_IPT;     // 4096 items per block
@@ -85,7 +88,7 @@ inline int grad_row_floats(int F) { return F <= 16 ? 32 : 64; }
 
 inline size_t geom_from_chunk(char* chunk, size_t P, GeomState& g, int F = 32) {
   char* p = chunk;
-  carve(p, g.rec, 3 * P);
+  carve(p, g.rec, REC4 * P);
   carve(p, g.tiles_touched, P);
   carve(p, g.rect, P);
   carve(p, g.clamped, P);

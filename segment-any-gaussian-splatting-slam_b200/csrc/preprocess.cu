@@ -130,9 +130,22 @@ preprocess_kernel(const FwdInputs in, const Cam cam, float4* __restrict__ rec, u
       rgb[2] = in.colors_precomp[3 * (size_t)idx + 2];
     }
     clamped[idx] = (uint8_t)cbits;
-    rec[3 * (size_t)idx + 0] = make_float4(point_image.x, point_image.y, conic.x, conic.y);
-    rec[3 * (size_t)idx + 1] = make_float4(conic.z, in.opacities[idx], czx, cyz);
-    rec[3 * (size_t)idx + 2] = make_float4(p_view.z, rgb[0], rgb[1], rgb[2]);
+    // Conservative screen-space box of the region where alpha = o * exp(power) can reach 1/255
+    // (the blend's cut-off, forward.cu:371-373): power >= -tau/2 with tau = 2 ln(255 o) bounds |dx| by
+    // sqrt(tau * cov_xx), |dy| by sqrt(tau * cov_yy). Margins (0.01 on tau, 0.1 % + 0.01 px on the extents) cover
+    // the float rounding of the blend's own power / exp evaluation, so skipping outside the box never changes a
+    // result. Opacities that can never reach 1/255 get a negative box.
+    const float opac = in.opacities[idx];
+    const float tau = 2.0f * logf(255.0f * opac) + 0.01f;
+    float hx = -1.f, hy = -1.f;
+    if (tau > 0.f) {
+      hx = sqrtf(tau * cxx) * 1.001f + 0.01f;
+      hy = sqrtf(tau * cyy) * 1.001f + 0.01f;
+    }
+    rec[REC4 * (size_t)idx + 0] = make_float4(point_image.x, point_image.y, conic.x, conic.y);
+    rec[REC4 * (size_t)idx + 1] = make_float4(conic.z, opac, hx, hy);
+    rec[REC4 * (size_t)idx + 2] = make_float4(p_view.z, rgb[0], rgb[1], rgb[2]);
+    rec[REC4 * (size_t)idx + 3] = make_float4(czx, cyz, 0.f, 0.f);
     my_radius_i = (int)my_radius;
     touched = (uint32_t)((y1 - y0) * (x1 - x0));
     rect[idx] = (uint32_t)x0 | ((uint32_t)y0 << 8) | ((uint32_t)x1 << 16) | ((uint32_t)y1 << 24);

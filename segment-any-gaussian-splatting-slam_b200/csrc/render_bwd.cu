@@ -25,13 +25,14 @@
 
 namespace gsr {
 
-constexpr int BB = 128;  // instances per staged batch
+// instances per staged batch (static shared memory stays below 48 KB at F = 32)
+template <int F> __host__ __device__ constexpr int batch_size() { return F == 16 ? 128 : 64; }
 
 template <int F>
 struct BwdSmem {
-  float4 rec[2][BB][3];
-  float4 feat[2][BB][F / 4];
-  uint32_t id[2][BB];
+  float4 rec[2][batch_size<F>()][REC4];
+  float4 feat[2][batch_size<F>()][F / 4];
+  uint32_t id[2][batch_size<F>()];
   uint64_t bar[2];
   uint32_t max_contrib;
 };
@@ -81,6 +82,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   const float* __restrict__ dL_dpix, const float* __restrict__ dL_dpix_obj,
                   float* __restrict__ grad_rows) {
   constexpr int ROW = (F == 16) ? 32 : 64;
+  constexpr int BB = batch_size<F>();
   __shared__ __align__(128) BwdSmem<F> sm;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int px = blockIdx.x * TILE_X + (warp & 1) * 8 + (lane & 7);
@@ -110,7 +112,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   const int nbatch = (todo + BB - 1) / BB;
   const uint32_t list_end = range.x + (uint32_t)todo;  // exclusive
 
-  constexpr uint32_t ROW_BYTES = 48 + 4 * F;
+  constexpr uint32_t ROW_BYTES = 16 * REC4 + 4 * F;
   auto issue = [&](int b) {
     const int st = b & 1;
     const int cnt = min(BB, todo - b * BB);
@@ -118,7 +120,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     if (tid < cnt) {
       const uint32_t id = point_list[list_end - 1 - (uint32_t)(b * BB + tid)];
       sm.id[st][tid] = id;
-      tma_load_1d(&sm.rec[st][tid][0], rec + 3 * (size_t)id, 48, &sm.bar[st]);
+      tma_load_1d(&sm.rec[st][tid][0], rec + REC4 * (size_t)id, 16 * REC4, &sm.bar[st]);
       tma_load_1d(&sm.feat[st][tid][0], feats + (size_t)id * F, 4 * F, &sm.bar[st]);
     }
   };
@@ -149,10 +151,13 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     for (int j = 0; j < cnt; j++) {
       const uint32_t pos = (uint32_t)(todo - 1 - (b * BB + j));  // 0-based position in the tile's list
       const float4 r0 = sm.rec[st][j][0];  // px, py, conic a, conic b
-      const float4 r1 = sm.rec[st][j][1];  // conic c, opacity, cov_zx, cov_yz
+      const float4 r1 = sm.rec[st][j][1];  // conic c, opacity, box half extents hx, hy
       const float dx = r0.x - pixx, dy = r0.y - pixy;
+      // conservative alpha >= 1/255 box (preprocess.cu): outside it the pair was skipped by the forward pass
+      const bool inbox = pos < last_contributor && fabsf(dx) <= r1.z && fabsf(dy) <= r1.w;
+      if (!__any_sync(FULL, inbox)) continue;
       const float power = -0.5f * (r0.z * dx * dx + r1.x * dy * dy) - r0.w * dx * dy;
-      const bool cand = pos < last_contributor && power <= 0.0f;
+      const bool cand = inbox && power <= 0.0f;
       if (!__any_sync(FULL, cand)) continue;
       float G = expf(power);
       float alpha = min(0.99f, r1.y * G);
@@ -167,7 +172,8 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       const float inv1ma = rcp_approx(1.f - alpha);
       T = T * inv1ma;
       const float w = alpha * T;  // d(out channel) / d(channel value of this Gaussian)
-      const float a = r0.z, bq = r0.w, c = r1.x, covzx = r1.z, covyz = r1.w;
+      const float4 r3 = sm.rec[st][j][3];  // cov_zx, cov_yz
+      const float a = r0.z, bq = r0.w, c = r1.x, covzx = r3.x, covyz = r3.y;
       const float cza = covzx * a + covyz * bq;
       const float czb = covzx * bq + covyz * c;
       const float depth = r2.x - cza * dx - czb * dy;

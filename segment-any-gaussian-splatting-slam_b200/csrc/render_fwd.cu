@@ -11,12 +11,13 @@
 
 namespace gsr {
 
-constexpr int RB = 128;  // instances per staged batch
+// instances per staged batch (static shared memory stays below 48 KB at F = 32)
+template <int F> __host__ __device__ constexpr int batch_size() { return F == 16 ? 128 : 64; }
 
 template <int F>
 struct FwdSmem {
-  float4 rec[2][RB][3];
-  float4 feat[2][RB][F / 4];
+  float4 rec[2][batch_size<F>()][REC4];
+  float4 feat[2][batch_size<F>()][F / 4];
   uint64_t bar[2];
 };
 
@@ -26,6 +27,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   const float4* __restrict__ rec, const float* __restrict__ feats, int W, int H,
                   const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                   float* __restrict__ out_depth, float* __restrict__ out_color, float* __restrict__ out_objects) {
+  constexpr int RB = batch_size<F>();
   __shared__ __align__(128) FwdSmem<F> sm;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int px = blockIdx.x * TILE_X + (warp & 1) * 8 + (lane & 7);
@@ -43,14 +45,14 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   }
   __syncthreads();
 
-  constexpr uint32_t ROW_BYTES = 48 + 4 * F;
+  constexpr uint32_t ROW_BYTES = 16 * REC4 + 4 * F;
   auto issue = [&](int b) {
     const int st = b & 1;
     const int cnt = min(RB, todo - b * RB);
     if (tid == 0) mbar_arrive_expect_tx(&sm.bar[st], (uint32_t)cnt * ROW_BYTES);
     if (tid < cnt) {
       const uint32_t id = point_list[range.x + b * RB + tid];
-      tma_load_1d(&sm.rec[st][tid][0], rec + 3 * (size_t)id, 48, &sm.bar[st]);
+      tma_load_1d(&sm.rec[st][tid][0], rec + REC4 * (size_t)id, 16 * REC4, &sm.bar[st]);
       tma_load_1d(&sm.feat[st][tid][0], feats + (size_t)id * F, 4 * F, &sm.bar[st]);
     }
   };
@@ -72,12 +74,15 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     if (!__all_sync(0xffffffffu, done)) {
       const float4* rp = &sm.rec[st][0][0];
       const float4* fp = &sm.feat[st][0][0];
-      for (int j = 0; j < cnt; j++, rp += 3, fp += F / 4) {
+      for (int j = 0; j < cnt; j++, rp += REC4, fp += F / 4) {
         const float4 r0 = rp[0];  // px, py, conic a, conic b
-        const float4 r1 = rp[1];  // conic c, opacity, cov_zx, cov_yz
+        const float4 r1 = rp[1];  // conic c, opacity, box half extents hx, hy
         const float dx = r0.x - pixx, dy = r0.y - pixy;
+        // outside the conservative alpha >= 1/255 box (preprocess.cu) the pixel would fail forward.cu:372
+        const bool inbox = !done && fabsf(dx) <= r1.z && fabsf(dy) <= r1.w;
+        if (!__any_sync(0xffffffffu, inbox)) continue;
         const float power = -0.5f * (r0.z * dx * dx + r1.x * dy * dy) - r0.w * dx * dy;
-        const bool cand = !done && power <= 0.0f;                  // forward.cu:365-366
+        const bool cand = inbox && power <= 0.0f;                  // forward.cu:365-366
         if (!__any_sync(0xffffffffu, cand)) continue;
         // T, alpha and the two thresholds use exactly the reference's operations (n_contrib and
         // final_T are bit-exact); lanes that are not candidates compute values that are masked out.
@@ -101,7 +106,8 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
             O[4 * q + 2] = fmaf(f4.z, w, O[4 * q + 2]);
             O[4 * q + 3] = fmaf(f4.w, w, O[4 * q + 3]);
           }
-          const float covzx = r1.z, covyz = r1.w;
+          const float4 r3 = rp[3];  // cov_zx, cov_yz
+          const float covzx = r3.x, covyz = r3.y;
           const float depth_c = r2.x - (covzx * r0.z + covyz * r0.w) * dx - (covzx * r0.w + covyz * r1.x) * dy;
           D = fmaf(depth_c, w, D);
           T = hit ? test_T : T;
@@ -149,7 +155,7 @@ count_pairs_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict_
   for (uint32_t i = range.x; i < range.y; i++) {
     if (__all_sync(0xffffffffu, done)) break;
     const uint32_t id = point_list[i];
-    const float4 r0 = rec[3 * (size_t)id], r1 = rec[3 * (size_t)id + 1];
+    const float4 r0 = rec[REC4 * (size_t)id], r1 = rec[REC4 * (size_t)id + 1];
     bool hit = false;
     if (!done) {
       n_eval++;

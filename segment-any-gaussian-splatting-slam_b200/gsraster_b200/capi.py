@@ -46,6 +46,7 @@ def lib():
         L.gsr_export_state.argtypes = [C.POINTER(Params), C.c_int] + [C.c_void_p] * 14
         L.gsr_count_pairs.argtypes = [C.POINTER(Params), C.c_int] + [C.c_void_p] * 3 + [C.POINTER(C.c_ulonglong)]
         L.gsr_get_stage_times.argtypes = [C.POINTER(C.c_float)]
+        L.gsr_last_forward_stats.argtypes = [C.POINTER(C.c_ulonglong)]
         L.gsr_set_stage_timing.argtypes = [C.c_int]
         _lib = L
     return _lib
@@ -216,7 +217,14 @@ def export_state(P, D, M, F, W, H, R, geomBuffer, binningBuffer, imageBuffer):
     return st
 
 
-STAGES = ("preprocess", "depth_sort_count", "emit_tile_sort_ranges", "render_fwd", "render_bwd", "preprocess_bwd")
+STAGES = ("preprocess", "depth_sort_offsets", "binning", "render_fwd", "render_bwd", "preprocess_bwd")
+
+
+def last_forward_stats():
+    """-> dict(R, l1_total) of the last forward call on this thread."""
+    c = (C.c_ulonglong * 2)()
+    _check(lib().gsr_last_forward_stats(c))
+    return dict(R=int(c[0]), l1_total=int(c[1]))
 
 
 def set_stage_timing(enable):

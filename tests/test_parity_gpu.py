@@ -34,13 +34,17 @@ def _check_images(mine, ref):
         assert err <= IMG_TOL, (k, err)
 
 
-def _check_grads(mine, ref, tol=GRAD_TOL):
+def _check_grads(mine, ref, tol=GRAD_TOL, ref_again=None):
+    """ref_again: a second run of the reference on the same inputs. Its float atomics make the reference's
+    own gradients differ run to run (measured on B200: up to 3.3e-4 on dL_dcov3D for screen-filling splats,
+    tests/gpu_gradnoise.py; the product's spread is ~5e-6), so the bar is 1e-3 plus 3x that spread."""
     for k in h.GRAD_KEYS:
         a, b = h.npy(mine[k]), h.npy(ref[k])
         if a.size == 0 and b.size == 0:
             continue
         err = h.grad_rel_err(a.reshape(b.shape), b)
-        assert err <= tol, (k, err)
+        t = tol + (3.0 * h.grad_rel_err(ref_again[k], ref[k]) if ref_again is not None else 0.0)
+        assert err <= t, (k, err, t)
 
 
 def _golden_cases():
@@ -94,7 +98,7 @@ def test_product_vs_reference_live(P, W, H, deg, view, mul):
     assert mine["R"] == ref["R"] and ref["R"] > 0
     _check_exact(mine, ref)
     _check_images(mine, ref)
-    _check_grads(mine, ref)
+    _check_grads(mine, ref, ref_again=h.run_ref(sc, cam, grads))
 
 
 @pytest.mark.skipif(not h.have_ref(32), reason="oracle/_ref F=32 build not shipped")
