@@ -6,7 +6,7 @@ argument order, same outputs, so `render_4` (gaussian_renderer/__init__.py:325-4
     GaussianRasterizer(settings)    .forward(...) -> (depth, color, radii, objects, is_used), .markVisible(positions)
     rasterize_gaussians(...)        autograd entry point            (reference :21-44)
 
-Underneath sits gsraster_b200.capi -> lib/libgsraster_b200.so (hand-written sm_100a CUDA behind the C ABI of
+Underneath sits the LibTorch binding lib/gsraster_b200_torch.so (or gsraster_b200.capi) -> lib/libgsraster_b200.so (hand-written sm_100a CUDA behind the C ABI of
 include/gsraster_b200.h). There is no CPU fallback: CPU tensors or a missing library raise.
 """
 from typing import NamedTuple
@@ -14,7 +14,14 @@ from typing import NamedTuple
 import torch
 import torch.nn as nn
 
-from gsraster_b200 import capi as _C
+from gsraster_b200 import torch_ext as _torch_ext
+
+# `_C` is the C++/LibTorch binding (csrc/torch_binding.cpp), like the reference's pybind `_C`; the ctypes binding
+# gsraster_b200.capi has the same functions and is used when the LibTorch shim has not been built.
+if _torch_ext.available():
+    _C = _torch_ext.load()
+else:
+    from gsraster_b200 import capi as _C
 
 
 def rasterize_gaussians(means3D, means2D, sh, sh_objs, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,

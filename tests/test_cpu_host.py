@@ -161,3 +161,13 @@ def test_dropin_modules_import_and_validate_like_the_reference():
     with pytest.raises(RuntimeError):  # CPU tensors: no CPU fallback
         r(means3D=m, means2D=m, opacities=torch.zeros(4, 1), shs=torch.zeros(4, 1, 3), sh_objs=torch.zeros(4, 1, 16),
           scales=m, rotations=torch.zeros(4, 4))
+
+
+def test_libtorch_binding_loads_with_reference_names():
+    from gsraster_b200 import torch_ext
+    assert torch_ext.available(), "run __graft_entry__.build()"
+    m = torch_ext.load()
+    for n in ("rasterize_gaussians", "rasterize_gaussians_backward", "mark_visible", "distCUDA2"):
+        assert hasattr(m, n), n
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        m.mark_visible(torch.zeros(4, 3), torch.eye(4), torch.eye(4))
