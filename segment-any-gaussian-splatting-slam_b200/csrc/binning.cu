@@ -312,13 +312,18 @@ __device__ __forceinline__ uint32_t super_rect(uint32_t rc, int shift) {
 // is point (x, y) (packed x | y<<8 | x<<16 | y<<24) inside rect? bytes 0,1: lo <= p ; bytes 2,3: !(hi <= p)
 __device__ __forceinline__ bool rect_has(uint32_t rc, uint32_t pxy) { return __vcmpleu4(rc, pxy) == 0x0000FFFFu; }
 
-// WRITE = false: per-(supertile, warp) counts; WRITE = true: ranked writes of {rect, idx}
+// Supertile lists. One block = 256 consecutive depth ranks = 8 warps. For every supertile s the
+// ballot of "rect overlaps s" ranks the lanes of a warp; per-warp popcounts go to shared memory,
+// an 8-way prefix orders the warps, and a scan over per-(supertile, block) counters (l1_scan_kernel)
+// orders the blocks. WRITE = false produces the block counters, WRITE = true the ranked writes.
+constexpr int L1_WARPS = 8;
 template <bool WRITE>
 __global__ void __launch_bounds__(256)
 l1_kernel(int P, SuperGrid sg, int shift, const uint64_t* __restrict__ dkeys, const uint32_t* __restrict__ tiles_touched,
-          const uint32_t* __restrict__ rect, uint32_t* __restrict__ warp_cnt, int NW, uint2* __restrict__ l1) {
+          const uint32_t* __restrict__ rect, uint32_t* __restrict__ blk_cnt, int NB, uint2* __restrict__ l1) {
+  __shared__ uint32_t cnt[L1_WARPS][256];  // [warp][supertile]; NS <= 256
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
-  const int lane = threadIdx.x & 31, w = k >> 5;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   uint32_t idx = 0, rc = 0, src = 0;
   bool vis = false;
   if (k < P) {
@@ -326,26 +331,42 @@ l1_kernel(int P, SuperGrid sg, int shift, const uint64_t* __restrict__ dkeys, co
     vis = tiles_touched[idx] != 0;
     if (vis) { rc = rect[idx]; src = super_rect(rc, shift); }
   }
-  if (!__any_sync(0xffffffffu, vis)) {
-    if (!WRITE && w < NW) for (int s = lane; s < sg.NS; s += 32) warp_cnt[(size_t)s * NW + w] = 0;
-    return;
+  const bool warp_vis = __any_sync(0xffffffffu, vis);
+  if (!warp_vis) {
+    for (int s = lane; s < sg.NS; s += 32) cnt[w][s] = 0;
+  } else {
+    for (int sy = 0, s = 0; sy < sg.sgy; sy++)
+      for (int sx = 0; sx < sg.sgx; sx++, s++) {
+        const uint32_t pxy = (uint32_t)sx | ((uint32_t)sy << 8);
+        const unsigned m = __ballot_sync(0xffffffffu, vis && rect_has(src, pxy | (pxy << 16)));
+        if (lane == 0) cnt[w][s] = __popc(m);
+      }
   }
-  for (int sy = 0; sy < sg.sgy; sy++) {
-    for (int sx = 0; sx < sg.sgx; sx++) {
+  __syncthreads();
+  if (threadIdx.x < sg.NS) {  // exclusive prefix over the 8 warps (+ block offset when writing)
+    const int s = threadIdx.x;
+    uint32_t run = WRITE ? blk_cnt[(size_t)s * NB + blockIdx.x] : 0u;
+#pragma unroll
+    for (int q = 0; q < L1_WARPS; q++) {
+      const uint32_t c = cnt[q][s];
+      cnt[q][s] = run;
+      run += c;
+    }
+    if (!WRITE) blk_cnt[(size_t)s * NB + blockIdx.x] = run;
+  }
+  if (!WRITE) return;
+  __syncthreads();
+  if (!warp_vis) return;
+  for (int sy = 0, s = 0; sy < sg.sgy; sy++)
+    for (int sx = 0; sx < sg.sgx; sx++, s++) {
       const uint32_t pxy = (uint32_t)sx | ((uint32_t)sy << 8);
       const bool in = vis && rect_has(src, pxy | (pxy << 16));
       const unsigned m = __ballot_sync(0xffffffffu, in);
-      const int s = sy * sg.sgx + sx;
-      if (!WRITE) {
-        if (lane == 0) warp_cnt[(size_t)s * NW + w] = __popc(m);
-      } else if (in) {
-        l1[warp_cnt[(size_t)s * NW + w] + __popc(m & ((1u << lane) - 1))] = make_uint2(rc, idx);
-      }
+      if (in) l1[cnt[w][s] + __popc(m & ((1u << lane) - 1))] = make_uint2(rc, idx);
     }
-  }
 }
 
-// one block per supertile: exclusive scan of its row of warp counters, offset by the list base
+// one block per supertile: exclusive scan of its row of block counters, offset by the list base
 __global__ void __launch_bounds__(256)
 l1_scan_kernel(uint32_t* __restrict__ warp_cnt, int NW, const uint32_t* __restrict__ l1_off) {
   __shared__ uint32_t warp_sums[8];
@@ -427,10 +448,10 @@ void launch_binning(int P, int64_t R, const Cam& cam, GeomState& g, BinState& b,
   if (R <= 0) return;
   const SuperGrid sg = super_grid(cam.gx, cam.gy);
   const int shift = sg.S == 8 ? 3 : 4;
-  const int NW = (P + 31) / 32, nb = (P + 255) / 256;
-  l1_kernel<false><<<nb, 256, 0, s>>>(P, sg, shift, g.dkeys_a, g.tiles_touched, g.rect, b.warp_cnt, NW, b.l1);
-  l1_scan_kernel<<<sg.NS, 256, 0, s>>>(b.warp_cnt, NW, img.l1_off);
-  l1_kernel<true><<<nb, 256, 0, s>>>(P, sg, shift, g.dkeys_a, g.tiles_touched, g.rect, b.warp_cnt, NW, b.l1);
+  const int nb = (P + 255) / 256;
+  l1_kernel<false><<<nb, 256, 0, s>>>(P, sg, shift, g.dkeys_a, g.tiles_touched, g.rect, b.warp_cnt, nb, b.l1);
+  l1_scan_kernel<<<sg.NS, 256, 0, s>>>(b.warp_cnt, nb, img.l1_off);
+  l1_kernel<true><<<nb, 256, 0, s>>>(P, sg, shift, g.dkeys_a, g.tiles_touched, g.rect, b.warp_cnt, nb, b.l1);
   tile_pull_kernel<<<sg.NS * (sg.S * sg.S / 8), 256, 0, s>>>(cam.gx, cam.gy, sg, b.l1, img.l1_off, img.tile_off,
                                                            b.point_list);
   launches += 4;

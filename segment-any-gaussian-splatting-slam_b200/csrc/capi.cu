@@ -71,6 +71,7 @@ int check_params(const gsr_params* p) {
   if ((p->width + 15) / 16 > 255 || (p->height + 15) / 16 > 255)
     return fail(GSR_ERR_UNSUPPORTED, "image larger than 4080x4080 tiles-per-axis limit");
   if (p->D < 0 || p->D > 3) return fail(GSR_ERR_INVALID_ARGUMENT, "SH degree must be 0..3");
+  if (p->M < 0 || p->M > 16) return fail(GSR_ERR_UNSUPPORTED, "M (SH coefficients per channel) must be <= 16");
   return GSR_OK;
 }
 gsr::Cam make_cam(const gsr_params* p, const float* view, const float* proj, const float* campos, const float* bg) {
@@ -181,7 +182,7 @@ int gsr_forward(const gsr_params* p, gsr_alloc_fn geom_alloc, void* geom_ctx, gs
   g_last_stats[0] = (unsigned long long)R;
   g_last_stats[1] = l1_total;
 
-  const size_t nw_ns = (size_t)((P + 31) / 32) * gsr::super_grid(cam.gx, cam.gy).NS;
+  const size_t nw_ns = (size_t)((P + 255) / 256) * gsr::super_grid(cam.gx, cam.gy).NS;  // per-(supertile, block) counters
   gsr::BinState b;
   char* bin_chunk = binning_alloc(binning_ctx, gsr::bin_from_chunk(nullptr, (size_t)R, (size_t)l1_total, nw_ns, b));
   if (!bin_chunk) return fail(GSR_ERR_ALLOC, "binning allocator returned NULL");

@@ -4,23 +4,51 @@
 // One pass: reads the packed gradient row written by K5, recomputes cov3D from scale/rotation
 // (no 24 B/Gaussian round trip), writes all eleven gradient tensors -- zeros for culled
 // Gaussians, so no pre-zeroing memset of 376 B/Gaussian (rasterize_points.cu:164-174) is needed.
+// Memory access: one thread per Gaussian computes, but every array-of-structs stream (SH in, the
+// ten gradient tensors out) goes through a shared-memory tile so that global loads/stores are
+// fully coalesced (a block's 128 Gaussians are one contiguous chunk of every (P, K) tensor).
 #include "common.cuh"
 #include "math.cuh"
 
 namespace gsr {
 
+constexpr int PB_THREADS = 128;
+constexpr int PB_TILE = PB_THREADS * 49;  // floats: SH rows of up to 48 floats at an odd stride
+
+// thread-private K values -> (P, K) row-major tensor, coalesced through the tile
+template <int K>
+__device__ __forceinline__ void stage_out(float* tile, float* __restrict__ gbase, const float (&vals)[K], int P) {
+#pragma unroll
+  for (int k = 0; k < K; k++) tile[threadIdx.x * K + k] = vals[k];
+  __syncthreads();
+  const int first = blockIdx.x * PB_THREADS;
+  const int n = min(PB_THREADS, P - first) * K;
+  float* dst = gbase + (size_t)first * K;
+  for (int i = threadIdx.x; i < n; i += PB_THREADS) dst[i] = tile[i];
+  __syncthreads();
+}
+
 template <int F>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(PB_THREADS)
 preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restrict__ tiles_touched,
                       const uint8_t* __restrict__ clampedb, const int* __restrict__ radii,
                       const float* __restrict__ grad_rows, const BwdOutputs out) {
   constexpr int ROW = (F == 16) ? 32 : 64;
   __shared__ CamS cs;
+  __shared__ float tile[PB_TILE];
   load_cam(cam, cs);
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= in.P) return;
+  const int first = blockIdx.x * PB_THREADS;
+  const int idx = first + threadIdx.x;
+  const bool valid = idx < in.P;
   const int M = in.M, D = in.D;
-  const bool visible = radii[idx] > 0;
+  const bool visible = valid && radii[idx] > 0;
+  const int SS = (3 * M) | 1;  // odd row stride -> conflict-free per-thread rows
+  if (in.shs != nullptr) {     // SH coefficients of the block's Gaussians: coalesced load, rows at stride SS
+    const int n = min(PB_THREADS, in.P - first) * 3 * M;
+    const float* src = in.shs + (size_t)first * 3 * M;
+    for (int i = threadIdx.x; i < n; i += PB_THREADS) tile[(i / (3 * M)) * SS + i % (3 * M)] = src[i];
+  }
+  __syncthreads();
 
   float g[12 + F];
 #pragma unroll
@@ -33,34 +61,25 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
       g[4 * q] = t.x; g[4 * q + 1] = t.y; g[4 * q + 2] = t.z; g[4 * q + 3] = t.w;
     }
   }
-  // unpacked per-Gaussian outputs of K5 (API tensors)
-  out.dL_dmean2D[3 * (size_t)idx] = g[0];
-  out.dL_dmean2D[3 * (size_t)idx + 1] = g[1];
-  out.dL_dmean2D[3 * (size_t)idx + 2] = 0.f;
-  {
-    float* c = out.dL_dconic + 6 * (size_t)idx;
-    c[0] = g[2]; c[1] = g[3]; c[2] = 0.f; c[3] = g[4]; c[4] = g[5]; c[5] = g[6];
-  }
-  out.dL_dopacity[idx] = g[7];
-  out.dL_ddepths[idx] = g[8];
-  out.dL_dcolor[3 * (size_t)idx] = g[9];
-  out.dL_dcolor[3 * (size_t)idx + 1] = g[10];
-  out.dL_dcolor[3 * (size_t)idx + 2] = g[11];
-  {
+  // scalar / float4 outputs of K5 are written directly (coalesced as they are)
+  if (valid) {
+    out.dL_dopacity[idx] = g[7];
+    out.dL_ddepths[idx] = g[8];
     float4* o = reinterpret_cast<float4*>(out.dL_dobjects + (size_t)idx * F);
 #pragma unroll
     for (int q = 0; q < F / 4; q++) o[q] = make_float4(g[12 + 4 * q], g[13 + 4 * q], g[14 + 4 * q], g[15 + 4 * q]);
   }
+  float basis[16];
+  float dRGB[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+  for (int k = 0; k < 16; k++) basis[k] = 0.f;
 
   float dmean[3] = {0.f, 0.f, 0.f};
   float dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   float dscale[3] = {0.f, 0.f, 0.f};
   float drot[4] = {0.f, 0.f, 0.f, 0.f};
 
-  if (!visible) {
-    if (out.dL_dsh)
-      for (int k = 0; k < 3 * M; k++) out.dL_dsh[(size_t)idx * 3 * M + k] = 0.f;
-  } else {
+  if (visible) {
     const float3 mean = {in.means3D[3 * idx], in.means3D[3 * idx + 1], in.means3D[3 * idx + 2]};
     float cov3D[6];
     float sx = 0, sy = 0, sz = 0;
@@ -153,13 +172,13 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
       const float3 dir_orig = {m.x - cs.campos[0], m.y - cs.campos[1], m.z - cs.campos[2]};
       const float len = sqrtf(dir_orig.x * dir_orig.x + dir_orig.y * dir_orig.y + dir_orig.z * dir_orig.z);
       const float x = dir_orig.x / len, y = dir_orig.y / len, z = dir_orig.z / len;
-      const float* sh = in.shs + (size_t)idx * M * 3;
-      float* dsh = out.dL_dsh + (size_t)idx * M * 3;
+      const float* sh = tile + threadIdx.x * SS;
       const uint8_t cb = clampedb[idx];
-      const float dRGB[3] = {g[9] * ((cb & 1) ? 0.f : 1.f), g[10] * ((cb & 2) ? 0.f : 1.f), g[11] * ((cb & 4) ? 0.f : 1.f)};
+      dRGB[0] = g[9] * ((cb & 1) ? 0.f : 1.f);
+      dRGB[1] = g[10] * ((cb & 2) ? 0.f : 1.f);
+      dRGB[2] = g[11] * ((cb & 4) ? 0.f : 1.f);
       float ddx = 0.f, ddy = 0.f, ddz = 0.f;  // dL_ddir
       const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
-      float basis[16];
       basis[0] = SH_C0;
       basis[1] = -SH_C1 * y; basis[2] = SH_C1 * z; basis[3] = -SH_C1 * x;
       basis[4] = SH_C2[0] * xy; basis[5] = SH_C2[1] * yz; basis[6] = SH_C2[2] * (2.f * zz - xx - yy);
@@ -170,13 +189,7 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
       basis[15] = SH_C3[6] * x * (xx - 3.f * yy);
       const int ncoef = (D + 1) * (D + 1);
 #pragma unroll
-      for (int k = 0; k < 16; k++) {
-        if (k < M) {
-          const float bk = k < ncoef ? basis[k] : 0.f;  // coefficients above the active degree get zero
-          dsh[3 * k] = bk * dRGB[0]; dsh[3 * k + 1] = bk * dRGB[1]; dsh[3 * k + 2] = bk * dRGB[2];
-        }
-      }
-      for (int k = 16; k < M; k++) { dsh[3 * k] = 0.f; dsh[3 * k + 1] = 0.f; dsh[3 * k + 2] = 0.f; }
+      for (int k = 0; k < 16; k++) basis[k] = k < ncoef ? basis[k] : 0.f;  // coefficients above the active degree get zero
 #pragma unroll
       for (int ch = 0; ch < 3; ch++) {
 #define S(k) sh[3 * (k) + ch]
@@ -246,26 +259,41 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
     }
   }
 
-  out.dL_dmean3D[3 * (size_t)idx] = dmean[0];
-  out.dL_dmean3D[3 * (size_t)idx + 1] = dmean[1];
-  out.dL_dmean3D[3 * (size_t)idx + 2] = dmean[2];
+  // ---- coalesced stores through the tile ----
+  __syncthreads();  // every thread is done reading its SH row
+  if (out.dL_dsh != nullptr && M > 0) {
+    float* row = tile + threadIdx.x * SS;
 #pragma unroll
-  for (int k = 0; k < 6; k++) out.dL_dcov3D[6 * (size_t)idx + k] = dcov[k];
-  if (out.dL_dscale) {
-    out.dL_dscale[3 * (size_t)idx] = dscale[0];
-    out.dL_dscale[3 * (size_t)idx + 1] = dscale[1];
-    out.dL_dscale[3 * (size_t)idx + 2] = dscale[2];
+    for (int k = 0; k < 16; k++) {
+      if (k < M) { row[3 * k] = basis[k] * dRGB[0]; row[3 * k + 1] = basis[k] * dRGB[1]; row[3 * k + 2] = basis[k] * dRGB[2]; }
+    }
+    __syncthreads();
+    const int n = min(PB_THREADS, in.P - first) * 3 * M;
+    float* dst = out.dL_dsh + (size_t)first * 3 * M;
+    for (int i = threadIdx.x; i < n; i += PB_THREADS) dst[i] = tile[(i / (3 * M)) * SS + i % (3 * M)];
+    __syncthreads();
   }
-  if (out.dL_drot) reinterpret_cast<float4*>(out.dL_drot)[idx] = make_float4(drot[0], drot[1], drot[2], drot[3]);
+  {
+    const float v3[3] = {g[0], g[1], 0.f};
+    stage_out<3>(tile, out.dL_dmean2D, v3, in.P);
+    const float v6[6] = {g[2], g[3], 0.f, g[4], g[5], g[6]};
+    stage_out<6>(tile, out.dL_dconic, v6, in.P);
+    const float c3[3] = {g[9], g[10], g[11]};
+    stage_out<3>(tile, out.dL_dcolor, c3, in.P);
+    stage_out<3>(tile, out.dL_dmean3D, dmean, in.P);
+    stage_out<6>(tile, out.dL_dcov3D, dcov, in.P);
+    if (out.dL_dscale) stage_out<3>(tile, out.dL_dscale, dscale, in.P);
+  }
+  if (out.dL_drot && valid) reinterpret_cast<float4*>(out.dL_drot)[idx] = make_float4(drot[0], drot[1], drot[2], drot[3]);
 }
 
 void launch_preprocess_backward(const FwdInputs& in, const Cam& cam, const GeomState& g, const int* radii,
                                 const BwdOutputs& out, cudaStream_t s) {
-  const int nb = (in.P + 255) / 256;
+  const int nb = (in.P + PB_THREADS - 1) / PB_THREADS;
   if (in.F == 16)
-    preprocess_bwd_kernel<16><<<nb, 256, 0, s>>>(in, cam, g.tiles_touched, g.clamped, radii, g.grad_rows, out);
+    preprocess_bwd_kernel<16><<<nb, PB_THREADS, 0, s>>>(in, cam, g.tiles_touched, g.clamped, radii, g.grad_rows, out);
   else
-    preprocess_bwd_kernel<32><<<nb, 256, 0, s>>>(in, cam, g.tiles_touched, g.clamped, radii, g.grad_rows, out);
+    preprocess_bwd_kernel<32><<<nb, PB_THREADS, 0, s>>>(in, cam, g.tiles_touched, g.clamped, radii, g.grad_rows, out);
 }
 
 }  // namespace gsr
