@@ -410,7 +410,8 @@ tile_pull_kernel(int gx, int gy, SuperGrid sg, const uint2* __restrict__ l1, con
   const int tx = (s % sg.sgx) * sg.S + tl % sg.S, ty = (s / sg.sgx) * sg.S + tl / sg.S;
   const bool live = tx < gx && ty < gy;
   const uint32_t pxy1 = (uint32_t)tx | ((uint32_t)ty << 8), pxy = pxy1 | (pxy1 << 16);
-  uint32_t off = live ? tile_off[ty * gx + tx] : 0;
+  uint32_t* out = point_list + (live ? tile_off[ty * gx + tx] : 0);
+  const unsigned lt = (1u << lane) - 1;
   const uint32_t beg = l1_off[s], end = l1_off[s + 1];
   const int n = (int)(end - beg);
   const int nchunk = (n + PULL_CHUNK - 1) / PULL_CHUNK;
@@ -430,14 +431,16 @@ tile_pull_kernel(int gx, int gy, SuperGrid sg, const uint2* __restrict__ l1, con
     __syncthreads();  // also orders reuse of buf[st] (read two iterations ago) against this write
     if (c + 1 < nchunk) fetch(c + 1);
     if (live) {
-      const int cnt = min(PULL_CHUNK, n - c * PULL_CHUNK);
-      for (int base = 0; base < cnt; base += 32) {  // warp-uniform trip count
-        const int i = base + lane;
-        const uint2 e = i < cnt ? buf[st][i] : make_uint2(0u, 0u);
+      // entries past the end of the list were staged as rect 0 (matches nothing): no bounds test needed
+      const int iters = (min(PULL_CHUNK, n - c * PULL_CHUNK) + 31) >> 5;
+      const uint2* bp = &buf[st][lane];
+#pragma unroll 4
+      for (int it = 0; it < iters; it++) {
+        const uint2 e = bp[it * 32];
         const bool in = rect_has(e.x, pxy);
         const unsigned m = __ballot_sync(0xffffffffu, in);
-        if (in) point_list[off + __popc(m & ((1u << lane) - 1))] = e.y;
-        off += __popc(m);
+        if (in) out[__popc(m & lt)] = e.y;
+        out += __popc(m);
       }
     }
   }

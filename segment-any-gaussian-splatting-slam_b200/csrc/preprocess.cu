@@ -66,13 +66,27 @@ __device__ __forceinline__ void sh_to_rgb(int deg, const float3 pos, const float
   rgb[2] = fmaxf(result.z, 0.0f);
 }
 
-__global__ void __launch_bounds__(256)
+constexpr int PF_THREADS = 128;
+
+__global__ void __launch_bounds__(PF_THREADS)
 preprocess_kernel(const FwdInputs in, const Cam cam, float4* __restrict__ rec, uint32_t* __restrict__ tiles_touched,
                   uint32_t* __restrict__ rect, uint8_t* __restrict__ clamped, uint64_t* __restrict__ dkeys,
                   int* __restrict__ radii, uint8_t* __restrict__ is_used, int* __restrict__ flags) {
   __shared__ CamS cs;
+  // SH rows of the block's Gaussians (M == 16: 12 float4 each) at a 13-float4 stride: loaded with
+  // coalesced 16-byte accesses, read back per thread conflict-free (the reference reads 48 scalars at a
+  // 192-byte stride per thread, forward.cu:20-71).
+  __shared__ float4 sh_tile[PF_THREADS * 13];
   load_cam(cam, cs);
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int first = blockIdx.x * PF_THREADS;
+  const int idx = first + threadIdx.x;
+  const bool staged_sh = in.colors_precomp == nullptr && in.M == 16 && (((uintptr_t)in.shs & 15) == 0);
+  if (staged_sh) {
+    const int n = min(PF_THREADS, in.P - first) * 12;
+    const float4* src = reinterpret_cast<const float4*>(in.shs) + (size_t)first * 12;
+    for (int i = threadIdx.x; i < n; i += PF_THREADS) sh_tile[(i / 12) * 13 + i % 12] = src[i];
+    __syncthreads();
+  }
   if (idx >= in.P) return;
 
   int my_radius_i = 0;
@@ -122,7 +136,12 @@ preprocess_kernel(const FwdInputs in, const Cam cam, float4* __restrict__ rec, u
 
     float rgb[3];
     unsigned cbits = 0;
-    if (in.colors_precomp == nullptr) {
+    if (staged_sh) {
+      float4 shl[12];
+#pragma unroll
+      for (int q = 0; q < 12; q++) shl[q] = sh_tile[threadIdx.x * 13 + q];
+      sh_to_rgb(in.D, p_orig, cs.campos, reinterpret_cast<const float*>(shl), rgb, cbits);
+    } else if (in.colors_precomp == nullptr) {
       sh_to_rgb(in.D, p_orig, cs.campos, in.shs + (size_t)idx * in.M * 3, rgb, cbits);
     } else {
       rgb[0] = in.colors_precomp[3 * (size_t)idx];
@@ -160,7 +179,7 @@ preprocess_kernel(const FwdInputs in, const Cam cam, float4* __restrict__ rec, u
 
 void launch_preprocess(const FwdInputs& in, const Cam& cam, GeomState& g, ImageState& img, int* radii,
                        uint8_t* is_used, cudaStream_t s) {
-  preprocess_kernel<<<(in.P + 255) / 256, 256, 0, s>>>(in, cam, g.rec, g.tiles_touched, g.rect, g.clamped, g.dkeys_a,
+  preprocess_kernel<<<(in.P + PF_THREADS - 1) / PF_THREADS, PF_THREADS, 0, s>>>(in, cam, g.rec, g.tiles_touched, g.rect, g.clamped, g.dkeys_a,
                                                       radii, is_used, g.flags);
   (void)img;
 }

@@ -35,7 +35,9 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
                       const float* __restrict__ grad_rows, const BwdOutputs out) {
   constexpr int ROW = (F == 16) ? 32 : 64;
   __shared__ CamS cs;
-  __shared__ float tile[PB_TILE];
+  __shared__ float4 tile4[PB_THREADS * 13];  // M == 16: SH rows of 12 float4 at a 13-float4 stride
+  float* tile = reinterpret_cast<float*>(tile4);
+  static_assert(PB_THREADS * 13 * 4 >= PB_TILE, "tile too small for the scalar layout");
   load_cam(cam, cs);
   const int first = blockIdx.x * PB_THREADS;
   const int idx = first + threadIdx.x;
@@ -43,7 +45,13 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
   const int M = in.M, D = in.D;
   const bool visible = valid && radii[idx] > 0;
   const int SS = (3 * M) | 1;  // odd row stride -> conflict-free per-thread rows
-  if (in.shs != nullptr) {     // SH coefficients of the block's Gaussians: coalesced load, rows at stride SS
+  // SH coefficients of the block's Gaussians: coalesced load into the tile
+  const bool sh16 = in.shs != nullptr && M == 16 && (((uintptr_t)in.shs | (uintptr_t)out.dL_dsh) & 15) == 0;
+  if (sh16) {
+    const int n = min(PB_THREADS, in.P - first) * 12;
+    const float4* src = reinterpret_cast<const float4*>(in.shs) + (size_t)first * 12;
+    for (int i = threadIdx.x; i < n; i += PB_THREADS) tile4[(i / 12) * 13 + i % 12] = src[i];
+  } else if (in.shs != nullptr) {  // general M: scalar rows at stride SS
     const int n = min(PB_THREADS, in.P - first) * 3 * M;
     const float* src = in.shs + (size_t)first * 3 * M;
     for (int i = threadIdx.x; i < n; i += PB_THREADS) tile[(i / (3 * M)) * SS + i % (3 * M)] = src[i];
@@ -190,31 +198,42 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
       const int ncoef = (D + 1) * (D + 1);
 #pragma unroll
       for (int k = 0; k < 16; k++) basis[k] = k < ncoef ? basis[k] : 0.f;  // coefficients above the active degree get zero
+      // dL/ddir = sum_k dbasis_k/ddir * W_k with W_k = <dRGB, sh_k>: one pass over the SH row (the reference
+      // walks it once per colour channel, backward.cu:45-135; same sums, different association).
+      float Wk[16];
+      if (sh16) {
+        const float4* r4 = tile4 + threadIdx.x * 13;
 #pragma unroll
-      for (int ch = 0; ch < 3; ch++) {
-#define S(k) sh[3 * (k) + ch]
-        float dRGBdx = 0.f, dRGBdy = 0.f, dRGBdz = 0.f;
-        if (D > 0) {
-          dRGBdx = -SH_C1 * S(3); dRGBdy = -SH_C1 * S(1); dRGBdz = SH_C1 * S(2);
-          if (D > 1) {
-            dRGBdx += SH_C2[0] * y * S(4) + SH_C2[2] * 2.f * -x * S(6) + SH_C2[3] * z * S(7) + SH_C2[4] * 2.f * x * S(8);
-            dRGBdy += SH_C2[0] * x * S(4) + SH_C2[1] * z * S(5) + SH_C2[2] * 2.f * -y * S(6) + SH_C2[4] * 2.f * -y * S(8);
-            dRGBdz += SH_C2[1] * y * S(5) + SH_C2[2] * 2.f * 2.f * z * S(6) + SH_C2[3] * x * S(7);
-            if (D > 2) {
-              dRGBdx += (SH_C3[0] * S(9) * 3.f * 2.f * xy + SH_C3[1] * S(10) * yz + SH_C3[2] * S(11) * -2.f * xy +
-                         SH_C3[3] * S(12) * -3.f * 2.f * xz + SH_C3[4] * S(13) * (-3.f * xx + 4.f * zz - yy) +
-                         SH_C3[5] * S(14) * 2.f * xz + SH_C3[6] * S(15) * 3.f * (xx - yy));
-              dRGBdy += (SH_C3[0] * S(9) * 3.f * (xx - yy) + SH_C3[1] * S(10) * xz +
-                         SH_C3[2] * S(11) * (-3.f * yy + 4.f * zz - xx) + SH_C3[3] * S(12) * -3.f * 2.f * yz +
-                         SH_C3[4] * S(13) * -2.f * xy + SH_C3[5] * S(14) * -2.f * yz + SH_C3[6] * S(15) * -3.f * 2.f * xy);
-              dRGBdz += (SH_C3[1] * S(10) * xy + SH_C3[2] * S(11) * 4.f * 2.f * yz +
-                         SH_C3[3] * S(12) * 3.f * (2.f * zz - xx - yy) + SH_C3[4] * S(13) * 4.f * 2.f * xz +
-                         SH_C3[5] * S(14) * (xx - yy));
-            }
+        for (int gq = 0; gq < 4; gq++) {
+          const float4 a4 = r4[3 * gq], b4 = r4[3 * gq + 1], c4 = r4[3 * gq + 2];
+          Wk[4 * gq + 0] = a4.x * dRGB[0] + a4.y * dRGB[1] + a4.z * dRGB[2];
+          Wk[4 * gq + 1] = a4.w * dRGB[0] + b4.x * dRGB[1] + b4.y * dRGB[2];
+          Wk[4 * gq + 2] = b4.z * dRGB[0] + b4.w * dRGB[1] + c4.x * dRGB[2];
+          Wk[4 * gq + 3] = c4.y * dRGB[0] + c4.z * dRGB[1] + c4.w * dRGB[2];
+        }
+      } else {
+#pragma unroll
+        for (int k = 0; k < 16; k++)
+          Wk[k] = k < M ? sh[3 * k] * dRGB[0] + sh[3 * k + 1] * dRGB[1] + sh[3 * k + 2] * dRGB[2] : 0.f;
+      }
+      if (D > 0) {
+        ddx = -SH_C1 * Wk[3]; ddy = -SH_C1 * Wk[1]; ddz = SH_C1 * Wk[2];
+        if (D > 1) {
+          ddx += SH_C2[0] * y * Wk[4] + SH_C2[2] * 2.f * -x * Wk[6] + SH_C2[3] * z * Wk[7] + SH_C2[4] * 2.f * x * Wk[8];
+          ddy += SH_C2[0] * x * Wk[4] + SH_C2[1] * z * Wk[5] + SH_C2[2] * 2.f * -y * Wk[6] + SH_C2[4] * 2.f * -y * Wk[8];
+          ddz += SH_C2[1] * y * Wk[5] + SH_C2[2] * 2.f * 2.f * z * Wk[6] + SH_C2[3] * x * Wk[7];
+          if (D > 2) {
+            ddx += (SH_C3[0] * Wk[9] * 3.f * 2.f * xy + SH_C3[1] * Wk[10] * yz + SH_C3[2] * Wk[11] * -2.f * xy +
+                    SH_C3[3] * Wk[12] * -3.f * 2.f * xz + SH_C3[4] * Wk[13] * (-3.f * xx + 4.f * zz - yy) +
+                    SH_C3[5] * Wk[14] * 2.f * xz + SH_C3[6] * Wk[15] * 3.f * (xx - yy));
+            ddy += (SH_C3[0] * Wk[9] * 3.f * (xx - yy) + SH_C3[1] * Wk[10] * xz +
+                    SH_C3[2] * Wk[11] * (-3.f * yy + 4.f * zz - xx) + SH_C3[3] * Wk[12] * -3.f * 2.f * yz +
+                    SH_C3[4] * Wk[13] * -2.f * xy + SH_C3[5] * Wk[14] * -2.f * yz + SH_C3[6] * Wk[15] * -3.f * 2.f * xy);
+            ddz += (SH_C3[1] * Wk[10] * xy + SH_C3[2] * Wk[11] * 4.f * 2.f * yz +
+                    SH_C3[3] * Wk[12] * 3.f * (2.f * zz - xx - yy) + SH_C3[4] * Wk[13] * 4.f * 2.f * xz +
+                    SH_C3[5] * Wk[14] * (xx - yy));
           }
         }
-#undef S
-        ddx += dRGBdx * dRGB[ch]; ddy += dRGBdy * dRGB[ch]; ddz += dRGBdz * dRGB[ch];
       }
       // dnormvdv (auxiliary.h:112-122)
       const float3 v = dir_orig;
@@ -261,7 +280,19 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
 
   // ---- coalesced stores through the tile ----
   __syncthreads();  // every thread is done reading its SH row
-  if (out.dL_dsh != nullptr && M > 0) {
+  if (sh16) {
+    float d48[48];
+#pragma unroll
+    for (int k = 0; k < 16; k++) { d48[3 * k] = basis[k] * dRGB[0]; d48[3 * k + 1] = basis[k] * dRGB[1]; d48[3 * k + 2] = basis[k] * dRGB[2]; }
+    float4* r4 = tile4 + threadIdx.x * 13;
+#pragma unroll
+    for (int qq = 0; qq < 12; qq++) r4[qq] = make_float4(d48[4 * qq], d48[4 * qq + 1], d48[4 * qq + 2], d48[4 * qq + 3]);
+    __syncthreads();
+    const int n = min(PB_THREADS, in.P - first) * 12;
+    float4* dst = reinterpret_cast<float4*>(out.dL_dsh) + (size_t)first * 12;
+    for (int i = threadIdx.x; i < n; i += PB_THREADS) dst[i] = tile4[(i / 12) * 13 + i % 12];
+    __syncthreads();
+  } else if (out.dL_dsh != nullptr && M > 0) {
     float* row = tile + threadIdx.x * SS;
 #pragma unroll
     for (int k = 0; k < 16; k++) {
