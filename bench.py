@@ -239,22 +239,46 @@ def run_e2e(args, cam, d, g, fwd, bwd, bucket, world, dev, sync_all):
     dd["viewmatrix"], dd["projmatrix"], dd["campos"] = (torch.empty_like(d["viewmatrix"]),
                                                          torch.empty_like(d["projmatrix"]),
                                                          torch.empty_like(d["campos"]))
-    gt = torch.empty(3, H, W, device=dev)
+    gt = [torch.empty(3, H, W, device=dev) for _ in range(2)]  # double-buffered: the copy of step i overlaps step i's forward
+    h_loss = [torch.zeros(1).pin_memory() for _ in range(2)]
     h2d = sum(t.numel() * 4 for t in (h_view, h_proj, h_campos, h_gt))
     inv_n = 1.0 / (3 * H * W)
+    copy_stream = torch.cuda.Stream(device=dev)
+    ev_gt = [torch.cuda.Event() for _ in range(2)]
+    ev_free = [torch.cuda.Event() for _ in range(2)]
+    ev_loss = [torch.cuda.Event() for _ in range(2)]
+    main = torch.cuda.current_stream()
+    for e_ in ev_free:
+        e_.record(main)
+    state = dict(i=0, last=0.0)
 
     def step():
+        i = state["i"]
+        k = i & 1
+        # ground-truth image: pinned host -> device on the copy stream, concurrent with this step's forward
+        copy_stream.wait_event(ev_free[k])
+        with torch.cuda.stream(copy_stream):
+            gt[k].copy_(h_gt, non_blocking=True)
+            ev_gt[k].record(copy_stream)
         dd["viewmatrix"].copy_(h_view, non_blocking=True)
         dd["projmatrix"].copy_(h_proj, non_blocking=True)
         dd["campos"].copy_(h_campos, non_blocking=True)
-        gt.copy_(h_gt, non_blocking=True)
         res = fwd(dd)
-        diff = res[2] - gt
+        main.wait_event(ev_gt[k])
+        diff = res[2] - gt[k]
         loss = diff.abs().sum() * inv_n
-        bwd(dd, res, g[0], torch.sign(diff) * inv_n, g[2])
+        grad_c = torch.sign(diff) * inv_n
+        ev_free[k].record(main)
+        bwd(dd, res, g[0], grad_c, g[2])
         if world > 1:
             dist.all_reduce(bucket.flat)
-        return float(loss.item())  # 4-byte D2H of the step's result
+        h_loss[k].copy_(loss.reshape(1), non_blocking=True)  # 4-byte D2H of the step's result
+        ev_loss[k].record(main)
+        if i > 0:  # read the previous step's loss: keeps one step in flight instead of draining the GPU
+            ev_loss[k ^ 1].synchronize()
+            state["last"] = float(h_loss[k ^ 1][0])
+        state["i"] = i + 1
+        return state["last"]
 
     for _ in range(3):
         step()
@@ -262,7 +286,9 @@ def run_e2e(args, cam, d, g, fwd, bwd, bucket, world, dev, sync_all):
     sync_all()
     ev0.record()
     for _ in range(args.steps):
-        loss = step()
+        step()
+    ev_loss[(state["i"] - 1) & 1].synchronize()
+    loss = float(h_loss[(state["i"] - 1) & 1][0])
     ev1.record()
     sync_all()
     return dict(ms=ev0.elapsed_time(ev1), h2d=h2d, d2h=4, loss=loss)

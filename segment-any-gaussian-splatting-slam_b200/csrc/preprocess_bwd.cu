@@ -32,7 +32,7 @@ template <int F>
 __global__ void __launch_bounds__(PB_THREADS)
 preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restrict__ tiles_touched,
                       const uint8_t* __restrict__ clampedb, const int* __restrict__ radii,
-                      const float* __restrict__ grad_rows, const BwdOutputs out) {
+                      const float* __restrict__ grad_rows, const float4* __restrict__ rec, const BwdOutputs out) {
   constexpr int ROW = (F == 16) ? 32 : 64;
   __shared__ CamS cs;
   __shared__ float4 tile4[PB_THREADS * 13];  // M == 16: SH rows of 12 float4 at a 13-float4 stride
@@ -68,6 +68,21 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
       float4 t = row[q];
       g[4 * q] = t.x; g[4 * q + 1] = t.y; g[4 * q + 2] = t.z; g[4 * q + 3] = t.w;
     }
+  }
+  if (visible) {
+    // K5 accumulates raw per-pixel moments (render_bwd.cu header); apply the per-Gaussian coefficients:
+    // reference backward.cu:653-677 with dL_dG = opacity * dL_dalpha, G-gradients and depth partials.
+    const float4 r0 = rec[REC4 * (size_t)idx], r1 = rec[REC4 * (size_t)idx + 1], r3 = rec[REC4 * (size_t)idx + 3];
+    const float ca = r0.z, cb2 = r0.w, cc = r1.x, op = r1.y, covzx = r3.x, covyz = r3.y;
+    const float cza = covzx * ca + covyz * cb2, czb = covzx * cb2 + covyz * cc;
+    const float Qx = g[0], Qy = g[1], Qxx = g[2], Qxy = g[3], Qyy = g[4], Wx = g[5], Wy = g[6], W0 = g[8];
+    g[0] = (-op * (ca * Qx + cb2 * Qy) - cza * W0) * (0.5f * cam.W);
+    g[1] = (-op * (cc * Qy + cb2 * Qx) - czb * W0) * (0.5f * cam.H);
+    g[2] = -0.5f * op * Qxx - covzx * Wx;
+    g[3] = -0.5f * op * Qxy - covyz * Wx - covzx * Wy;
+    g[4] = -0.5f * op * Qyy - covyz * Wy;
+    g[5] = -ca * Wx - cb2 * Wy;  // d/dcov_zx
+    g[6] = -cb2 * Wx;            // d/dcov_yz (sic, backward.cu:629)
   }
   // scalar / float4 outputs of K5 are written directly (coalesced as they are)
   if (valid) {
@@ -322,9 +337,9 @@ void launch_preprocess_backward(const FwdInputs& in, const Cam& cam, const GeomS
                                 const BwdOutputs& out, cudaStream_t s) {
   const int nb = (in.P + PB_THREADS - 1) / PB_THREADS;
   if (in.F == 16)
-    preprocess_bwd_kernel<16><<<nb, PB_THREADS, 0, s>>>(in, cam, g.tiles_touched, g.clamped, radii, g.grad_rows, out);
+    preprocess_bwd_kernel<16><<<nb, PB_THREADS, 0, s>>>(in, cam, g.tiles_touched, g.clamped, radii, g.grad_rows, g.rec, out);
   else
-    preprocess_bwd_kernel<32><<<nb, PB_THREADS, 0, s>>>(in, cam, g.tiles_touched, g.clamped, radii, g.grad_rows, out);
+    preprocess_bwd_kernel<32><<<nb, PB_THREADS, 0, s>>>(in, cam, g.tiles_touched, g.clamped, radii, g.grad_rows, g.rec, out);
 }
 
 }  // namespace gsr

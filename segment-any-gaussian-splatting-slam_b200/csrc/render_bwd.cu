@@ -18,8 +18,14 @@
 //    (slot s of lane l holds channel s ^ (l & 15)), which makes the butterfly transpose-reduce
 //    select-free: v[s] += shfl_xor(v[s ^ B], B).
 //
-// Gradient row layout (float index): 0 dmean2D.x  1 dmean2D.y  2 dconic.x  3 dconic.y  4 dconic.w
-// 5 dcov_zx  6 dcov_yz  7 dopacity  8 ddepth  9..11 dcolor  12..12+F-1 dfeature.
+//  * The nine geometric gradients of a pair are linear combinations, with per-GAUSSIAN coefficients
+//    (conic, opacity, cov_zx/yz), of nine per-PIXEL moments of q = G dL/da and wd = w dL/dD:
+//    sum q {1, dx, dy, dx dx, dx dy, dy dy} and sum wd {1, dx, dy}. Sums commute with the
+//    combination, so the kernel accumulates the raw moments and the per-Gaussian backward
+//    (preprocess_bwd.cu) applies the coefficients once per Gaussian instead of once per pair.
+//
+// Gradient row layout (float index): 0 Qx  1 Qy  2 Qxx  3 Qxy  4 Qyy  5 Wx  6 Wy  7 Q0 (= dopacity)
+// 8 W0 (= ddepth)  9..11 dcolor  12..12+F-1 dfeature.
 #include "common.cuh"
 #include "tma.cuh"
 
@@ -195,19 +201,17 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       const float dL_da = T * E - S * inv1ma;
       S = fmaf(w, E, S);
       const float wd = w * dpd;
-      const float dL_dG = r1.y * dL_da;
-      const float gdx = G * dx, gdy = G * dy;
-      const float dG_ddelx = -gdx * a - gdy * bq;
-      const float dG_ddely = -gdy * c - gdx * bq;
+      const float q = G * dL_da;
+      const float qx = q * dx, qy = q * dy;
       float v[16];
-      v[0] = (dL_dG * dG_ddelx - wd * cza) * ddelx_dx;
-      v[1] = (dL_dG * dG_ddely - wd * czb) * ddely_dy;
-      v[2] = -0.5f * gdx * dx * dL_dG - wd * covzx * dx;
-      v[3] = -0.5f * gdx * dy * dL_dG - wd * (covyz * dx + covzx * dy);
-      v[4] = -0.5f * gdy * dy * dL_dG - wd * covyz * dy;
-      v[5] = -wd * (a * dx + bq * dy);  // d/dcov_zx
-      v[6] = -wd * bq * dx;             // d/dcov_yz (sic, backward.cu:629)
-      v[7] = G * dL_da;
+      v[0] = qx;
+      v[1] = qy;
+      v[2] = qx * dx;
+      v[3] = qx * dy;
+      v[4] = qy * dy;
+      v[5] = wd * dx;
+      v[6] = wd * dy;
+      v[7] = q;
       v[8] = wd;
       v[9] = w * dpx[0];
       v[10] = w * dpx[1];
