@@ -205,6 +205,9 @@ def run_mine(args, rank, world, local_rank):
                  n_blend=cp["blended"], n_eval_bwd=int(st["n_contrib"].to(torch.int64).sum()),
                  warp_blended=cp["warp_blended"], l1_total=l1_total)
     del st
+    for _ in range(3):  # settle the caching allocator again after the statistics pass (untimed, in addition to W)
+        step()
+    sync_all()
 
     # ---- timed region 1: inputs resident in HBM ----
     clocks = ClockSampler(local_rank)

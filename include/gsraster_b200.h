@@ -81,6 +81,25 @@ int gsr_backward(const gsr_params* params, int num_rendered,
                  float* dL_dcolor, float* dL_dobjects, float* dL_dmean3D, float* dL_dcov3D,
                  float* dL_dsh, float* dL_dscale, float* dL_drot);
 
+/* EXTENSION (no reference equivalent: the reference never differentiates w.r.t. the camera):
+ * gsr_backward plus the gradients w.r.t. the three camera inputs of gsr_forward, each treated as an independent
+ * input: dL_dviewmatrix[16] and dL_dprojmatrix[16] (column-major flat like the inputs; the unused rows -- row 3 of
+ * the view matrix, row 2 of the projection matrix -- are zero) and dL_dcampos[3]. The t = V p path reuses the
+ * reference's per-Gaussian intermediates (including its dropped dL_dcovyz terms, backward.cu:263-268), so that at SH
+ * degree 0 the rigid-motion identity "moving the camera == moving every Gaussian the other way" holds exactly
+ * against dL_dmean3D / dL_dcov3D. The 27 sums are reduced warp -> block -> double-precision atomics. */
+int gsr_backward_pose(const gsr_params* params, int num_rendered,
+                      const float* background, const float* means3D, const float* shs, const float* sh_objs,
+                      const float* colors_precomp, const float* scales, const float* rotations,
+                      const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                      const float* cam_pos, const int* radii,
+                      char* geom_buffer, char* binning_buffer, char* image_buffer,
+                      const float* dL_dpix_depth, const float* dL_dpix, const float* dL_dpix_obj,
+                      float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_ddepths,
+                      float* dL_dcolor, float* dL_dobjects, float* dL_dmean3D, float* dL_dcov3D,
+                      float* dL_dsh, float* dL_dscale, float* dL_drot,
+                      float* dL_dviewmatrix, float* dL_dprojmatrix, float* dL_dcampos);
+
 /* Replaces Rasterizer::markVisible (rasterizer.h:24-29, rasterizer_impl.cu:141-153). */
 int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                      uint8_t* present, void* stream);
@@ -127,7 +146,9 @@ int gsr_count_pairs(const gsr_params* params, int num_rendered, const char* geom
                     const char* binning_buffer, const char* image_buffer, unsigned long long* counts);
 
 /* Sizes seen by the last gsr_forward on this thread: out[0] = num_rendered R, out[1] = total length
- * of the supertile lists (binning intermediate). For bench.py's algorithmic-bytes model. */
+ * of the supertile lists (binning intermediate), out[2..4] = host microseconds blocked in the
+ * num_rendered synchronisation / spent in the binning allocator callback / spent launching the
+ * post-sync kernels, out[5] reserved. `out` holds 6 values. For bench.py's model and diagnostics. */
 int gsr_last_forward_stats(unsigned long long* out);
 
 /* Kernel launches issued by the last forward/backward/knn call on this thread (for bench.py). */

@@ -2,6 +2,7 @@
 // order mirrors Rasterizer::forward / ::backward of the reference (rasterizer_impl.cu:201-352,
 // 356-466); every stage is one of our sm_100a kernels. There is NO CPU fallback: any CUDA failure
 // is reported through the status code + gsr_last_error().
+#include <chrono>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -19,7 +20,11 @@ void launch_export_keys(int T, const uint2* ranges, const uint32_t* point_list, 
 namespace {
 thread_local std::string g_err;
 thread_local int g_launches = 0;
-thread_local unsigned long long g_last_stats[2] = {0, 0};
+thread_local unsigned long long g_last_stats[6] = {0, 0, 0, 0, 0, 0};
+inline unsigned long long now_us() {
+  return (unsigned long long)std::chrono::duration_cast<std::chrono::microseconds>(
+             std::chrono::steady_clock::now().time_since_epoch()).count();
+}
 thread_local int* g_pinned = nullptr;  // 8 ints of pinned host memory for the num_rendered read-back
 
 // ---- optional per-stage event timing (gsr_set_stage_timing) ----
@@ -171,8 +176,10 @@ int gsr_forward(const gsr_params* p, gsr_alloc_fn geom_alloc, void* geom_ctx, gs
 
   // the one data-dependent host sync of the path (reference: rasterizer_impl.cu:289-290)
   if (!g_pinned) CUDA_TRY(cudaHostAlloc(&g_pinned, 8 * sizeof(int), cudaHostAllocDefault));
+  const unsigned long long t_enq = now_us();
   CUDA_TRY(cudaMemcpyAsync(g_pinned, g.flags, 4 * sizeof(int), cudaMemcpyDeviceToHost, stream));
   CUDA_TRY(cudaStreamSynchronize(stream));
+  const unsigned long long t_sync = now_us();
   const int64_t R = (int64_t)(uint32_t)g_pinned[0];
   const uint64_t l1_total = (uint64_t)(uint32_t)g_pinned[2] | ((uint64_t)(uint32_t)g_pinned[3] << 32);
   if (g_pinned[1]) return fail(GSR_ERR_INVALID_ARGUMENT, "Point is filtered although prefiltered is set");
@@ -187,6 +194,7 @@ int gsr_forward(const gsr_params* p, gsr_alloc_fn geom_alloc, void* geom_ctx, gs
   char* bin_chunk = binning_alloc(binning_ctx, gsr::bin_from_chunk(nullptr, (size_t)R, (size_t)l1_total, nw_ns, b));
   if (!bin_chunk) return fail(GSR_ERR_ALLOC, "binning allocator returned NULL");
   gsr::bin_from_chunk(bin_chunk, (size_t)R, (size_t)l1_total, nw_ns, b);
+  const unsigned long long t_alloc = now_us();
   {
     StageTimer tm(2, stream);
     gsr::launch_binning(P, R, cam, g, b, img, stream, g_launches);
@@ -198,19 +206,25 @@ int gsr_forward(const gsr_params* p, gsr_alloc_fn geom_alloc, void* geom_ctx, gs
   }
   g_launches += 1;
   STAGE_CHECK("render_forward");
+  g_last_stats[2] = t_sync - t_enq;           // host us blocked in the num_rendered synchronisation
+  g_last_stats[3] = t_alloc - t_sync;         // host us in the binning allocator callback
+  g_last_stats[4] = now_us() - t_alloc;       // host us launching binning + forward blend
   return GSR_OK;
 }
 
-int gsr_backward(const gsr_params* p, int num_rendered, const float* background, const float* means3D,
+static int backward_impl(const gsr_params* p, int num_rendered, const float* background, const float* means3D,
                  const float* shs, const float* sh_objs, const float* colors_precomp, const float* scales,
                  const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
                  const float* projmatrix, const float* cam_pos, const int* radii, char* geom_buffer,
                  char* binning_buffer, char* image_buffer, const float* dL_dpix_depth, const float* dL_dpix,
                  const float* dL_dpix_obj, float* dL_dmean2D, float* dL_dconic, float* dL_dopacity,
                  float* dL_ddepths, float* dL_dcolor, float* dL_dobjects, float* dL_dmean3D, float* dL_dcov3D,
-                 float* dL_dsh, float* dL_dscale, float* dL_drot) {
+                 float* dL_dsh, float* dL_dscale, float* dL_drot, float* dL_dviewmatrix, float* dL_dprojmatrix,
+                 float* dL_dcampos) {
   g_launches = 0;
   if (int rc = check_params(p)) return rc;
+  if (dL_dviewmatrix && (!dL_dprojmatrix || !dL_dcampos))
+    return fail(GSR_ERR_INVALID_ARGUMENT, "camera gradients: provide all three outputs or none");
   if (p->P == 0) return GSR_OK;
   if (!geom_buffer || !binning_buffer || !image_buffer) return fail(GSR_ERR_INVALID_ARGUMENT, "scratch buffer is NULL");
   if (!dL_dpix_depth || !dL_dpix || !dL_dpix_obj) return fail(GSR_ERR_INVALID_ARGUMENT, "upstream gradient is NULL");
@@ -243,20 +257,52 @@ int gsr_backward(const gsr_params* p, int num_rendered, const float* background,
   STAGE_CHECK("render_backward");
   const gsr::FwdInputs in = make_inputs(p, means3D, shs, colors_precomp, nullptr, scales, rotations, cov3D_precomp);
   gsr::BwdOutputs out{dL_dmean2D, dL_dconic, dL_dopacity, dL_ddepths, dL_dcolor, dL_dobjects,
-                      dL_dmean3D, dL_dcov3D, dL_dsh,      dL_dscale,  dL_drot};
+                      dL_dmean3D, dL_dcov3D, dL_dsh,      dL_dscale,  dL_drot,
+                      dL_dviewmatrix, dL_dprojmatrix, dL_dcampos};
   {
     StageTimer tm(5, stream);
     gsr::launch_preprocess_backward(in, cam, g, radii, out, stream);
   }
-  g_launches += 1;
+  g_launches += dL_dviewmatrix ? 2 : 1;
   STAGE_CHECK("preprocess_backward");
   return GSR_OK;
 }
 
+int gsr_backward(const gsr_params* p, int num_rendered, const float* background, const float* means3D,
+                 const float* shs, const float* sh_objs, const float* colors_precomp, const float* scales,
+                 const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                 const float* projmatrix, const float* cam_pos, const int* radii, char* geom_buffer,
+                 char* binning_buffer, char* image_buffer, const float* dL_dpix_depth, const float* dL_dpix,
+                 const float* dL_dpix_obj, float* dL_dmean2D, float* dL_dconic, float* dL_dopacity,
+                 float* dL_ddepths, float* dL_dcolor, float* dL_dobjects, float* dL_dmean3D, float* dL_dcov3D,
+                 float* dL_dsh, float* dL_dscale, float* dL_drot) {
+  return backward_impl(p, num_rendered, background, means3D, shs, sh_objs, colors_precomp, scales, rotations,
+                       cov3D_precomp, viewmatrix, projmatrix, cam_pos, radii, geom_buffer, binning_buffer, image_buffer,
+                       dL_dpix_depth, dL_dpix, dL_dpix_obj, dL_dmean2D, dL_dconic, dL_dopacity, dL_ddepths, dL_dcolor,
+                       dL_dobjects, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, nullptr, nullptr, nullptr);
+}
+
+int gsr_backward_pose(const gsr_params* p, int num_rendered, const float* background, const float* means3D,
+                      const float* shs, const float* sh_objs, const float* colors_precomp, const float* scales,
+                      const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                      const float* projmatrix, const float* cam_pos, const int* radii, char* geom_buffer,
+                      char* binning_buffer, char* image_buffer, const float* dL_dpix_depth, const float* dL_dpix,
+                      const float* dL_dpix_obj, float* dL_dmean2D, float* dL_dconic, float* dL_dopacity,
+                      float* dL_ddepths, float* dL_dcolor, float* dL_dobjects, float* dL_dmean3D, float* dL_dcov3D,
+                      float* dL_dsh, float* dL_dscale, float* dL_drot, float* dL_dviewmatrix, float* dL_dprojmatrix,
+                      float* dL_dcampos) {
+  if (!dL_dviewmatrix || !dL_dprojmatrix || !dL_dcampos)
+    return fail(GSR_ERR_INVALID_ARGUMENT, "camera gradient output is NULL");
+  return backward_impl(p, num_rendered, background, means3D, shs, sh_objs, colors_precomp, scales, rotations,
+                       cov3D_precomp, viewmatrix, projmatrix, cam_pos, radii, geom_buffer, binning_buffer, image_buffer,
+                       dL_dpix_depth, dL_dpix, dL_dpix_obj, dL_dmean2D, dL_dconic, dL_dopacity, dL_ddepths, dL_dcolor,
+                       dL_dobjects, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, dL_dviewmatrix, dL_dprojmatrix,
+                       dL_dcampos);
+}
+
 int gsr_last_forward_stats(unsigned long long* out) {
   if (!out) return fail(GSR_ERR_INVALID_ARGUMENT, "out is NULL");
-  out[0] = g_last_stats[0];
-  out[1] = g_last_stats[1];
+  for (int i = 0; i < 6; i++) out[i] = g_last_stats[i];
   return GSR_OK;
 }
 int gsr_set_stage_timing(int enable) {

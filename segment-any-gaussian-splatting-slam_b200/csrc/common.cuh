@@ -50,6 +50,7 @@ struct GeomState {
   uint32_t* block_sums;   // emit_blocks(P) + 8
   int* flags;             // [0] num_rendered, [1] prefiltered-cull error, [2..3] L1 list total (u64)
   float* grad_rows;       // P * 32 (F=16) or P * 48 (F=32): backward intermediate, see render_bwd.cu
+  double* pose_acc;       // 32: camera-pose gradient accumulators (extension, see preprocess_bwd.cu)
 };
 struct ImageState {
   float* final_T;
@@ -99,6 +100,7 @@ inline size_t geom_from_chunk(char* chunk, size_t P, GeomState& g, int F = 32) {
   carve(p, g.digit_total, RADIX);
   carve(p, g.block_sums, (size_t)emit_blocks((int64_t)P) + 8);
   carve(p, g.flags, 8);
+  carve(p, g.pose_acc, 32);
   carve(p, g.grad_rows, P * (size_t)grad_row_floats(F));
   return (size_t)(p - chunk) + 256;
 }
@@ -181,6 +183,8 @@ void launch_count_pairs(const Cam& cam, const GeomState& g, const BinState& b, c
 struct BwdOutputs {
   float* dL_dmean2D; float* dL_dconic; float* dL_dopacity; float* dL_ddepths; float* dL_dcolor; float* dL_dobjects;
   float* dL_dmean3D; float* dL_dcov3D; float* dL_dsh; float* dL_dscale; float* dL_drot;
+  // extension (no reference equivalent): gradients w.r.t. the camera inputs, NULL = not requested
+  float* dL_dviewmatrix; float* dL_dprojmatrix; float* dL_dcampos;
 };
 void launch_preprocess_backward(const FwdInputs& in, const Cam& cam, const GeomState& g, const int* radii,
                                 const BwdOutputs& out, cudaStream_t s);

@@ -28,11 +28,12 @@ __device__ __forceinline__ void stage_out(float* tile, float* __restrict__ gbase
   __syncthreads();
 }
 
-template <int F>
+template <int F, bool POSE>
 __global__ void __launch_bounds__(PB_THREADS)
 preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restrict__ tiles_touched,
                       const uint8_t* __restrict__ clampedb, const int* __restrict__ radii,
-                      const float* __restrict__ grad_rows, const float4* __restrict__ rec, const BwdOutputs out) {
+                      const float* __restrict__ grad_rows, const float4* __restrict__ rec, double* __restrict__ pose_acc,
+                      const BwdOutputs out) {
   constexpr int ROW = (F == 16) ? 32 : 64;
   __shared__ CamS cs;
   __shared__ float4 tile4[PB_THREADS * 13];  // M == 16: SH rows of 12 float4 at a 13-float4 stride
@@ -97,6 +98,11 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
 #pragma unroll
   for (int k = 0; k < 16; k++) basis[k] = 0.f;
 
+  // camera-pose partial sums of this Gaussian: [0..11] dL/dV rows 0..2 (r*4+c), [12..23] dL/dPV rows 0,1,3, [24..26] dL/dcampos
+  constexpr bool want_pose = POSE;
+  float pv[27];
+#pragma unroll
+  for (int k = 0; k < 27; k++) pv[k] = 0.f;
   float dmean[3] = {0.f, 0.f, 0.f};
   float dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   float dscale[3] = {0.f, 0.f, 0.f};
@@ -157,6 +163,11 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
     const float dL_dT10 = 2 * TV(1, 0) * dL_dc + TV(0, 0) * dL_db + TV(2, 0) * dL_dcovyz;
     const float dL_dT11 = 2 * TV(1, 1) * dL_dc + TV(0, 1) * dL_db;  // reference drops the dL_dcovyz term (backward.cu:263-265)
     const float dL_dT12 = 2 * TV(1, 2) * dL_dc + TV(0, 2) * dL_db;  // idem (backward.cu:266-268)
+    // full dL/dA (A = Jm * R_cw) for the pose gradient: row 1 with the dL_dcovyz terms the reference's mean path
+    // drops, row 2 (constant-Jacobian row, only reaches cov_zx / cov_yz)
+    float dA1[3] = {dL_dT10, dL_dT11 + TV(2, 1) * dL_dcovyz, dL_dT12 + TV(2, 2) * dL_dcovyz};
+    float dA2[3] = {dL_dcovzx * TV(0, 0) + dL_dcovyz * TV(1, 0), dL_dcovzx * TV(0, 1) + dL_dcovyz * TV(1, 1),
+                    dL_dcovzx * TV(0, 2) + dL_dcovyz * TV(1, 2)};
 #undef TV
 #undef TT
     const float* V = cs.V;
@@ -170,6 +181,24 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
     const float dL_dty = y_grad_mul * -h_y * tz2 * dL_dJ12;
     const float dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * c2.tx) * tz3 * dL_dJ02 +
                          (2 * h_y * c2.ty) * tz3 * dL_dJ12;
+    if (want_pose) {
+      const float p4[4] = {mean.x, mean.y, mean.z, 1.f};
+      const float dA0[3] = {dL_dT00, dL_dT01, dL_dT02};
+      const float Jm00 = h_x * tz, Jm11 = h_y * tz, Jm02 = -h_x * c2.tx * tz2, Jm12 = -h_y * c2.ty * tz2;
+      const float dtr[3] = {dL_dtx, dL_dty, dL_dtz + g[8]};  // g[8] = dL/d(depth), depth = t.z
+#pragma unroll
+      for (int c = 0; c < 4; c++) {
+        pv[0 + c] = dtr[0] * p4[c];
+        pv[4 + c] = dtr[1] * p4[c];
+        pv[8 + c] = dtr[2] * p4[c];
+      }
+#pragma unroll
+      for (int j = 0; j < 3; j++) {  // dL/dR_cw[k][j] = sum_i Jm[i][k] dL/dA[i][j]
+        pv[0 + j] += Jm00 * dA0[j];
+        pv[4 + j] += Jm11 * dA1[j];
+        pv[8 + j] += Jm02 * dA0[j] + Jm12 * dA1[j] + dA2[j];
+      }
+    }
     dmean[0] = V[0] * dL_dtx + V[1] * dL_dty + V[2] * dL_dtz;
     dmean[1] = V[4] * dL_dtx + V[5] * dL_dty + V[6] * dL_dtz;
     dmean[2] = V[8] * dL_dtx + V[9] * dL_dty + V[10] * dL_dtz;
@@ -186,6 +215,16 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
     dmean[2] += ddep * (V[10] - V[11] * mulz);
     const float mul1 = (proj[0] * m.x + proj[4] * m.y + proj[8] * m.z + proj[12]) * m_w * m_w;
     const float mul2 = (proj[1] * m.x + proj[5] * m.y + proj[9] * m.z + proj[13]) * m_w * m_w;
+    if (want_pose) {
+      const float p4[4] = {m.x, m.y, m.z, 1.f};
+      const float r3 = -(g[0] * mul1 + g[1] * mul2);
+#pragma unroll
+      for (int c = 0; c < 4; c++) {
+        pv[12 + c] = g[0] * m_w * p4[c];
+        pv[16 + c] = g[1] * m_w * p4[c];
+        pv[20 + c] = r3 * p4[c];
+      }
+    }
     dmean[0] += (proj[0] * m_w - proj[3] * mul1) * g[0] + (proj[1] * m_w - proj[3] * mul2) * g[1];
     dmean[1] += (proj[4] * m_w - proj[7] * mul1) * g[0] + (proj[5] * m_w - proj[7] * mul2) * g[1];
     dmean[2] += (proj[8] * m_w - proj[11] * mul1) * g[0] + (proj[9] * m_w - proj[11] * mul2) * g[1];
@@ -254,9 +293,11 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
       const float3 v = dir_orig;
       const float sum2 = v.x * v.x + v.y * v.y + v.z * v.z;
       const float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
-      dmean[0] += ((+sum2 - v.x * v.x) * ddx - v.y * v.x * ddy - v.z * v.x * ddz) * invsum32;
-      dmean[1] += (-v.x * v.y * ddx + (sum2 - v.y * v.y) * ddy - v.z * v.y * ddz) * invsum32;
-      dmean[2] += (-v.x * v.z * ddx - v.y * v.z * ddy + (sum2 - v.z * v.z) * ddz) * invsum32;
+      const float sdx = ((+sum2 - v.x * v.x) * ddx - v.y * v.x * ddy - v.z * v.x * ddz) * invsum32;
+      const float sdy = (-v.x * v.y * ddx + (sum2 - v.y * v.y) * ddy - v.z * v.y * ddz) * invsum32;
+      const float sdz = (-v.x * v.z * ddx - v.y * v.z * ddy + (sum2 - v.z * v.z) * ddz) * invsum32;
+      dmean[0] += sdx; dmean[1] += sdy; dmean[2] += sdz;
+      pv[24] = -sdx; pv[25] = -sdy; pv[26] = -sdz;  // dir = mean - campos
     }
 
     if (in.scales != nullptr) {
@@ -331,15 +372,47 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
     if (out.dL_dscale) stage_out<3>(tile, out.dL_dscale, dscale, in.P);
   }
   if (out.dL_drot && valid) reinterpret_cast<float4*>(out.dL_drot)[idx] = make_float4(drot[0], drot[1], drot[2], drot[3]);
+  if (want_pose) {  // block-uniform: warp shuffle -> shared -> one double atomic per value per block
+    if (threadIdx.x < 27) tile[threadIdx.x] = 0.f;
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 27; k++) {
+      float v = pv[k];
+#pragma unroll
+      for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if ((threadIdx.x & 31) == 0 && v != 0.f) atomicAdd(&tile[k], v);
+    }
+    __syncthreads();
+    if (threadIdx.x < 27 && tile[threadIdx.x] != 0.f) atomicAdd(&pose_acc[threadIdx.x], (double)tile[threadIdx.x]);
+  }
+}
+
+// pose accumulators (double) -> the three camera-gradient outputs (column-major flat matrices like the inputs)
+__global__ void pose_finalize_kernel(const double* __restrict__ acc, float* __restrict__ dV, float* __restrict__ dPV,
+                                     float* __restrict__ dC) {
+  const int t = threadIdx.x;
+  if (t < 16) {
+    const int r = t & 3, c = t >> 2;  // flat index 4c + r
+    dV[t] = r < 3 ? (float)acc[r * 4 + c] : 0.f;
+    const int row = r == 0 ? 0 : (r == 1 ? 1 : (r == 3 ? 2 : -1));
+    dPV[t] = row >= 0 ? (float)acc[12 + row * 4 + c] : 0.f;
+  }
+  if (t < 3 && dC) dC[t] = (float)acc[24 + t];
 }
 
 void launch_preprocess_backward(const FwdInputs& in, const Cam& cam, const GeomState& g, const int* radii,
                                 const BwdOutputs& out, cudaStream_t s) {
   const int nb = (in.P + PB_THREADS - 1) / PB_THREADS;
-  if (in.F == 16)
-    preprocess_bwd_kernel<16><<<nb, PB_THREADS, 0, s>>>(in, cam, g.tiles_touched, g.clamped, radii, g.grad_rows, g.rec, out);
-  else
-    preprocess_bwd_kernel<32><<<nb, PB_THREADS, 0, s>>>(in, cam, g.tiles_touched, g.clamped, radii, g.grad_rows, g.rec, out);
+  if (out.dL_dviewmatrix) cudaMemsetAsync(g.pose_acc, 0, 32 * sizeof(double), s);
+#define GSR_LAUNCH_PB(FF, PP)                                                                                      \
+  preprocess_bwd_kernel<FF, PP><<<nb, PB_THREADS, 0, s>>>(in, cam, g.tiles_touched, g.clamped, radii, g.grad_rows, \
+                                                          g.rec, g.pose_acc, out)
+  const bool pose = out.dL_dviewmatrix != nullptr;
+  if (in.F == 16) { if (pose) GSR_LAUNCH_PB(16, true); else GSR_LAUNCH_PB(16, false); }
+  else            { if (pose) GSR_LAUNCH_PB(32, true); else GSR_LAUNCH_PB(32, false); }
+#undef GSR_LAUNCH_PB
+  if (out.dL_dviewmatrix)
+    pose_finalize_kernel<<<1, 32, 0, s>>>(g.pose_acc, out.dL_dviewmatrix, out.dL_dprojmatrix, out.dL_dcampos);
 }
 
 }  // namespace gsr

@@ -41,6 +41,7 @@ def lib():
         L.gsr_forward.argtypes = [C.POINTER(Params), ALLOC_FN, C.c_void_p, ALLOC_FN, C.c_void_p, ALLOC_FN,
                                   C.c_void_p] + [C.c_void_p] * 17 + [C.POINTER(C.c_int)]
         L.gsr_backward.argtypes = [C.POINTER(Params), C.c_int] + [C.c_void_p] * 29
+        L.gsr_backward_pose.argtypes = [C.POINTER(Params), C.c_int] + [C.c_void_p] * 32
         L.gsr_mark_visible.argtypes = [C.c_int] + [C.c_void_p] * 5
         L.gsr_knn.argtypes = [C.c_int] + [C.c_void_p] * 4
         L.gsr_export_state.argtypes = [C.POINTER(Params), C.c_int] + [C.c_void_p] * 14
@@ -130,8 +131,10 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier,
                                  cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_depth,
                                  dL_dout_color, sh, dL_dout_objects, sh_objs, degree, campos, geomBuffer, R,
-                                 binningBuffer, imageBuffer, debug, out=None):
-    """`out` (extension): dict of preallocated contiguous fp32 tensors keyed like the local `g` below
+                                 binningBuffer, imageBuffer, debug, out=None, camera_grads=False):
+    """`camera_grads` (extension, gsr_backward_pose): also compute dL/dviewmatrix (4,4), dL/dprojmatrix (4,4),
+    dL/dcampos (3,) -- same flat layout as the inputs -- left in `rasterize_gaussians_backward.last_camera_grads`.
+    `out` (extension): dict of preallocated contiguous fp32 tensors keyed like the local `g` below
     (e.g. views into one flat all-reduce bucket, see mapping.GradBucket) that the kernels write
     directly; missing keys are allocated here.
     -> (dL_dmeans2D, dL_dcolors, dL_dobjects, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
@@ -157,12 +160,17 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
         keep = [_f32c(t) for t in (background, means3D, sh, sh_objs, colors, scales, rotations, cov3D_precomp,
                                    viewmatrix, projmatrix, campos)]
         ups = [_f32c(t) for t in (dL_dout_depth, dL_dout_color, dL_dout_objects)]
+        args = [C.byref(prm), int(R), *[_ptr(t) for t in keep], _ptr(radii), _ptr(geomBuffer), _ptr(binningBuffer),
+                _ptr(imageBuffer), *[_ptr(t) for t in ups], _ptr(g["means2D"]), _ptr(g["conic"]), _ptr(g["opacity"]),
+                _ptr(g["depths"]), _ptr(g["colors"]), _ptr(g["objects"]), _ptr(g["means3D"]), _ptr(g["cov3D"]),
+                _ptr(g["sh"]), _ptr(g["scales"]), _ptr(g["rotations"])]
         with torch.cuda.device(dev):
-            rc = lib().gsr_backward(C.byref(prm), int(R), *[_ptr(t) for t in keep], _ptr(radii), _ptr(geomBuffer),
-                                    _ptr(binningBuffer), _ptr(imageBuffer), *[_ptr(t) for t in ups],
-                                    _ptr(g["means2D"]), _ptr(g["conic"]), _ptr(g["opacity"]), _ptr(g["depths"]),
-                                    _ptr(g["colors"]), _ptr(g["objects"]), _ptr(g["means3D"]), _ptr(g["cov3D"]),
-                                    _ptr(g["sh"]), _ptr(g["scales"]), _ptr(g["rotations"]))
+            if camera_grads:
+                cg = (torch.empty((4, 4), **o), torch.empty((4, 4), **o), torch.empty((3,), **o))
+                rc = lib().gsr_backward_pose(*args, *[_ptr(t) for t in cg])
+                rasterize_gaussians_backward.last_camera_grads = cg
+            else:
+                rc = lib().gsr_backward(*args)
         _check(rc)
         if scales is None or scales.numel() == 0:
             g["scales"].zero_()
@@ -222,9 +230,9 @@ STAGES = ("preprocess", "depth_sort_offsets", "binning", "render_fwd", "render_b
 
 def last_forward_stats():
     """-> dict(R, l1_total) of the last forward call on this thread."""
-    c = (C.c_ulonglong * 2)()
+    c = (C.c_ulonglong * 6)()
     _check(lib().gsr_last_forward_stats(c))
-    return dict(R=int(c[0]), l1_total=int(c[1]))
+    return dict(R=int(c[0]), l1_total=int(c[1]), sync_us=int(c[2]), alloc_us=int(c[3]), launch_us=int(c[4]))
 
 
 def set_stage_timing(enable):

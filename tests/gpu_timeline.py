@@ -39,12 +39,14 @@ capi.set_stage_timing(True)
 capi.get_stage_times()
 ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(steps)]
 host = []
+fstats = []
 t00 = time.perf_counter()
 for s in range(steps):
     t0 = time.perf_counter()
     ev[s][0].record()
     res = fwd()
     t1 = time.perf_counter()
+    fstats.append(capi.last_forward_stats())
     ev[s][1].record()
     bwd(res)
     t2 = time.perf_counter()
@@ -56,7 +58,8 @@ st = capi.get_stage_times()
 print(f"P={P} R={res[0]} wall/step {1e3 * wall / steps:.3f} ms")
 for s in range(steps):
     print(f" step {s}: host fwd {1e3 * host[s][0]:.3f} bwd {1e3 * host[s][1]:.3f} ms | gpu fwd "
-          f"{ev[s][0].elapsed_time(ev[s][1]):.3f} bwd {ev[s][1].elapsed_time(ev[s][2]):.3f} ms")
+          f"{ev[s][0].elapsed_time(ev[s][1]):.3f} bwd {ev[s][1].elapsed_time(ev[s][2]):.3f} ms | sync/alloc/launch us "
+          f"{fstats[s]['sync_us']}/{fstats[s]['alloc_us']}/{fstats[s]['launch_us']}")
 print(" stage ms/step:", {k: round(v / steps, 4) for k, v in st.items()}, "sum", round(sum(st.values()) / steps, 4))
 # forward only (render FPS)
 torch.cuda.synchronize()

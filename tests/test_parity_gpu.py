@@ -326,3 +326,124 @@ def test_libtorch_binding_matches_ctypes_binding():
     assert torch.equal(m.mark_visible(d["means3D"], d["viewmatrix"], d["projmatrix"]),
                        capi.mark_visible(d["means3D"], d["viewmatrix"], d["projmatrix"]))
     assert torch.equal(m.distCUDA2(d["means3D"]), capi.distCUDA2(d["means3D"]))
+
+
+# ---- camera-pose gradient (extension; parity unpinned by the reference) -------------------
+def _camera_grad_run(sc, cam, grads):
+    import torch
+    from gsraster_b200 import capi
+    d = h.to_torch(sc, cam)
+    e = torch.empty(0, device="cuda")
+    r = capi.rasterize_gaussians(d["bg"], d["means3D"], e, d["opacities"], d["scales"], d["rotations"], 1.0, e,
+                                 d["viewmatrix"], d["projmatrix"], cam.tanfovx, cam.tanfovy, cam.H, cam.W, d["shs"],
+                                 d["sh_objs"], sc.sh_degree, d["campos"], False, False)
+    gd, gc, go = [torch.from_numpy(g).cuda() for g in grads]
+    g = capi.rasterize_gaussians_backward(d["bg"], d["means3D"], r[4], e, d["scales"], d["rotations"], 1.0, e,
+                                          d["viewmatrix"], d["projmatrix"], cam.tanfovx, cam.tanfovy, gd, gc, d["shs"], go,
+                                          d["sh_objs"], sc.sh_degree, d["campos"], r[6], r[0], r[7], r[8], False,
+                                          camera_grads=True)
+    dV, dPV, dC = [t.double().cpu().numpy() for t in capi.rasterize_gaussians_backward.last_camera_grads]
+    return r, g, dV, dPV, dC
+
+
+@pytest.mark.parametrize("P,W,H,mul", [(20_000, 320, 256, 2.0), (1_000_000, 1280, 1024, 1.0)])
+def test_camera_gradient_rigid_motion_identity(P, W, H, mul):
+    """SH degree 0: L(V G, PV G) == L with every Gaussian moved by G (p -> G p, Sigma -> R Sigma R^T), so for any
+    twist (omega, t) the directional derivative through the camera gradients must equal the one through
+    dL_dmeans3D / dL_dcov3D. Second case = BASELINE config 5 size (1M Gaussians)."""
+    sc = scenes.make_scene(P, sh_degree=0, F=16, seed=91, W=W, H=H, scale_mul=mul)
+    cam = scenes.make_camera(W, H, 2)
+    grads = scenes.make_upstream_grads(W, H, 16, seed=5)
+    grads = tuple(g * (W * H) for g in grads)  # O(1) upstream gradients
+    r, g, dV, dPV, dC = _camera_grad_run(sc, cam, grads)
+    assert np.abs(dC).max() == 0  # colour does not depend on the view direction at degree 0
+    dmean = g[4].double().cpu().numpy()
+    dcov = g[5].double().cpu().numpy()
+    # reconstruct Sigma (6) per Gaussian in double from scale / rotation (forward.cu:122-168 convention)
+    q = sc.rotations.astype(np.float64)
+    x, y, z, w = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+    Rm = np.stack([1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y),
+                   2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x),
+                   2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)], 1).reshape(-1, 3, 3)
+    S2 = sc.scales.astype(np.float64) ** 2
+    Sigma = np.einsum("nij,nj,nkj->nik", Rm, S2, Rm)
+    dS = np.zeros_like(Sigma)  # dL/dSigma as a full symmetric-matrix gradient: off-diagonals split in two
+    dS[:, 0, 0], dS[:, 1, 1], dS[:, 2, 2] = dcov[:, 0], dcov[:, 3], dcov[:, 5]
+    dS[:, 0, 1] = dS[:, 1, 0] = 0.5 * dcov[:, 1]
+    dS[:, 0, 2] = dS[:, 2, 0] = 0.5 * dcov[:, 2]
+    dS[:, 1, 2] = dS[:, 2, 1] = 0.5 * dcov[:, 4]
+    V = cam.viewmatrix.T.astype(np.float64)    # math matrices: flat index 4c + r
+    PV = cam.projmatrix.T.astype(np.float64)
+    gV, gPV = dV.T, dPV.T                       # dL/dV[r][c]
+    p = sc.means3D.astype(np.float64)
+    rng = np.random.default_rng(0)
+    for _ in range(4):
+        om, t = rng.normal(size=3), rng.normal(size=3)
+        K = np.array([[0, -om[2], om[1]], [om[2], 0, -om[0]], [-om[1], om[0], 0]])
+        Gd = np.zeros((4, 4)); Gd[:3, :3] = K; Gd[:3, 3] = t  # d/d eps of G = exp(eps * twist) at 0
+        cam_side = (gV * (V @ Gd)).sum() + (gPV * (PV @ Gd)).sum()
+        dp = p @ K.T + t
+        dSig = K @ Sigma + Sigma @ K.T
+        gauss_side = (dmean * dp).sum() + (dS * dSig).sum()
+        assert abs(cam_side - gauss_side) <= 2e-3 * max(abs(cam_side), abs(gauss_side), 1e-6), (cam_side, gauss_side)
+
+
+def test_camera_centre_gradient_finite_differences():
+    """campos only enters through the SH view direction (forward.cu:25-27): colours are smooth in it and the
+    geometry does not move, so central differences of the forward pass are clean."""
+    import torch
+    from gsraster_b200 import capi
+    W, H, P = 320, 256, 20_000
+    sc = scenes.make_scene(P, sh_degree=3, F=16, seed=92, W=W, H=H, scale_mul=2.0)
+    sc.shs[:, 1:, :] *= 6.0  # make the view-dependent part matter
+    cam = scenes.make_camera(W, H, 1)
+    grads = tuple(g * (W * H) for g in scenes.make_upstream_grads(W, H, 16, seed=6))
+    r, g, dV, dPV, dC = _camera_grad_run(sc, cam, grads)
+    d = h.to_torch(sc, cam)
+    e = torch.empty(0, device="cuda")
+    gc = torch.from_numpy(grads[1]).cuda().double()
+
+    def loss(c):
+        rr = capi.rasterize_gaussians(d["bg"], d["means3D"], e, d["opacities"], d["scales"], d["rotations"], 1.0, e,
+                                      d["viewmatrix"], d["projmatrix"], cam.tanfovx, cam.tanfovy, H, W, d["shs"],
+                                      d["sh_objs"], 3, torch.tensor(c, dtype=torch.float32, device="cuda"), False, False)
+        return float((rr[2].double() * gc).sum())
+
+    c0 = cam.campos.astype(np.float64)
+    for k in range(3):
+        eps = 2e-2
+        cp, cm = c0.copy(), c0.copy()
+        cp[k] += eps; cm[k] -= eps
+        fd = (loss(cp) - loss(cm)) / (2 * eps)
+        assert abs(fd - dC[k]) <= 2e-2 * max(abs(fd), np.abs(dC).max()), (k, fd, dC[k])
+
+
+def test_tracking_autograd_wrapper():
+    import torch
+    from diff_gaussian_rasterization import GaussianRasterizationSettings
+    from gsraster_b200 import tracking
+    W, H, P = 160, 128, 5_000
+    sc = scenes.make_scene(P, sh_degree=1, F=16, seed=93, W=W, H=H, scale_mul=3.0)
+    cam = scenes.make_camera(W, H, 0)
+    d = h.to_torch(sc, cam)
+    rs = GaussianRasterizationSettings(H, W, cam.tanfovx, cam.tanfovy, d["bg"], 1.0, d["viewmatrix"], d["projmatrix"],
+                                       1, d["campos"], False, False)
+    V = d["viewmatrix"].clone().requires_grad_(True)
+    PV = d["projmatrix"].clone().requires_grad_(True)
+    c = d["campos"].clone().requires_grad_(True)
+    depth, color, radii, objects, used = tracking.rasterize_with_camera_grads(
+        V, PV, c, d["means3D"], d["shs"], d["sh_objs"], d["opacities"], d["scales"], d["rotations"], rs)
+    (color.sum() + 0.1 * depth.sum()).backward()
+    assert V.grad.shape == (4, 4) and PV.grad.shape == (4, 4) and c.grad.shape == (3,)
+    assert float(V.grad.abs().sum()) > 0 and float(PV.grad.abs().sum()) > 0 and float(c.grad.abs().sum()) > 0
+    assert float(V.grad[:, 3].abs().sum()) == 0  # flat index 4c + 3 == row 3 of V: unused by the rasterizer
+
+
+@pytest.mark.skipif(not os.path.exists(h.REF_KNN_LIB), reason="oracle/_ref knn not shipped")
+def test_knn_config5_5M_points():
+    import torch
+    from gsraster_b200 import capi
+    pts = scenes.make_points(5_000_000, seed=55)
+    mine = capi.distCUDA2(torch.from_numpy(pts).cuda())
+    ref = h.run_ref_knn(pts)
+    assert torch.equal(mine.view(torch.int32), ref.view(torch.int32))
