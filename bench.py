@@ -35,7 +35,7 @@ UNIT = "iters/s"
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="mine", choices=["mine", "reference"])
     ap.add_argument("--P", type=int, default=1_000_000)
@@ -71,7 +71,7 @@ class ClockSampler:
             return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
@@ -205,13 +205,13 @@ def run_mine(args, rank, world, local_rank):
                  n_blend=cp["blended"], n_eval_bwd=int(st["n_contrib"].to(torch.int64).sum()),
                  warp_blended=cp["warp_blended"], l1_total=l1_total)
     del st
+    clocks = ClockSampler(local_rank)
+    clocks.start()  # started a few steps early: nvidia-smi needs tens of ms before its first sample
     for _ in range(3):  # settle the caching allocator again after the statistics pass (untimed, in addition to W)
         step()
     sync_all()
 
     # ---- timed region 1: inputs resident in HBM ----
-    clocks = ClockSampler(local_rank)
-    clocks.start()
     instrument = not os.environ.get("GSR_BENCH_NO_STAGE_TIMING")
     capi.set_stage_timing(instrument)
     capi.get_stage_times()
