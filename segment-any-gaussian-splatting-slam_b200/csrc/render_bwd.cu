@@ -80,7 +80,7 @@ __device__ __forceinline__ float rcp_approx(float x) {
 }
 
 template <int F>
-__global__ void __launch_bounds__(256, (F == 16 ? 2 : 1))
+__global__ void __launch_bounds__(256, (F == 16 ? 3 : 1))
 render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
                   const float4* __restrict__ rec, const float* __restrict__ feats, int W, int H,
                   const float* __restrict__ bg, const float* __restrict__ final_T,
