@@ -14,7 +14,7 @@ constexpr int TILE_X = 16, TILE_Y = 16;  // fixed by parity: reference config.h:
 //
 // geometry (per Gaussian):
 //   rec           4 x float4 = 64 B   {px, py, conic.a, conic.b} {conic.c, opacity, hx, hy}
-//                                      {depth, r, g, b} {cov_zx, cov_yz, 0, 0} -- the record the blend kernels
+//                                      {depth, r, g, b} {cov_zx, cov_yz, index bits, 0} -- the record the blend kernels
 //                                      stage by TMA; (hx, hy) = half extents of the axis-aligned box around the
 //                                      alpha >= 1/255 ellipse (conservative), negative if opacity can never reach it
 //   tiles_touched u32, rect u32 (x0 | y0<<8 | x1<<16 | y1<<24), clamped u8 (bit c = channel c clamped)
@@ -63,6 +63,8 @@ struct ImageState {
 };
 struct BinState {
   uint32_t* point_list;
+  uint32_t* hitw;       // blend masks written by the forward blend: for tile t, group g of 32 list entries and warp w
+                        // (8x4 pixel block) word [((range.x >> 5) + t + g) * 8 + w], bit i = the warp blended entry 32 g + i
   uint2* l1;            // {rect, idx}
   uint32_t* warp_cnt;   // [NS][NW]
 };
@@ -122,10 +124,12 @@ inline size_t sat_ints(int gx, int gy) {
   const SuperGrid sg = super_grid(gx, gy);
   return (size_t)(gx + 1) * (gy + 1) + (size_t)(sg.sgx + 1) * (sg.sgy + 1);
 }
-// point_list comes first: the backward pass calls this with l1_total = nw_ns = 0.
+inline size_t hitw_words(size_t R) { return ((R >> 5) + 255 * 255 + 2) * 8; }  // any grid up to 255 x 255 tiles
+// point_list and hitw come first: the backward pass calls this with l1_total = nw_ns = 0.
 inline size_t bin_from_chunk(char* chunk, size_t R, size_t l1_total, size_t nw_ns, BinState& b) {
   char* p = chunk;
   carve(p, b.point_list, R ? R : 1);
+  carve(p, b.hitw, hitw_words(R));
   carve(p, b.l1, l1_total ? l1_total : 1);
   carve(p, b.warp_cnt, nw_ns ? nw_ns : 1);
   return (size_t)(p - chunk) + 256;

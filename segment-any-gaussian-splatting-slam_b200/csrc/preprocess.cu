@@ -164,7 +164,7 @@ preprocess_kernel(const FwdInputs in, const Cam cam, float4* __restrict__ rec, u
     rec[REC4 * (size_t)idx + 0] = make_float4(point_image.x, point_image.y, conic.x, conic.y);
     rec[REC4 * (size_t)idx + 1] = make_float4(conic.z, opac, hx, hy);
     rec[REC4 * (size_t)idx + 2] = make_float4(p_view.z, rgb[0], rgb[1], rgb[2]);
-    rec[REC4 * (size_t)idx + 3] = make_float4(czx, cyz, 0.f, 0.f);
+    rec[REC4 * (size_t)idx + 3] = make_float4(czx, cyz, __uint_as_float((uint32_t)idx), 0.f);
     my_radius_i = (int)my_radius;
     touched = (uint32_t)((y1 - y0) * (x1 - x0));
     rect[idx] = (uint32_t)x0 | ((uint32_t)y0 << 8) | ((uint32_t)x1 << 16) | ((uint32_t)y1 << 24);

@@ -31,68 +31,177 @@
 
 namespace gsr {
 
-// instances per staged batch (static shared memory stays below 48 KB at F = 32)
-template <int F> __host__ __device__ constexpr int batch_size() { return F == 16 ? 128 : 64; }
+// ---------------------------------------------------------------------------------------------
+// Pixel reduction on the tensor cores. For one warp (an 8x4 pixel block, lane = pixel) and one
+// Gaussian g the 12+F sums over the 32 pixels are
+//   raw[g][c] = sum_p A[g][p] * B[p][c]
+// with A = q (columns 0..7) or w (columns 8..) and B a per-WARP constant matrix:
+//   columns 0..7   {1, u, v, u u, u v, v v, 0, 0}                       (u, v = pixel offset from the
+//   columns 8..15  dL/dD {1, u, v}, dL/dC {r, g, b}, 0, 0                block centre: exact in tf32)
+//   columns 16..   dL/dO[channel]
+// i.e. a (16 Gaussians x 32 pixels) x (32 pixels x 16+F) product per 16 hits of the warp:
+// mma.sync m16n8k8 tf32 with the 3xTF32 split (hi*hi + lo*hi + hi*lo, fp32 accumulate), which keeps
+// fp32-level accuracy. The hit path only stores w and q of its pixel into the warp's slot buffer;
+// every 16 hits the warp runs the product, transposes the result through shared memory and
+// shifts the raw moments from the block centre to the Gaussian centre (dx = gx' - u):
+//   sum q dx = gx' S1 - Su,  sum q dx dx = gx'^2 S1 - 2 gx' Su + Suu, ...
+// before ONE vector red.global.add.v4.f32 per 4 row entries. This replaces the 32 shuffles + ~100
+// select/add instructions per (warp, Gaussian) of a shuffle butterfly.
+//
+// Which (warp, instance) pairs blend is known from the forward pass (BinState::hitw, one bit per
+// (warp, instance)): each warp walks only its own hits, so the loop body is branch-free and the
+// 60 % of (warp, instance) iterations that the forward pass rejected cost nothing here.
+// ---------------------------------------------------------------------------------------------
+constexpr int SLOTS = 16;    // Gaussians per product
+constexpr int WSTRIDE = 36;  // slot-row stride (floats): A-fragment loads are bank-conflict free
 
 template <int F>
+struct BwdCfg {
+  static constexpr int BB = (F == 16) ? 128 : 64;       // instances per staged batch
+  static constexpr int NT = 2 + F / 8;                  // 8-column output tiles
+  static constexpr int NC = 8 * NT;                     // output columns
+  static constexpr int NBW = (NT - 1) * 8;              // B-fragment registers of the w side per lane
+  static constexpr int DSTRIDE = (F == 16) ? 40 : 56;   // result-tile row stride (floats)
+  static constexpr int ROW = (F == 16) ? 32 : 64;       // gradient row (floats)
+};
+
+template <int F>
+struct BwdRow {  // one staged instance: 64-byte record + feature row
+  float4 rec[REC4];
+  float4 feat[F / 4];
+};
+template <int F>
 struct BwdSmem {
-  float4 rec[2][batch_size<F>()][REC4];
-  float4 feat[2][batch_size<F>()][F / 4];
-  uint32_t id[2][batch_size<F>()];
+  BwdRow<F> row[2][BwdCfg<F>::BB];
+  float4 meta[8][SLOTS];                   // per warp, per slot: {Gaussian index bits, gx', gy', -}
+  float wq[8][2 * SLOTS * WSTRIDE];        // per warp: w rows, then q rows; re-used for the result tile
+  float bfrag[8][8 + BwdCfg<F>::NBW][32];  // per warp: B fragments [register][lane]: 8 of the q side, then the w side
   uint64_t bar[2];
   uint32_t max_contrib;
 };
+static_assert(SLOTS * BwdCfg<16>::DSTRIDE <= 2 * SLOTS * WSTRIDE, "result tile must fit");
+static_assert(SLOTS * BwdCfg<32>::DSTRIDE <= 2 * SLOTS * WSTRIDE, "result tile must fit");
 
 constexpr unsigned FULL = 0xffffffffu;
 
-// Select-free butterfly reduce over N = 16 or 32 slots. Precondition: slot s of lane l holds the
-// partial sum of logical index s ^ (l & (N-1)). Returns, in every lane l, the warp total of logical
-// index l & (N-1).
-template <int N>
-__device__ __forceinline__ float warp_permuted_reduce(float (&v)[N]) {
-#pragma unroll
-  for (int B = N / 2; B >= 1; B >>= 1) {
-#pragma unroll
-    for (int s = 0; s < B; s++) v[s] += __shfl_xor_sync(FULL, v[s + B], B);
-  }
-  if (N == 16) v[0] += __shfl_xor_sync(FULL, v[0], 16);
-  return v[0];
-}
-// Transpose-reduce with selects for values that cannot be produced in permuted order:
-// v[0..15] per lane -> every lane l returns the warp total of v[l & 15].
-__device__ __forceinline__ float warp_transpose_reduce16(float (&v)[16], int lane) {
-#pragma unroll
-  for (int B = 8; B >= 1; B >>= 1) {
-    const bool up = lane & B;
-#pragma unroll
-    for (int i = 0; i < B; i++) {
-      const float send = up ? v[i] : v[i + B];
-      const float keep = up ? v[i + B] : v[i];
-      v[i] = keep + __shfl_xor_sync(FULL, send, B);
-    }
-  }
-  return v[0] + __shfl_xor_sync(FULL, v[0], 16);
-}
 __device__ __forceinline__ float rcp_approx(float x) {
   float r;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
   return r;
 }
+// x = hi + lo with hi representable in tf32; lo is passed as raw fp32 bits (the MMA reads its top 19 bits)
+__device__ __forceinline__ void tf32_split(float x, uint32_t& hi, uint32_t& lo) {
+  hi = __float_as_uint(x) & 0xffffe000u;  // truncation (1 LOP3; cvt.rna.tf32 is a 4-instruction sequence in SASS)
+  lo = __float_as_uint(x - __uint_as_float(hi));
+}
+__device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+// (ns x 32 pixels) x (32 pixels x NC) on the tensor cores, then one row update per slot.
+template <int F>
+__device__ __forceinline__ void flush_slots(float* __restrict__ wbuf, const float4* __restrict__ meta,
+                                            const float (*__restrict__ bfrag)[32], int ns, int lane,
+                                            float* __restrict__ grad_rows) {
+  using Cfg = BwdCfg<F>;
+  constexpr int NT = Cfg::NT, NC = Cfg::NC, DS = Cfg::DSTRIDE, ROW = Cfg::ROW;
+  const int gid = lane >> 2, tig = lane & 3;
+  const float* qbuf = wbuf + SLOTS * WSTRIDE;
+  __syncwarp();
+  float acc[NT][4];
+#pragma unroll
+  for (int nt = 0; nt < NT; nt++) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
+#pragma unroll
+  for (int ks = 0; ks < 4; ks++) {
+    const int o0 = gid * WSTRIDE + 8 * ks + tig, o1 = o0 + 4;
+    uint32_t ah[4], al[4];
+    tf32_split(qbuf[o0], ah[0], al[0]);
+    tf32_split(qbuf[o0 + 8 * WSTRIDE], ah[1], al[1]);
+    tf32_split(qbuf[o1], ah[2], al[2]);
+    tf32_split(qbuf[o1 + 8 * WSTRIDE], ah[3], al[3]);
+    // q side: {1, u, v, uu, uv, vv, 0, 0}[gid] at pixels (tig, ks) and (tig + 4, ks): exact in tf32
+    const uint32_t bq[2] = {__float_as_uint(bfrag[2 * ks][lane]), __float_as_uint(bfrag[2 * ks + 1][lane])};
+    mma_tf32(acc[0], ah, bq[0], bq[1]);
+    mma_tf32(acc[0], al, bq[0], bq[1]);
+    tf32_split(wbuf[o0], ah[0], al[0]);
+    tf32_split(wbuf[o0 + 8 * WSTRIDE], ah[1], al[1]);
+    tf32_split(wbuf[o1], ah[2], al[2]);
+    tf32_split(wbuf[o1 + 8 * WSTRIDE], ah[3], al[3]);
+#pragma unroll
+    for (int nt = 1; nt < NT; nt++) {
+      uint32_t b0h, b0l, b1h, b1l;
+      tf32_split(bfrag[8 + ((nt - 1) * 4 + ks) * 2 + 0][lane], b0h, b0l);
+      tf32_split(bfrag[8 + ((nt - 1) * 4 + ks) * 2 + 1][lane], b1h, b1l);
+      mma_tf32(acc[nt], ah, b0h, b1h);
+      mma_tf32(acc[nt], al, b0h, b1h);
+      mma_tf32(acc[nt], ah, b0l, b1l);
+    }
+  }
+  __syncwarp();  // all fragment loads done: the slot buffer becomes the result tile
+  float* const D = wbuf;
+#pragma unroll
+  for (int nt = 0; nt < NT; nt++) {
+    *reinterpret_cast<float2*>(&D[gid * DS + 8 * nt + 2 * tig]) = make_float2(acc[nt][0], acc[nt][1]);
+    *reinterpret_cast<float2*>(&D[(gid + 8) * DS + 8 * nt + 2 * tig]) = make_float2(acc[nt][2], acc[nt][3]);
+  }
+  __syncwarp();
+  // lane -> (slot, half of the NC columns); half 0 shifts the raw moments to the Gaussian centre
+  const int slot = lane >> 1, half = lane & 1;
+  if (slot < ns) {
+    const float4 m = meta[slot];
+    float v[NC / 2];
+#pragma unroll
+    for (int i = 0; i < NC / 8; i++) {
+      const float4 t = *reinterpret_cast<const float4*>(&D[slot * DS + half * (NC / 2) + 4 * i]);
+      v[4 * i + 0] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
+    }
+    if (half == 0) {
+      const float gx = m.y, gy = m.z;
+      const float S1 = v[0], Su = v[1], Sv = v[2], Suu = v[3], Suv = v[4], Svv = v[5];
+      const float Wd = v[8], Wdu = v[9], Wdv = v[10], Wr = v[11], Wg = v[12], Wb = v[13];
+      const float Qx = fmaf(gx, S1, -Su), Qy = fmaf(gy, S1, -Sv);
+      v[0] = Qx;
+      v[1] = Qy;
+      v[2] = fmaf(gx, Qx, fmaf(-gx, Su, Suu));                // gx^2 S1 - 2 gx Su + Suu
+      v[3] = fmaf(gy, Qx, fmaf(-gx, Sv, Suv));                // gx gy S1 - gy Su - gx Sv + Suv
+      v[4] = fmaf(gy, Qy, fmaf(-gy, Sv, Svv));
+      v[5] = fmaf(gx, Wd, -Wdu);
+      v[6] = fmaf(gy, Wd, -Wdv);
+      v[7] = S1;
+      v[8] = Wd;
+      v[9] = Wr; v[10] = Wg; v[11] = Wb;
+#pragma unroll
+      for (int i = 16; i < NC / 2; i++) v[i - 4] = v[i];      // F = 32: features 0..7 follow the 12 specials
+    }
+    float* row = grad_rows + (size_t)__float_as_uint(m.x) * ROW + (half ? NC / 2 - 4 : 0);
+#pragma unroll
+    for (int i = 0; i < NC / 8; i++)
+      if (half || i + 1 < NC / 8) red_add_v4(row + 4 * i, v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+  }
+  __syncwarp();  // result tile consumed before the next hit overwrites the slot buffer
+}
 
 template <int F>
-__global__ void __launch_bounds__(256, (F == 16 ? 3 : 1))
+__global__ void __launch_bounds__(256, (F == 16 ? 2 : 1))
 render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
-                  const float4* __restrict__ rec, const float* __restrict__ feats, int W, int H,
-                  const float* __restrict__ bg, const float* __restrict__ final_T,
-                  const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix_depth,
-                  const float* __restrict__ dL_dpix, const float* __restrict__ dL_dpix_obj,
-                  float* __restrict__ grad_rows) {
-  constexpr int ROW = (F == 16) ? 32 : 64;
-  constexpr int BB = batch_size<F>();
-  __shared__ __align__(128) BwdSmem<F> sm;
+                  const uint32_t* __restrict__ hitw, const float4* __restrict__ rec,
+                  const float* __restrict__ feats, int W, int H, const float* __restrict__ bg,
+                  const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib,
+                  const float* __restrict__ dL_dpix_depth, const float* __restrict__ dL_dpix,
+                  const float* __restrict__ dL_dpix_obj, float* __restrict__ grad_rows) {
+  using Cfg = BwdCfg<F>;
+  constexpr int BB = Cfg::BB;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  BwdSmem<F>& sm = *reinterpret_cast<BwdSmem<F>*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int px = blockIdx.x * TILE_X + (warp & 1) * 8 + (lane & 7);
-  const int py = blockIdx.y * TILE_Y + (warp >> 1) * 4 + (lane >> 3);
+  const int bx0 = blockIdx.x * TILE_X + (warp & 1) * 8, by0 = blockIdx.y * TILE_Y + (warp >> 1) * 4;
+  const int px = bx0 + (lane & 7), py = by0 + (lane >> 3);
   const bool inside = px < W && py < H;
   const float pixx = (float)px, pixy = (float)py;
   const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
@@ -117,6 +226,8 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   const int todo = (int)sm.max_contrib;
   const int nbatch = (todo + BB - 1) / BB;
   const uint32_t list_end = range.x + (uint32_t)todo;  // exclusive
+  // a pair is live for this pixel iff its list position < n_contrib  <=>  walk index >= thr
+  const int thr = todo - (int)last_contributor;
 
   constexpr uint32_t ROW_BYTES = 16 * REC4 + 4 * F;
   auto issue = [&](int b) {
@@ -125,127 +236,143 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     if (tid == 0) mbar_arrive_expect_tx(&sm.bar[st], (uint32_t)cnt * ROW_BYTES);
     if (tid < cnt) {
       const uint32_t id = point_list[list_end - 1 - (uint32_t)(b * BB + tid)];
-      sm.id[st][tid] = id;
-      tma_load_1d(&sm.rec[st][tid][0], rec + REC4 * (size_t)id, 16 * REC4, &sm.bar[st]);
-      tma_load_1d(&sm.feat[st][tid][0], feats + (size_t)id * F, 4 * F, &sm.bar[st]);
+      tma_load_1d(&sm.row[st][tid].rec[0], rec + REC4 * (size_t)id, 16 * REC4, &sm.bar[st]);
+      tma_load_1d(&sm.row[st][tid].feat[0], feats + (size_t)id * F, 4 * F, &sm.bar[st]);
     }
   };
+  // Forward blend masks of this warp (see BinState::hitw): batch b walks list positions p_top, p_top - 1, ...;
+  // lane l holds the word of group (p_top >> 5) - l.
+  const uint32_t* const hw = hitw + (size_t)((range.x >> 5) + blockIdx.y * gridDim.x + blockIdx.x) * 8 + warp;
+  auto load_masks = [&](int b) -> uint32_t {
+    const int g = ((todo - 1 - b * BB) >> 5) - lane;
+    return (b < nbatch && lane <= BB / 32 && g >= 0) ? __ldg(hw + (size_t)g * 8) : 0u;
+  };
+  uint32_t wv_next = load_masks(0);
+  if (nbatch > 0) issue(0);
 
+  // ---- per-pixel upstream gradients (lane = pixel) ----
   const float T_final = inside ? final_T[pix_id] : 0.f;
   float T = T_final;
-  float dpx[3], dpo[F], dpo_perm[F], dpd = 0.f;
+  float dpx[3], dpo[F], dpd = 0.f;
 #pragma unroll
   for (int c = 0; c < 3; c++) dpx[c] = inside ? dL_dpix[c * HW + pix_id] : 0.f;
 #pragma unroll
-  for (int c = 0; c < F; c++) {
-    dpo[c] = inside ? dL_dpix_obj[c * HW + pix_id] : 0.f;
-    dpo_perm[c] = inside ? dL_dpix_obj[(size_t)(c ^ (lane & (F - 1))) * HW + pix_id] : 0.f;
-  }
+  for (int c = 0; c < F; c++) dpo[c] = inside ? dL_dpix_obj[c * HW + pix_id] : 0.f;
   if (inside) dpd = dL_dpix_depth[pix_id];
   // suffix sum S, seeded with the background term T_final * (<bg, dL/dC> + 15 dL/dD)
   // (backward.cu:607-610, 648): it always appears as (S + that) / (1 - alpha).
   float S = T_final * (bg[0] * dpx[0] + bg[1] * dpx[1] + bg[2] * dpx[2] + 15.f * dpd);
-  const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
 
-  if (nbatch > 0) issue(0);
-  __syncthreads();  // sm.id of batch 0 visible to all warps
+  // ---- B matrix of the warp, stored in mma.m16n8k8 fragment order: element (pixel p, column c) belongs to
+  //      lane 4 (c % 8) + (x & 3), register ((c / 8) * 4 + y) * 2 + (x >> 2), p = (x, y) ----
+  {
+    const int x = lane & 7, y = lane >> 3;
+    const float u = (float)x - 3.5f, v = (float)y - 1.5f;
+    float (*bf)[32] = sm.bfrag[warp];
+    const int rbase = y * 2 + (x >> 2), lbase = x & 3;
+    const float colq[8] = {1.f, u, v, u * u, u * v, v * v, 0.f, 0.f};
+    const float col8[8] = {dpd, dpd * u, dpd * v, dpx[0], dpx[1], dpx[2], 0.f, 0.f};
+#pragma unroll
+    for (int c = 0; c < 8; c++) {
+      bf[rbase][4 * c + lbase] = colq[c];
+      bf[8 + rbase][4 * c + lbase] = col8[c];
+    }
+#pragma unroll
+    for (int c = 0; c < F; c++) bf[8 + (1 + c / 8) * 8 + rbase][4 * (c % 8) + lbase] = dpo[c];
+  }
+  float* const wbuf = sm.wq[warp];
+  const float cx = (float)bx0 + 3.5f, cy = (float)by0 + 1.5f;  // block centre
+  int ns = 0;  // filled slots (warp-uniform)
+  float* wp = wbuf + lane;  // this lane's w entry of slot ns; q follows SLOTS rows later
+
+  __syncthreads();  // B fragments visible
   for (int b = 0; b < nbatch; b++) {
     const int st = b & 1;
     if (b + 1 < nbatch) issue(b + 1);
     mbar_wait(&sm.bar[st], (uint32_t)(b >> 1) & 1u);
-    const int cnt = min(BB, todo - b * BB);
-    for (int j = 0; j < cnt; j++) {
-      const uint32_t pos = (uint32_t)(todo - 1 - (b * BB + j));  // 0-based position in the tile's list
-      const float4 r0 = sm.rec[st][j][0];  // px, py, conic a, conic b
-      const float4 r1 = sm.rec[st][j][1];  // conic c, opacity, box half extents hx, hy
-      const float dx = r0.x - pixx, dy = r0.y - pixy;
-      // conservative alpha >= 1/255 box (preprocess.cu): outside it the pair was skipped by the forward pass
-      const bool inbox = pos < last_contributor && fabsf(dx) <= r1.z && fabsf(dy) <= r1.w;
-      if (!__any_sync(FULL, inbox)) continue;
-      const float power = -0.5f * (r0.z * dx * dx + r1.x * dy * dy) - r0.w * dx * dy;
-      const bool cand = inbox && power <= 0.0f;
-      if (!__any_sync(FULL, cand)) continue;
-      float G = expf(power);
-      float alpha = min(0.99f, r1.y * G);
-      const bool hit = cand && alpha >= 1.0f / 255.0f;
-      if (!__any_sync(FULL, hit)) continue;
-
-      // Lanes without a hit run the same instructions with G = alpha = 0, which zeroes every
-      // partial sum below and leaves T and S unchanged (hit rate inside such a warp is ~95 %).
-      G = hit ? G : 0.f;
-      alpha = hit ? alpha : 0.f;
-      const float4 r2 = sm.rec[st][j][2];  // depth, r, g, b
-      const float inv1ma = rcp_approx(1.f - alpha);
-      T = T * inv1ma;
-      const float w = alpha * T;  // d(out channel) / d(channel value of this Gaussian)
-      const float4 r3 = sm.rec[st][j][3];  // cov_zx, cov_yz
-      const float a = r0.z, bq = r0.w, c = r1.x, covzx = r3.x, covyz = r3.y;
-      const float cza = covzx * a + covyz * bq;
-      const float czb = covzx * bq + covyz * c;
-      const float depth = r2.x - cza * dx - czb * dy;
-      float E = depth * dpd;
-      E = fmaf(r2.y, dpx[0], E);
-      E = fmaf(r2.z, dpx[1], E);
-      E = fmaf(r2.w, dpx[2], E);
-      float vf[F];
+    const int thr_b = thr - b * BB;
+    const uint32_t wv = wv_next;
+    wv_next = load_masks(b + 1);
+    const int p_top = todo - 1 - b * BB;
+#pragma unroll 1
+    for (int k = 0; k < BB / 32; k++) {
+      const int p_hi = p_top - 32 * k;  // list position of walk index 32 k of this batch
+      if (p_hi < 0) break;
+      const int i1 = (p_top >> 5) - (p_hi >> 5);
+      const uint32_t W1 = __shfl_sync(FULL, wv, i1), W0 = __shfl_sync(FULL, wv, i1 + 1);
+      // bit l of m = mask bit of position p_hi - l
+      uint32_t m = __brev(__funnelshift_rc(W0, W1, (p_hi & 31) + 1));
+      while (m) {
+        const int j = 32 * k + __ffs(m) - 1;
+        m &= m - 1;
+        const BwdRow<F>& R = sm.row[st][j];
+        const float4 r0 = R.rec[0];  // px, py, conic a, conic b
+        const float4 r1 = R.rec[1];  // conic c, opacity, box half extents hx, hy
+        const float4 r2 = R.rec[2];  // depth, r, g, b
+        const float4 r3 = R.rec[3];  // cov_zx, cov_yz, Gaussian index bits
+        const float dx = r0.x - pixx, dy = r0.y - pixy;
+        const float power = -0.5f * (r0.z * dx * dx + r1.x * dy * dy) - r0.w * dx * dy;
+        float G = expf(power);
+        float alpha = min(0.99f, r1.y * G);
+        // the forward pass blended this pair iff (forward.cu:365-379, backward.cu:549-551):
+        const bool hit = j >= thr_b && power <= 0.0f && alpha >= 1.0f / 255.0f;
+        // Lanes without a hit run the same instructions with G = alpha = 0, which zeroes w and q
+        // and leaves T and S unchanged.
+        G = hit ? G : 0.f;
+        alpha = hit ? alpha : 0.f;
+        const float inv1ma = rcp_approx(1.f - alpha);
+        T = T * inv1ma;
+        const float w = alpha * T;  // d(out channel) / d(channel value of this Gaussian)
+        const float cza = r3.x * r0.z + r3.y * r0.w;
+        const float czb = r3.x * r0.w + r3.y * r1.x;
+        const float depth = r2.x - cza * dx - czb * dy;
+        float E0 = depth * dpd, E1 = r2.y * dpx[0], E2 = r2.z * dpx[1], E3 = r2.w * dpx[2];
 #pragma unroll
-      for (int q = 0; q < F / 4; q++) {
-        const float4 f4 = sm.feat[st][j][q];
-        E = fmaf(f4.x, dpo[4 * q + 0], E);
-        E = fmaf(f4.y, dpo[4 * q + 1], E);
-        E = fmaf(f4.z, dpo[4 * q + 2], E);
-        E = fmaf(f4.w, dpo[4 * q + 3], E);
-      }
-#pragma unroll
-      for (int k = 0; k < F; k++) vf[k] = w * dpo_perm[k];
-      const float dL_da = T * E - S * inv1ma;
-      S = fmaf(w, E, S);
-      const float wd = w * dpd;
-      const float q = G * dL_da;
-      const float qx = q * dx, qy = q * dy;
-      float v[16];
-      v[0] = qx;
-      v[1] = qy;
-      v[2] = qx * dx;
-      v[3] = qx * dy;
-      v[4] = qy * dy;
-      v[5] = wd * dx;
-      v[6] = wd * dy;
-      v[7] = q;
-      v[8] = wd;
-      v[9] = w * dpx[0];
-      v[10] = w * dpx[1];
-      v[11] = w * dpx[2];
-      v[12] = v[13] = v[14] = v[15] = 0.f;
-
-      const uint32_t gid = sm.id[st][j];
-      float* row = grad_rows + (size_t)gid * ROW;
-      const float sf = warp_permuted_reduce<F>(vf);        // lane l: feature channel l & (F-1)
-      const float ss = warp_transpose_reduce16(v, lane);   // lane l: special l & 15
-      if constexpr (F == 16) {
-        // one RED: lanes 0..15 -> features, lanes 16..27 -> the 12 specials
-        if (lane < 28) atomicAdd(row + (lane < 16 ? 12 + lane : lane - 16), lane < 16 ? sf : ss);
-      } else {
-        atomicAdd(row + 12 + lane, sf);
-        if (lane < 12) atomicAdd(row + lane, ss);
+        for (int q4 = 0; q4 < F / 4; q4++) {
+          const float4 f4 = R.feat[q4];
+          E0 = fmaf(f4.x, dpo[4 * q4 + 0], E0);
+          E1 = fmaf(f4.y, dpo[4 * q4 + 1], E1);
+          E2 = fmaf(f4.z, dpo[4 * q4 + 2], E2);
+          E3 = fmaf(f4.w, dpo[4 * q4 + 3], E3);
+        }
+        const float E = (E0 + E1) + (E2 + E3);
+        const float dL_da = T * E - S * inv1ma;
+        S = fmaf(w, E, S);
+        wp[0] = w;
+        wp[SLOTS * WSTRIDE] = G * dL_da;
+        wp += WSTRIDE;
+        if (lane == 0) sm.meta[warp][ns] = make_float4(r3.z, r0.x - cx, r0.y - cy, 0.f);
+        ns++;
+        if (ns == SLOTS) {
+          flush_slots<F>(wbuf, sm.meta[warp], sm.bfrag[warp], SLOTS, lane, grad_rows);
+          ns = 0;
+          wp = wbuf + lane;
+        }
       }
     }
     __syncthreads();  // release stage st for the copy issued at the top of the next iteration
   }
+  if (ns > 0) flush_slots<F>(wbuf, sm.meta[warp], sm.bfrag[warp], ns, lane, grad_rows);
 }
 
 void launch_render_backward(int F, const Cam& cam, const GeomState& g, const BinState& b, const ImageState& img,
                             const float* sh_objs, const float* dL_dpix_depth, const float* dL_dpix,
                             const float* dL_dpix_obj, cudaStream_t s) {
   dim3 grid(cam.gx, cam.gy), block(256);
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(render_bwd_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmem<16>));
+    cudaFuncSetAttribute(render_bwd_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmem<32>));
+    attr_set = true;
+  }
   if (F == 16)
-    render_bwd_kernel<16><<<grid, block, 0, s>>>(img.ranges, b.point_list, g.rec, sh_objs, cam.W, cam.H, cam.bg,
-                                                 img.final_T, img.n_contrib, dL_dpix_depth, dL_dpix, dL_dpix_obj,
-                                                 g.grad_rows);
+    render_bwd_kernel<16><<<grid, block, sizeof(BwdSmem<16>), s>>>(
+        img.ranges, b.point_list, b.hitw, g.rec, sh_objs, cam.W, cam.H, cam.bg, img.final_T, img.n_contrib,
+        dL_dpix_depth, dL_dpix, dL_dpix_obj, g.grad_rows);
   else
-    render_bwd_kernel<32><<<grid, block, 0, s>>>(img.ranges, b.point_list, g.rec, sh_objs, cam.W, cam.H, cam.bg,
-                                                 img.final_T, img.n_contrib, dL_dpix_depth, dL_dpix, dL_dpix_obj,
-                                                 g.grad_rows);
+    render_bwd_kernel<32><<<grid, block, sizeof(BwdSmem<32>), s>>>(
+        img.ranges, b.point_list, b.hitw, g.rec, sh_objs, cam.W, cam.H, cam.bg, img.final_T, img.n_contrib,
+        dL_dpix_depth, dL_dpix, dL_dpix_obj, g.grad_rows);
 }
 
 }  // namespace gsr

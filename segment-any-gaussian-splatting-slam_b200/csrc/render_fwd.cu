@@ -26,7 +26,8 @@ __global__ void __launch_bounds__(256)
 render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
                   const float4* __restrict__ rec, const float* __restrict__ feats, int W, int H,
                   const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
-                  float* __restrict__ out_depth, float* __restrict__ out_color, float* __restrict__ out_objects) {
+                  float* __restrict__ out_depth, float* __restrict__ out_color, float* __restrict__ out_objects,
+                  uint32_t* __restrict__ hitw) {
   constexpr int RB = batch_size<F>();
   __shared__ __align__(128) FwdSmem<F> sm;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -37,6 +38,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
   const int todo = (int)(range.y - range.x);
   const int nbatch = (todo + RB - 1) / RB;
+  const uint32_t gbase = (range.x >> 5) + blockIdx.y * gridDim.x + blockIdx.x;  // first mask group of this tile
 
   if (tid == 0) {
     mbar_init(&sm.bar[0], 1);
@@ -71,6 +73,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     if (b + 1 < nbatch) issue(b + 1);  // stage (b+1)&1 was released by the barrier ending iteration b-1
     mbar_wait(&sm.bar[st], (uint32_t)(b >> 1) & 1u);
     const int cnt = min(RB, todo - b * RB);
+    uint32_t mymask = 0;  // lane k: bit i = this warp blended staged instance 32 k + i
     if (!__all_sync(0xffffffffu, done)) {
       const float4* rp = &sm.rec[st][0][0];
       const float4* fp = &sm.feat[st][0][0];
@@ -112,11 +115,14 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
           D = fmaf(depth_c, w, D);
           T = hit ? test_T : T;
           last_contributor = hit ? (uint32_t)(b * RB + j + 1) : last_contributor;
+          // per-(warp, instance) blend mask for the backward pass (it walks only these pairs)
+          if (lane == (j >> 5)) mymask |= 1u << (j & 31);
         }
         if (__any_sync(0xffffffffu, stop) && __all_sync(0xffffffffu, done)) break;
       }
     }
     // block vote (reference forward.cu:339-341) + release of stage st for the copy issued next iteration
+    if (32 * lane < cnt) hitw[(size_t)(gbase + (uint32_t)(b * (RB / 32) + lane)) * 8 + warp] = mymask;
     const int num_done = __syncthreads_count(done);
     if (num_done == 256) {
       if (b + 1 < nbatch) mbar_wait(&sm.bar[(b + 1) & 1], (uint32_t)((b + 1) >> 1) & 1u);  // drain in-flight TMA
@@ -196,10 +202,12 @@ void launch_render_forward(int F, const Cam& cam, const GeomState& g, const BinS
   dim3 grid(cam.gx, cam.gy), block(256);
   if (F == 16)
     render_fwd_kernel<16><<<grid, block, 0, s>>>(img.ranges, b.point_list, g.rec, sh_objs, cam.W, cam.H, cam.bg,
-                                                 img.final_T, img.n_contrib, out_depth, out_color, out_objects);
+                                                 img.final_T, img.n_contrib, out_depth, out_color, out_objects,
+                                                 b.hitw);
   else
     render_fwd_kernel<32><<<grid, block, 0, s>>>(img.ranges, b.point_list, g.rec, sh_objs, cam.W, cam.H, cam.bg,
-                                                 img.final_T, img.n_contrib, out_depth, out_color, out_objects);
+                                                 img.final_T, img.n_contrib, out_depth, out_color, out_objects,
+                                                 b.hitw);
 }
 
 }  // namespace gsr

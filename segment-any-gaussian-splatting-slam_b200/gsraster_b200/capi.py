@@ -6,6 +6,7 @@ LibTorch binding (submodules/diff-gaussian-rasterization/rasterize_points.cu:35-
 CPU fallback: a missing library or a non-CUDA tensor raises.
 """
 import ctypes as C
+import sys
 import os
 
 import torch
@@ -76,15 +77,49 @@ def _f32c(t):
 
 
 class _Resizer:
-    """torch-backed scratch allocator (reference: resizeFunctional, rasterize_points.cu:27-33)."""
+    """torch-backed scratch allocator (reference: resizeFunctional, rasterize_points.cu:27-33).
 
-    def __init__(self, device):
+    The three scratch buffers of a step are hundreds of MB and are requested with the same sizes every step; taking
+    them from torch's caching allocator lets smaller requests split the cached blocks, which ends in sporadic
+    cudaMalloc calls (~100 ms) in the middle of a mapping loop. So each (device, role) keeps a few buffers of its own
+    and hands one out again once nothing else references it (Python references and autograd saved tensors both count)."""
+
+    _pools = {}
+    _POOL_MAX = 8
+
+    def __init__(self, device, role=""):
+        self.device = device
+        self.key = (str(device), role)
         self.t = torch.empty(0, dtype=torch.uint8, device=device)
         self.cb = ALLOC_FN(self._alloc)
 
     def _alloc(self, _ctx, n):
-        self.t = torch.empty(int(n) + 256, dtype=torch.uint8, device=self.t.device)
+        n = int(n) + 256
+        pool = _Resizer._pools.setdefault(self.key, [])
+        for i in range(len(pool)):
+            t = pool[i]
+            # free <=> only the pool list and the local name refer to it, and no autograd node saved it
+            if sys.getrefcount(t) <= 3 and t._use_count() <= 1:
+                if n <= t.numel() <= n + n // 2 + (1 << 20):
+                    self.t = t
+                    return t.data_ptr()
+        t = None
+        self.t = torch.empty(n + n // 16, dtype=torch.uint8, device=self.device)  # head-room: R varies a little per view
+        pool.append(self.t)
+        if len(pool) > _Resizer._POOL_MAX:
+            for i in range(len(pool)):  # drop the oldest unreferenced buffer
+                if sys.getrefcount(pool[i]) <= 2 and pool[i]._use_count() <= 1:
+                    del pool[i]
+                    break
+            else:
+                del pool[0]
         return self.t.data_ptr()
+
+    def take(self):
+        """Hand the buffer to the caller and break the self -> callback -> bound method -> self cycle, so that the
+        buffer's life ends with the caller's reference and not at the next cyclic-GC run."""
+        t, self.t, self.cb = self.t, None, None
+        return t
 
 
 def _stream_ptr():
@@ -109,12 +144,12 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
     out_objects = torch.empty((F, H, W), dtype=torch.float32, device=dev)
     radii = torch.empty((P,), dtype=torch.int32, device=dev)
     is_used = torch.empty((P,), dtype=torch.bool, device=dev)
-    geo, binb, img = _Resizer(dev), _Resizer(dev), _Resizer(dev)
+    geo, binb, img = _Resizer(dev, "geom"), _Resizer(dev, "binning"), _Resizer(dev, "image")
     rendered = C.c_int(0)
     if P == 0:
         for t in (out_depth, out_color, out_objects):
             t.zero_()
-        return 0, out_depth, out_color, out_objects, radii, is_used, geo.t, binb.t, img.t
+        return 0, out_depth, out_color, out_objects, radii, is_used, geo.take(), binb.take(), img.take()
     M = sh.size(1) if (sh is not None and sh.numel() != 0) else 0
     prm = Params(P, int(degree), int(M), int(F), W, H, float(tan_fovx), float(tan_fovy), float(scale_modifier),
                  int(bool(prefiltered)), int(bool(debug)), _stream_ptr())
@@ -124,8 +159,9 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         rc = lib().gsr_forward(C.byref(prm), geo.cb, None, binb.cb, None, img.cb, None, *[_ptr(t) for t in keep],
                                _ptr(out_depth), _ptr(out_color), _ptr(out_objects), _ptr(radii), _ptr(is_used),
                                C.byref(rendered))
+    bufs = (geo.take(), binb.take(), img.take())
     _check(rc)
-    return rendered.value, out_depth, out_color, out_objects, radii, is_used, geo.t, binb.t, img.t
+    return (rendered.value, out_depth, out_color, out_objects, radii, is_used) + bufs
 
 
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier,

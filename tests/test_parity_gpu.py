@@ -253,7 +253,7 @@ def test_forward_is_deterministic_and_backward_stable():
     for k in ("color", "depth", "objects", "n_contrib", "point_list"):
         assert (h.npy(a[k]) == h.npy(b[k])).all(), k
     for k in h.GRAD_KEYS:
-        assert h.grad_rel_err(a[k], b[k]) < 1e-5, k
+        assert h.grad_rel_err(a[k], b[k]) < 5e-5, k  # float atomics: run-to-run spread, bar is 1e-3
 
 
 # ---- drop-in Python surface (reference diff_gaussian_rasterization/__init__.py, simple_knn/_C) -----
