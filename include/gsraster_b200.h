@@ -136,6 +136,10 @@ size_t gsr_binning_bytes(int64_t num_rendered);
 #define GSR_NUM_STAGES 6
 int gsr_set_stage_timing(int enable);
 int gsr_get_stage_times(float* ms);
+/* Stream time between the end of the previously recorded stage and the start of stage i (launch gaps, the
+ * num_rendered synchronisation, work of the caller between forward and backward), accumulated by the last
+ * gsr_get_stage_times call; reading clears it. */
+int gsr_get_stage_gaps(float* ms);
 
 /* Work counters of a finished forward pass, for the FP32 roofline of the blend kernels
  * (SURVEY.md 8d "N_eval / N_contrib"): replays the blend tests (no blending) and returns on the

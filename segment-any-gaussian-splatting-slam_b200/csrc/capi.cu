@@ -32,6 +32,7 @@ struct StageSpan { int stage; cudaEvent_t a, b; };
 thread_local bool g_timing = false;
 thread_local std::vector<StageSpan> g_spans;
 thread_local std::vector<cudaEvent_t> g_free_events;
+thread_local float g_gaps[GSR_NUM_STAGES] = {0, 0, 0, 0, 0, 0};  // idle time on the stream before each stage
 cudaEvent_t take_event() {
   cudaEvent_t e;
   if (!g_free_events.empty()) { e = g_free_events.back(); g_free_events.pop_back(); return e; }
@@ -311,15 +312,25 @@ int gsr_set_stage_timing(int enable) {
 }
 int gsr_get_stage_times(float* ms) {
   if (!ms) return fail(GSR_ERR_INVALID_ARGUMENT, "ms is NULL");
+  const StageSpan* prev = nullptr;
   for (const StageSpan& sp : g_spans) {
     CUDA_TRY(cudaEventSynchronize(sp.b));
     float t = 0.f;
     CUDA_TRY(cudaEventElapsedTime(&t, sp.a, sp.b));
     if (sp.stage >= 0 && sp.stage < GSR_NUM_STAGES) ms[sp.stage] += t;
+    if (prev && sp.stage >= 0 && sp.stage < GSR_NUM_STAGES && cudaEventElapsedTime(&t, prev->b, sp.a) == cudaSuccess)
+      g_gaps[sp.stage] += t;
+    prev = &sp;
     g_free_events.push_back(sp.a);
     g_free_events.push_back(sp.b);
   }
   g_spans.clear();
+  return GSR_OK;
+}
+
+int gsr_get_stage_gaps(float* ms) {
+  if (!ms) return fail(GSR_ERR_INVALID_ARGUMENT, "ms is NULL");
+  for (int i = 0; i < GSR_NUM_STAGES; i++) { ms[i] = g_gaps[i]; g_gaps[i] = 0.f; }
   return GSR_OK;
 }
 

@@ -303,51 +303,75 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       // bit l of m = mask bit of position p_hi - l
       uint32_t m = __brev(__funnelshift_rc(W0, W1, (p_hi & 31) + 1));
       while (m) {
-        const int j = 32 * k + __ffs(m) - 1;
-        m &= m - 1;
-        const BwdRow<F>& R = sm.row[st][j];
-        const float4 r0 = R.rec[0];  // px, py, conic a, conic b
-        const float4 r1 = R.rec[1];  // conic c, opacity, box half extents hx, hy
-        const float4 r2 = R.rec[2];  // depth, r, g, b
-        const float4 r3 = R.rec[3];  // cov_zx, cov_yz, Gaussian index bits
-        const float dx = r0.x - pixx, dy = r0.y - pixy;
-        const float power = -0.5f * (r0.z * dx * dx + r1.x * dy * dy) - r0.w * dx * dy;
-        float G = expf(power);
-        float alpha = min(0.99f, r1.y * G);
-        // the forward pass blended this pair iff (forward.cu:365-379, backward.cu:549-551):
-        const bool hit = j >= thr_b && power <= 0.0f && alpha >= 1.0f / 255.0f;
-        // Lanes without a hit run the same instructions with G = alpha = 0, which zeroes w and q
-        // and leaves T and S unchanged.
-        G = hit ? G : 0.f;
-        alpha = hit ? alpha : 0.f;
-        const float inv1ma = rcp_approx(1.f - alpha);
-        T = T * inv1ma;
-        const float w = alpha * T;  // d(out channel) / d(channel value of this Gaussian)
-        const float cza = r3.x * r0.z + r3.y * r0.w;
-        const float czb = r3.x * r0.w + r3.y * r1.x;
-        const float depth = r2.x - cza * dx - czb * dy;
-        float E0 = depth * dpd, E1 = r2.y * dpx[0], E2 = r2.z * dpx[1], E3 = r2.w * dpx[2];
-#pragma unroll
-        for (int q4 = 0; q4 < F / 4; q4++) {
-          const float4 f4 = R.feat[q4];
-          E0 = fmaf(f4.x, dpo[4 * q4 + 0], E0);
-          E1 = fmaf(f4.y, dpo[4 * q4 + 1], E1);
-          E2 = fmaf(f4.z, dpo[4 * q4 + 2], E2);
-          E3 = fmaf(f4.w, dpo[4 * q4 + 3], E3);
-        }
-        const float E = (E0 + E1) + (E2 + E3);
-        const float dL_da = T * E - S * inv1ma;
-        S = fmaf(w, E, S);
-        wp[0] = w;
-        wp[SLOTS * WSTRIDE] = G * dL_da;
-        wp += WSTRIDE;
-        if (lane == 0) sm.meta[warp][ns] = make_float4(r3.z, r0.x - cx, r0.y - cy, 0.f);
-        ns++;
-        if (ns == SLOTS) {
-          flush_slots<F>(wbuf, sm.meta[warp], sm.bfrag[warp], SLOTS, lane, grad_rows);
+        // two hits per iteration (the second may be absent): their geometry / alpha / dot-product chains are
+        // independent, only the T and S recurrences are serial
+        if (ns > SLOTS - 2) {
+          flush_slots<F>(wbuf, sm.meta[warp], sm.bfrag[warp], ns, lane, grad_rows);
           ns = 0;
           wp = wbuf + lane;
         }
+        const int ja = 32 * k + __ffs(m) - 1;
+        m &= m - 1;
+        const bool two = m != 0;
+        const int jb = two ? 32 * k + __ffs(m) - 1 : ja;
+        m &= m - 1;
+        float Gv[2], av[2], Ev[2], gxv[2], gyv[2], idv[2];
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          const int j = h ? jb : ja;
+          const BwdRow<F>& R = sm.row[st][j];
+          const float4 r0 = R.rec[0];  // px, py, conic a, conic b
+          const float4 r1 = R.rec[1];  // conic c, opacity, box half extents hx, hy
+          const float4 r2 = R.rec[2];  // depth, r, g, b
+          const float4 r3 = R.rec[3];  // cov_zx, cov_yz, Gaussian index bits
+          const float dx = r0.x - pixx, dy = r0.y - pixy;
+          const float power = -0.5f * (r0.z * dx * dx + r1.x * dy * dy) - r0.w * dx * dy;
+          const float G = expf(power);
+          const float alpha = min(0.99f, r1.y * G);
+          // the forward pass blended this pair iff (forward.cu:365-379, backward.cu:549-551):
+          const bool hit = (h == 0 || two) && j >= thr_b && power <= 0.0f && alpha >= 1.0f / 255.0f;
+          // Lanes without a hit run the same instructions with G = alpha = 0, which zeroes w and q
+          // and leaves T and S unchanged.
+          Gv[h] = hit ? G : 0.f;
+          av[h] = hit ? alpha : 0.f;
+          const float cza = r3.x * r0.z + r3.y * r0.w;
+          const float czb = r3.x * r0.w + r3.y * r1.x;
+          const float depth = r2.x - cza * dx - czb * dy;
+          float E0 = depth * dpd, E1 = r2.y * dpx[0], E2 = r2.z * dpx[1], E3 = r2.w * dpx[2];
+#pragma unroll
+          for (int q4 = 0; q4 < F / 4; q4++) {
+            const float4 f4 = R.feat[q4];
+            E0 = fmaf(f4.x, dpo[4 * q4 + 0], E0);
+            E1 = fmaf(f4.y, dpo[4 * q4 + 1], E1);
+            E2 = fmaf(f4.z, dpo[4 * q4 + 2], E2);
+            E3 = fmaf(f4.w, dpo[4 * q4 + 3], E3);
+          }
+          Ev[h] = (E0 + E1) + (E2 + E3);
+          gxv[h] = r0.x - cx;
+          gyv[h] = r0.y - cy;
+          idv[h] = r3.z;
+        }
+        const float inv_a = rcp_approx(1.f - av[0]), inv_b = rcp_approx(1.f - av[1]);
+        const float Ta = T * inv_a;
+        const float wa = av[0] * Ta;  // d(out channel) / d(channel value of this Gaussian)
+        const float qa = Gv[0] * (Ta * Ev[0] - S * inv_a);
+        const float Sa = fmaf(wa, Ev[0], S);
+        const float Tb = Ta * inv_b;
+        const float wb = av[1] * Tb;
+        const float qb = Gv[1] * (Tb * Ev[1] - Sa * inv_b);
+        T = Tb;
+        S = fmaf(wb, Ev[1], Sa);
+        wp[0] = wa;
+        wp[SLOTS * WSTRIDE] = qa;
+        if (lane == 0) sm.meta[warp][ns] = make_float4(idv[0], gxv[0], gyv[0], 0.f);
+        if (two) {
+          wp[WSTRIDE] = wb;
+          wp[SLOTS * WSTRIDE + WSTRIDE] = qb;
+          if (lane == 0) sm.meta[warp][ns + 1] = make_float4(idv[1], gxv[1], gyv[1], 0.f);
+        }
+        const int adv = two ? 2 : 1;
+        ns += adv;
+        wp += adv * WSTRIDE;
       }
     }
     __syncthreads();  // release stage st for the copy issued at the top of the next iteration

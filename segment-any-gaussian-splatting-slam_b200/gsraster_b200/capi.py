@@ -48,6 +48,7 @@ def lib():
         L.gsr_export_state.argtypes = [C.POINTER(Params), C.c_int] + [C.c_void_p] * 14
         L.gsr_count_pairs.argtypes = [C.POINTER(Params), C.c_int] + [C.c_void_p] * 3 + [C.POINTER(C.c_ulonglong)]
         L.gsr_get_stage_times.argtypes = [C.POINTER(C.c_float)]
+        L.gsr_get_stage_gaps.argtypes = [C.POINTER(C.c_float)]
         L.gsr_last_forward_stats.argtypes = [C.POINTER(C.c_ulonglong)]
         L.gsr_set_stage_timing.argtypes = [C.c_int]
         _lib = L
@@ -279,6 +280,13 @@ def get_stage_times():
     """Milliseconds per stage accumulated since the previous call (synchronises)."""
     ms = (C.c_float * len(STAGES))()
     _check(lib().gsr_get_stage_times(ms))
+    return dict(zip(STAGES, [float(v) for v in ms]))
+
+
+def get_stage_gaps():
+    """Idle milliseconds on the stream before each stage (see gsr_get_stage_gaps); call after get_stage_times()."""
+    ms = (C.c_float * len(STAGES))()
+    _check(lib().gsr_get_stage_gaps(ms))
     return dict(zip(STAGES, [float(v) for v in ms]))
 
 

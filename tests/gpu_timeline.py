@@ -61,6 +61,8 @@ for s in range(steps):
           f"{ev[s][0].elapsed_time(ev[s][1]):.3f} bwd {ev[s][1].elapsed_time(ev[s][2]):.3f} ms | sync/alloc/launch us "
           f"{fstats[s]['sync_us']}/{fstats[s]['alloc_us']}/{fstats[s]['launch_us']}")
 print(" stage ms/step:", {k: round(v / steps, 4) for k, v in st.items()}, "sum", round(sum(st.values()) / steps, 4))
+gp = capi.get_stage_gaps()
+print(" idle before stage, ms/step:", {k: round(v / steps, 4) for k, v in gp.items()}, "sum", round(sum(gp.values()) / steps, 4))
 # forward only (render FPS)
 torch.cuda.synchronize()
 t0 = time.perf_counter()
