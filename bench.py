@@ -421,6 +421,8 @@ def main():
     if world > 1:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        # NCCL writes its version / INFO lines to stdout by default; stdout of rank 0 carries exactly one JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     r = run_mine(args, rank, world, local_rank)
     if world > 1:

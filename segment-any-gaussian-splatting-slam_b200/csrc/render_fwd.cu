@@ -35,6 +35,9 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   const int py = blockIdx.y * TILE_Y + (warp >> 1) * 4 + (lane >> 3);
   const bool inside = px < W && py < H;
   const float pixx = (float)px, pixy = (float)py;
+  // pixel-centre extent of this warp's 8x4 block
+  const float bxlo = (float)(blockIdx.x * TILE_X + (warp & 1) * 8), bxhi = bxlo + 7.f;
+  const float bylo = (float)(blockIdx.y * TILE_Y + (warp >> 1) * 4), byhi = bylo + 3.f;
   const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
   const int todo = (int)(range.y - range.x);
   const int nbatch = (todo + RB - 1) / RB;
@@ -75,53 +78,75 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     const int cnt = min(RB, todo - b * RB);
     uint32_t mymask = 0;  // lane k: bit i = this warp blended staged instance 32 k + i
     if (!__all_sync(0xffffffffu, done)) {
-      const float4* rp = &sm.rec[st][0][0];
-      const float4* fp = &sm.feat[st][0][0];
-      for (int j = 0; j < cnt; j++, rp += REC4, fp += F / 4) {
-        const float4 r0 = rp[0];  // px, py, conic a, conic b
-        const float4 r1 = rp[1];  // conic c, opacity, box half extents hx, hy
-        const float dx = r0.x - pixx, dy = r0.y - pixy;
-        // outside the conservative alpha >= 1/255 box (preprocess.cu) the pixel would fail forward.cu:372
-        const bool inbox = !done && fabsf(dx) <= r1.z && fabsf(dy) <= r1.w;
-        if (!__any_sync(0xffffffffu, inbox)) continue;
-        const float power = -0.5f * (r0.z * dx * dx + r1.x * dy * dy) - r0.w * dx * dy;
-        const bool cand = inbox && power <= 0.0f;                  // forward.cu:365-366
-        if (!__any_sync(0xffffffffu, cand)) continue;
-        // T, alpha and the two thresholds use exactly the reference's operations (n_contrib and
-        // final_T are bit-exact); lanes that are not candidates compute values that are masked out.
-        const float alpha = min(0.99f, r1.y * expf(power));       // forward.cu:371
-        const bool ok = cand && alpha >= 1.0f / 255.0f;            // forward.cu:372-373
-        const float test_T = T * (1 - alpha);
-        const bool stop = ok && test_T < 0.0001f;                  // forward.cu:375-379: pixel done, not blended
-        const bool hit = ok && !stop;
-        done = done || stop;
-        if (__any_sync(0xffffffffu, hit)) {
-          const float4 r2 = rp[2];  // depth, r, g, b
-          const float w = hit ? alpha * T : 0.f;  // colour/feature/depth sums need 1e-4, not bit-exactness
-          C[0] = fmaf(r2.y, w, C[0]);
-          C[1] = fmaf(r2.z, w, C[1]);
-          C[2] = fmaf(r2.w, w, C[2]);
+      // Candidate instances of this warp: the alpha >= 1/255 box (preprocess.cu) meets the warp's 8x4 pixel block.
+      // Lane l tests instances l, l + 32, ...; one ballot per 32 instances. A pixel outside the box fails
+      // forward.cu:372, so walking only the candidates changes no result.
+      uint32_t candw[RB / 32];
 #pragma unroll
-          for (int q = 0; q < F / 4; q++) {
-            const float4 f4 = fp[q];
-            O[4 * q + 0] = fmaf(f4.x, w, O[4 * q + 0]);
-            O[4 * q + 1] = fmaf(f4.y, w, O[4 * q + 1]);
-            O[4 * q + 2] = fmaf(f4.z, w, O[4 * q + 2]);
-            O[4 * q + 3] = fmaf(f4.w, w, O[4 * q + 3]);
-          }
-          const float4 r3 = rp[3];  // cov_zx, cov_yz
-          const float covzx = r3.x, covyz = r3.y;
-          const float depth_c = r2.x - (covzx * r0.z + covyz * r0.w) * dx - (covzx * r0.w + covyz * r1.x) * dy;
-          D = fmaf(depth_c, w, D);
-          T = hit ? test_T : T;
-          last_contributor = hit ? (uint32_t)(b * RB + j + 1) : last_contributor;
-          // per-(warp, instance) blend mask for the backward pass (it walks only these pairs)
-          if (lane == (j >> 5)) mymask |= 1u << (j & 31);
+      for (int k = 0; k < RB / 32; k++) {
+        const int j = 32 * k + lane;
+        bool c = false;
+        if (j < cnt) {
+          const float2 xy = *reinterpret_cast<const float2*>(&sm.rec[st][j][0]);
+          const float2 hh = *reinterpret_cast<const float2*>(&sm.rec[st][j][1].z);
+          // nearest pixel column / row of the block to the centre
+          const float ddx = fmaxf(fmaxf(bxlo - xy.x, xy.x - bxhi), 0.f);
+          const float ddy = fmaxf(fmaxf(bylo - xy.y, xy.y - byhi), 0.f);
+          c = ddx <= hh.x && ddy <= hh.y;
         }
-        if (__any_sync(0xffffffffu, stop) && __all_sync(0xffffffffu, done)) break;
+        candw[k] = __ballot_sync(0xffffffffu, c);
+      }
+      bool all_done = false;
+#pragma unroll
+      for (int k = 0; k < RB / 32; k++) {
+        uint32_t m = candw[k];
+        while (m && !all_done) {
+          const int j = 32 * k + __ffs(m) - 1;
+          m &= m - 1;
+          const float4* rp = &sm.rec[st][j][0];
+          const float4 r0 = rp[0];  // px, py, conic a, conic b
+          const float4 r1 = rp[1];  // conic c, opacity, box half extents hx, hy
+          const float dx = r0.x - pixx, dy = r0.y - pixy;
+          const float power = -0.5f * (r0.z * dx * dx + r1.x * dy * dy) - r0.w * dx * dy;
+          // outside the conservative box the pixel would fail forward.cu:372
+          const bool cand = !done && fabsf(dx) <= r1.z && fabsf(dy) <= r1.w && power <= 0.0f;  // forward.cu:365-366
+          if (!__any_sync(0xffffffffu, cand)) continue;
+          // T, alpha and the two thresholds use exactly the reference's operations (n_contrib and
+          // final_T are bit-exact); lanes that are not candidates compute values that are masked out.
+          const float alpha = min(0.99f, r1.y * expf(power));       // forward.cu:371
+          const bool ok = cand && alpha >= 1.0f / 255.0f;            // forward.cu:372-373
+          const float test_T = T * (1 - alpha);
+          const bool stop = ok && test_T < 0.0001f;                  // forward.cu:375-379: pixel done, not blended
+          const bool hit = ok && !stop;
+          done = done || stop;
+          if (__any_sync(0xffffffffu, hit)) {
+            const float4* fp = &sm.feat[st][j][0];
+            const float4 r2 = rp[2];  // depth, r, g, b
+            const float w = hit ? alpha * T : 0.f;  // colour/feature/depth sums need 1e-4, not bit-exactness
+            C[0] = fmaf(r2.y, w, C[0]);
+            C[1] = fmaf(r2.z, w, C[1]);
+            C[2] = fmaf(r2.w, w, C[2]);
+#pragma unroll
+            for (int q = 0; q < F / 4; q++) {
+              const float4 f4 = fp[q];
+              O[4 * q + 0] = fmaf(f4.x, w, O[4 * q + 0]);
+              O[4 * q + 1] = fmaf(f4.y, w, O[4 * q + 1]);
+              O[4 * q + 2] = fmaf(f4.z, w, O[4 * q + 2]);
+              O[4 * q + 3] = fmaf(f4.w, w, O[4 * q + 3]);
+            }
+            const float4 r3 = rp[3];  // cov_zx, cov_yz
+            const float covzx = r3.x, covyz = r3.y;
+            const float depth_c = r2.x - (covzx * r0.z + covyz * r0.w) * dx - (covzx * r0.w + covyz * r1.x) * dy;
+            D = fmaf(depth_c, w, D);
+            T = hit ? test_T : T;
+            last_contributor = hit ? (uint32_t)(b * RB + j + 1) : last_contributor;
+            // per-(warp, instance) blend mask for the backward pass (it walks only these pairs)
+            if (lane == k) mymask |= 1u << (j & 31);
+          }
+          if (__any_sync(0xffffffffu, stop)) all_done = __all_sync(0xffffffffu, done);
+        }
       }
     }
-    // block vote (reference forward.cu:339-341) + release of stage st for the copy issued next iteration
     if (32 * lane < cnt) hitw[(size_t)(gbase + (uint32_t)(b * (RB / 32) + lane)) * 8 + warp] = mymask;
     const int num_done = __syncthreads_count(done);
     if (num_done == 256) {
