@@ -309,8 +309,6 @@ __device__ __forceinline__ uint32_t super_rect(uint32_t rc, int shift) {
   const uint32_t x0 = rc & 255u, y0 = (rc >> 8) & 255u, x1 = (rc >> 16) & 255u, y1 = rc >> 24;
   return (x0 >> shift) | ((y0 >> shift) << 8) | ((((x1 - 1) >> shift) + 1) << 16) | ((((y1 - 1) >> shift) + 1) << 24);
 }
-// is point (x, y) (packed x | y<<8 | x<<16 | y<<24) inside rect? bytes 0,1: lo <= p ; bytes 2,3: !(hi <= p)
-__device__ __forceinline__ bool rect_has(uint32_t rc, uint32_t pxy) { return __vcmpleu4(rc, pxy) == 0x0000FFFFu; }
 
 // Supertile lists. One block = 256 consecutive depth ranks = 8 warps. For every supertile s the
 // ballot of "rect overlaps s" ranks the lanes of a warp; per-warp popcounts go to shared memory,
@@ -455,9 +453,12 @@ void launch_binning(int P, int64_t R, const Cam& cam, GeomState& g, BinState& b,
   l1_kernel<false><<<nb, 256, 0, s>>>(P, sg, shift, g.dkeys_a, g.tiles_touched, g.rect, b.warp_cnt, nb, b.l1);
   l1_scan_kernel<<<sg.NS, 256, 0, s>>>(b.warp_cnt, nb, img.l1_off);
   l1_kernel<true><<<nb, 256, 0, s>>>(P, sg, shift, g.dkeys_a, g.tiles_touched, g.rect, b.warp_cnt, nb, b.l1);
+  launches += 3;
+}
+void launch_tile_pull(const Cam& cam, const BinState& b, const ImageState& img, cudaStream_t s) {
+  const SuperGrid sg = super_grid(cam.gx, cam.gy);
   tile_pull_kernel<<<sg.NS * (sg.S * sg.S / 8), 256, 0, s>>>(cam.gx, cam.gy, sg, b.l1, img.l1_off, img.tile_off,
                                                            b.point_list);
-  launches += 4;
 }
 
 // ---- parity export ------------------------------------------------------------------------------

@@ -350,6 +350,7 @@ int gsr_count_pairs(const gsr_params* p, int num_rendered, const char* geom_buff
   unsigned long long* d = nullptr;
   CUDA_TRY(cudaMalloc(&d, 4 * sizeof(unsigned long long)));
   CUDA_TRY(cudaMemsetAsync(d, 0, 4 * sizeof(unsigned long long), stream));
+  if (num_rendered > 0) gsr::launch_tile_pull(cam, b, img, stream);  // the forward blend only materialises the prefix it consumed
   gsr::launch_count_pairs(cam, g, b, img, d, stream);
   cudaError_t e = cudaMemcpyAsync(counts, d, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
@@ -401,6 +402,7 @@ int gsr_export_state(const gsr_params* p, int num_rendered, const char* geom_buf
   gsr::BinState b{};
   if (binning_buffer)
     gsr::bin_from_chunk(const_cast<char*>(binning_buffer), (size_t)(num_rendered > 0 ? num_rendered : 0), 0, 0, b);
+  if (num_rendered > 0 && binning_buffer && (point_list || sorted_keys)) gsr::launch_tile_pull(cam, b, img, stream);
   gsr::launch_export(P, num_rendered, cam, g, b, tiles_touched, depths, means2D, conic_opacity, rgb, clamped,
                      sorted_keys, stream);
   if (num_rendered > 0 && binning_buffer) {

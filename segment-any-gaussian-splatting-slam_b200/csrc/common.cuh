@@ -81,6 +81,9 @@ __host__ __device__ inline SuperGrid super_grid(int gx, int gy) {
   return g;
 }
 
+// is point (x, y) (packed x | y<<8 | x<<16 | y<<24) inside the packed rect? bytes 0,1: lo <= p ; bytes 2,3: !(hi <= p)
+__device__ __forceinline__ bool rect_has(uint32_t rc, uint32_t pxy) { return __vcmpleu4(rc, pxy) == 0x0000FFFFu; }
+
 template <typename T>
 inline void carve(char*& p, T*& out, size_t count) {
   p = reinterpret_cast<char*>(align_up(reinterpret_cast<size_t>(p), 256));
@@ -173,9 +176,11 @@ void launch_preprocess(const FwdInputs& in, const Cam& cam, GeomState& g, ImageS
 // depth sort (leaves depth-ordered keys in g.dkeys_a) + tile / supertile offsets from the coverage
 // grids: ranges, tile_off, l1_off, R -> g.flags[0], L1 total -> g.flags[2..3]
 void launch_depth_sort_and_offsets(int P, const Cam& cam, GeomState& g, ImageState& img, cudaStream_t s, int& launches);
-// supertile lists + per-tile pull into point_list
+// supertile lists (the forward blend pulls each tile's list out of its supertile's list as it goes)
 void launch_binning(int P, int64_t R, const Cam& cam, GeomState& g, BinState& b, ImageState& img, cudaStream_t s,
                     int& launches);
+// materialises every tile's full list in point_list (parity export / diagnostics only)
+void launch_tile_pull(const Cam& cam, const BinState& b, const ImageState& img, cudaStream_t s);
 void launch_render_forward(int F, const Cam& cam, const GeomState& g, const BinState& b,
                            ImageState& img, const float* sh_objs, float* out_depth, float* out_color,
                            float* out_objects, cudaStream_t s);

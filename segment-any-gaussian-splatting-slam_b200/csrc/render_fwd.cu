@@ -14,16 +14,21 @@ namespace gsr {
 // instances per staged batch (static shared memory stays below 48 KB at F = 32)
 template <int F> __host__ __device__ constexpr int batch_size() { return F == 16 ? 128 : 64; }
 
+constexpr int QCAP = 512;  // >= batch + one scan round (256)
+
 template <int F>
 struct FwdSmem {
   float4 rec[2][batch_size<F>()][REC4];
   float4 feat[2][batch_size<F>()][F / 4];
   uint64_t bar[2];
+  uint32_t q[QCAP];     // ring of Gaussian indices pulled from the supertile list, in list order
+  uint32_t wsum[2][8];  // per-warp match counts of a scan round (double-buffered: one barrier per round)
 };
 
 template <int F>
 __global__ void __launch_bounds__(256)
-render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+render_fwd_kernel(const uint2* __restrict__ ranges, uint32_t* __restrict__ point_list, SuperGrid sg,
+                  const uint2* __restrict__ l1, const uint32_t* __restrict__ l1_off,
                   const float4* __restrict__ rec, const float* __restrict__ feats, int W, int H,
                   const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                   float* __restrict__ out_depth, float* __restrict__ out_color, float* __restrict__ out_objects,
@@ -50,16 +55,54 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   }
   __syncthreads();
 
+  // The tile's list is the depth-ordered subsequence of its supertile's list {rect, idx} whose rect covers the
+  // tile (binning.cu). It is pulled here, batch by batch and only as far as the blend gets: pixels saturate after
+  // a few hundred entries while lists are thousands long, so most of the list is never materialised. The consumed
+  // prefix is written to point_list for the backward pass (gsr_export_state runs the full pull for parity checks).
+  const int sidx = (blockIdx.y / sg.S) * sg.sgx + blockIdx.x / sg.S;
+  const uint32_t l1_beg = l1_off[sidx];
+  const int l1_n = (int)(l1_off[sidx + 1] - l1_beg);
+  const uint32_t pxy1 = blockIdx.x | (blockIdx.y << 8), pxy = pxy1 | (pxy1 << 16);
+  int cur = 0;                       // scan position in the supertile list
+  uint32_t q_head = 0, q_tail = 0;   // consumed / produced counts (block-uniform)
+  int round = 0;
+  auto refill = [&](int need) {
+    while ((int)(q_tail - q_head) < need && cur < l1_n) {
+      const int i = cur + tid;
+      const uint2 e = i < l1_n ? l1[l1_beg + i] : make_uint2(0u, 0u);  // rect 0 matches no tile
+      const bool in = rect_has(e.x, pxy);
+      const unsigned m = __ballot_sync(0xffffffffu, in);
+      uint32_t* ws = sm.wsum[round & 1];
+      if (lane == 0) ws[warp] = __popc(m);
+      __syncthreads();
+      uint32_t off = 0, tot = 0;
+#pragma unroll
+      for (int k = 0; k < 8; k++) {
+        const uint32_t c = ws[k];
+        off += k < warp ? c : 0u;
+        tot += c;
+      }
+      if (in) sm.q[(q_tail + off + __popc(m & ((1u << lane) - 1))) & (QCAP - 1)] = e.y;
+      q_tail += tot;
+      cur += 256;
+      round++;
+    }
+    __syncthreads();  // queue entries visible
+  };
+
   constexpr uint32_t ROW_BYTES = 16 * REC4 + 4 * F;
   auto issue = [&](int b) {
     const int st = b & 1;
     const int cnt = min(RB, todo - b * RB);
+    refill(cnt);
     if (tid == 0) mbar_arrive_expect_tx(&sm.bar[st], (uint32_t)cnt * ROW_BYTES);
     if (tid < cnt) {
-      const uint32_t id = point_list[range.x + b * RB + tid];
+      const uint32_t id = sm.q[(q_head + tid) & (QCAP - 1)];
+      point_list[range.x + b * RB + tid] = id;
       tma_load_1d(&sm.rec[st][tid][0], rec + REC4 * (size_t)id, 16 * REC4, &sm.bar[st]);
       tma_load_1d(&sm.feat[st][tid][0], feats + (size_t)id * F, 4 * F, &sm.bar[st]);
     }
+    q_head += (uint32_t)cnt;
   };
 
   float T = 1.0f, D = 0.f;
@@ -225,12 +268,13 @@ void launch_render_forward(int F, const Cam& cam, const GeomState& g, const BinS
                            ImageState& img, const float* sh_objs, float* out_depth, float* out_color,
                            float* out_objects, cudaStream_t s) {
   dim3 grid(cam.gx, cam.gy), block(256);
+  const SuperGrid sg = super_grid(cam.gx, cam.gy);
   if (F == 16)
-    render_fwd_kernel<16><<<grid, block, 0, s>>>(img.ranges, b.point_list, g.rec, sh_objs, cam.W, cam.H, cam.bg,
+    render_fwd_kernel<16><<<grid, block, 0, s>>>(img.ranges, b.point_list, sg, b.l1, img.l1_off, g.rec, sh_objs, cam.W, cam.H, cam.bg,
                                                  img.final_T, img.n_contrib, out_depth, out_color, out_objects,
                                                  b.hitw);
   else
-    render_fwd_kernel<32><<<grid, block, 0, s>>>(img.ranges, b.point_list, g.rec, sh_objs, cam.W, cam.H, cam.bg,
+    render_fwd_kernel<32><<<grid, block, 0, s>>>(img.ranges, b.point_list, sg, b.l1, img.l1_off, g.rec, sh_objs, cam.W, cam.H, cam.bg,
                                                  img.final_T, img.n_contrib, out_depth, out_color, out_objects,
                                                  b.hitw);
 }
