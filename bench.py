@@ -129,8 +129,8 @@ def stage_model(args, stats):
         # 4 depth passes over P 8-byte items (histogram read + scatter read + write) + coverage grids (8 B/Gaussian)
         "depth_sort_offsets": ("hbm", P * (4 * 24 + 8)),
         # supertile lists: 2 sweeps over (depth key 8 + tiles_touched 4 + rect 4) B/Gaussian, 8 B/entry written;
-        # tile pull: 8 B/entry read (once from HBM, S*S/8 times from L2), 4 B/instance written
-        "binning": ("hbm", P * 32 + L1 * 16 + R * 4),
+        # (the per-tile pull, 4 B/instance, now lives in the forward blend and covers only the consumed prefix)
+        "binning": ("hbm", P * 32 + L1 * 16),
         "render_fwd": ("fp32", 13 * stats["n_eval_fwd"] + (15 + 2 * (3 + F)) * stats["n_blend"]),
         "render_bwd": ("fp32", 13 * stats["n_eval_bwd"] + (100 + 7 * (3 + F)) * stats["n_blend"]),
         "preprocess_bwd": ("hbm", Pv * ((95 + 12 * M) + (64 + 12 * M)) + (P - Pv) * 4),
