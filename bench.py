@@ -45,6 +45,8 @@ def parse_args():
     ap.add_argument("--deg", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--dense-allreduce", action="store_true",
+                    help="N > 1: sum the full 4(11+3M+F) B/Gaussian bucket instead of the sparse (touched-rows) exchange")
     ap.add_argument("--distinct-views", action="store_true", help="rank r renders keyframe pose r (unequal work)")
     return ap.parse_args()
 
@@ -157,6 +159,10 @@ def run_mine(args, rank, world, local_rank):
     e = torch.empty(0, device=dev)
     bucket = mapping.GradBucket(P, M, F, dev)
     launches = [0]
+    sparse = world > 1 and not args.dense_allreduce
+    ex = mapping.SparseGradExchange(bucket) if sparse else None
+    if sparse:
+        capi.set_touched_mask(ex.touched)
 
     def fwd(dd):
         return capi.rasterize_gaussians(dd["bg"], dd["means3D"], e, dd["opacities"], dd["scales"], dd["rotations"],
@@ -173,17 +179,21 @@ def run_mine(args, rank, world, local_rank):
     def step():
         res = fwd(d)
         launches[0] += capi.last_launch_count()
+        if sparse:
+            ex.begin_step()
         bwd(d, res, g[0], g[1], g[2])
         launches[0] += capi.last_launch_count()
         if world > 1:
             if ar_events is not None:
                 a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 a.record()
-                dist.all_reduce(bucket.flat)
-                b.record()
-                ar_events.append((a, b))
+            if sparse:
+                ex.exchange()      # flags MAX-reduce, nonzero (host sync), row gather, SUM-reduce of the touched rows
             else:
                 dist.all_reduce(bucket.flat)
+            if ar_events is not None:
+                b.record()
+                ar_events.append((a, b))
         return res
 
     ar_events = None
@@ -248,7 +258,7 @@ def run_mine(args, rank, world, local_rank):
     # ---- timed region 2: end to end with host buffers ----
     e2e = None
     if not args.no_e2e:
-        e2e = run_e2e(args, cam, d, g, fwd, bwd, bucket, world, dev, sync_all)
+        e2e = run_e2e(args, cam, d, g, fwd, bwd, bucket, world, dev, sync_all, ex)
     clk = clocks.stop()
     rank_ms = [sum(stage_ms.values())]
     if world > 1:  # per-rank kernel time (sum of the six stages): shows the skew the all-reduce has to absorb
@@ -261,10 +271,11 @@ def run_mine(args, rank, world, local_rank):
         if e2e:
             e2e["ms"] = float(t[1])
     return dict(ms=ms, ms_instr=ms_instr, gap_ms=gap_ms, stage_ms=stage_ms, stats=stats, launches=n_launch, e2e=e2e, clocks=clk,
-                bucket_bytes=bucket.nbytes, allreduce_ms=allreduce_ms, rank_ms=rank_ms)
+                bucket_bytes=bucket.nbytes, allreduce_ms=allreduce_ms, rank_ms=rank_ms,
+                exchange_rows=(ex.last_rows if sparse else P))
 
 
-def run_e2e(args, cam, d, g, fwd, bwd, bucket, world, dev, sync_all):
+def run_e2e(args, cam, d, g, fwd, bwd, bucket, world, dev, sync_all, ex=None):
     """Same step through the public API with HOST buffers: per step the keyframe (view matrix,
     projection matrix, camera centre, ground-truth RGB image) is copied from pinned host memory, an
     L1 photometric loss on the rendered colour produces dL/dcolour on the device, and the loss
@@ -310,9 +321,14 @@ def run_e2e(args, cam, d, g, fwd, bwd, bucket, world, dev, sync_all):
         loss = diff.abs().sum() * inv_n
         grad_c = torch.sign(diff) * inv_n
         ev_free[k].record(main)
+        if ex is not None:
+            ex.begin_step()
         bwd(dd, res, g[0], grad_c, g[2])
         if world > 1:
-            dist.all_reduce(bucket.flat)
+            if ex is not None:
+                ex.exchange()
+            else:
+                dist.all_reduce(bucket.flat)
         h_loss[k].copy_(loss.reshape(1), non_blocking=True)  # 4-byte D2H of the step's result
         ev_loss[k].record(main)
         if i > 0:  # read the previous step's loss: keeps one step in flight instead of draining the GPU
@@ -460,18 +476,25 @@ def main():
                config=dict(workload="headline: 1 view fwd+bwd per GPU per step, %d Gaussians, %dx%d, SH deg %d (M=%d), "
                                     "F=%d feature channels" % (args.P, args.width, args.height, args.deg,
                                                                (args.deg + 1) ** 2, args.F),
-                           parallelism="view-data-parallel x%d (%s), replicated Gaussians, 1 NCCL all-reduce of %d MB/step" % (
+                           parallelism="view-data-parallel x%d (%s), replicated Gaussians, %s" % (
                                world, "pose of view r on rank r" if args.distinct_views else
                                "same pose, per-rank upstream gradients: equal work per rank",
-                               r["bucket_bytes"] // 1000000) if world > 1 else "single GPU",
+                               "1 NCCL all-reduce of the dense %d MB bucket/step" % (r["bucket_bytes"] // 1000000)
+                               if args.dense_allreduce else
+                               "sparse gradient exchange: NCCL MAX-reduce of the touched flags + SUM-reduce of the "
+                               "%d touched rows (of %d) = %d MB/step" % (
+                                   r["exchange_rows"], args.P,
+                                   r["exchange_rows"] * (r["bucket_bytes"] // args.P) // 1000000)) if world > 1 else "single GPU",
                            l2="inputs (>=300 MB of Gaussian parameters) larger than the 126 MB L2; no flush needed",
                            **{k: r["stats"][k] for k in ("Pvis", "R", "l1_total", "n_eval_fwd", "n_blend", "warp_blended", "n_eval_bwd")}),
                gpu_launches=r["launches"], clocks=r["clocks"], roofline=roof, stages=stages,
                ms_per_step_instrumented=round(r["ms_instr"] / K, 4),
                idle_before_stage_ms={k: round(v / K, 4) for k, v in r["gap_ms"].items()})
     if world > 1:
-        out["allreduce"] = dict(ms=round(r["allreduce_ms"], 4), bytes=r["bucket_bytes"],
-                                busbw_gbs=round(2 * (world - 1) / world * r["bucket_bytes"] / r["allreduce_ms"] / 1e6, 1),
+        xbytes = r["exchange_rows"] * (r["bucket_bytes"] // args.P)
+        out["allreduce"] = dict(ms=round(r["allreduce_ms"], 4), bytes=xbytes, dense_bytes=r["bucket_bytes"],
+                                rows=r["exchange_rows"], mode="dense" if args.dense_allreduce else "sparse",
+                                busbw_gbs=round(2 * (world - 1) / world * xbytes / r["allreduce_ms"] / 1e6, 1),
                                 rank_kernel_ms_per_step=[round(x / K, 4) for x in r["rank_ms"]])
     if r["e2e"]:
         e = r["e2e"]

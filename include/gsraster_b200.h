@@ -141,6 +141,12 @@ int gsr_get_stage_times(float* ms);
  * gsr_get_stage_times call; reading clears it. */
 int gsr_get_stage_gaps(float* ms);
 
+/* Sparse gradient exchange (extension for the view-data-parallel mapping step, no reference equivalent): while a
+ * mask is set, every gsr_backward / gsr_backward_pose call of this thread stores 1 into mask[i] (device memory, P
+ * bytes, zeroed by the caller) for every Gaussian i that received a contribution from the backward blend. All other
+ * Gaussians have exactly-zero parameter gradients, so an exchange over ranks can skip them. NULL disables. */
+int gsr_set_touched_mask(uint8_t* mask);
+
 /* Work counters of a finished forward pass, for the FP32 roofline of the blend kernels
  * (SURVEY.md 8d "N_eval / N_contrib"): replays the blend tests (no blending) and returns on the
  * HOST counts[0] = (pixel, Gaussian) pairs evaluated by a per-pixel early-exit walk,

@@ -30,6 +30,7 @@ thread_local int* g_pinned = nullptr;  // 8 ints of pinned host memory for the n
 // ---- optional per-stage event timing (gsr_set_stage_timing) ----
 struct StageSpan { int stage; cudaEvent_t a, b; };
 thread_local bool g_timing = false;
+thread_local uint8_t* g_touched = nullptr;  // gsr_set_touched_mask
 thread_local std::vector<StageSpan> g_spans;
 thread_local std::vector<cudaEvent_t> g_free_events;
 thread_local float g_gaps[GSR_NUM_STAGES] = {0, 0, 0, 0, 0, 0};  // idle time on the stream before each stage
@@ -249,9 +250,9 @@ static int backward_impl(const gsr_params* p, int num_rendered, const float* bac
 
   {
     StageTimer tm(4, stream);
-    CUDA_TRY(cudaMemsetAsync(g.grad_rows, 0, (size_t)P * gsr::grad_row_floats(p->F) * sizeof(float), stream));
+    CUDA_TRY(cudaMemsetAsync(g.grad_rows, 0, (size_t)P * gsr::grad_row_floats(p->F) * sizeof(float) + (size_t)P, stream));  // rows + touched flags
     if (num_rendered > 0) {
-      gsr::launch_render_backward(p->F, cam, g, b, img, sh_objs, dL_dpix_depth, dL_dpix, dL_dpix_obj, stream);
+      gsr::launch_render_backward(p->F, cam, g, b, img, sh_objs, dL_dpix_depth, dL_dpix, dL_dpix_obj, g_touched, stream);
       g_launches += 1;
     }
   }
@@ -325,6 +326,11 @@ int gsr_get_stage_times(float* ms) {
     g_free_events.push_back(sp.b);
   }
   g_spans.clear();
+  return GSR_OK;
+}
+
+int gsr_set_touched_mask(uint8_t* mask) {
+  g_touched = mask;
   return GSR_OK;
 }
 

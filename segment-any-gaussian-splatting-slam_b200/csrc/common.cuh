@@ -49,7 +49,8 @@ struct GeomState {
   uint32_t* digit_total;  // 256
   uint32_t* block_sums;   // emit_blocks(P) + 8
   int* flags;             // [0] num_rendered, [1] prefiltered-cull error, [2..3] L1 list total (u64)
-  float* grad_rows;       // P * 32 (F=16) or P * 48 (F=32): backward intermediate, see render_bwd.cu
+  float* grad_rows;       // P * 32 (F=16) or P * 64 (F=32): backward intermediate, see render_bwd.cu
+  uint8_t* touched;       // P (directly behind grad_rows, one memset): 1 = the backward blend wrote this Gaussian's row
   double* pose_acc;       // 32: camera-pose gradient accumulators (extension, see preprocess_bwd.cu)
 };
 struct ImageState {
@@ -107,6 +108,8 @@ inline size_t geom_from_chunk(char* chunk, size_t P, GeomState& g, int F = 32) {
   carve(p, g.flags, 8);
   carve(p, g.pose_acc, 32);
   carve(p, g.grad_rows, P * (size_t)grad_row_floats(F));
+  g.touched = reinterpret_cast<uint8_t*>(g.grad_rows + P * (size_t)grad_row_floats(F));
+  p += align_up(P, 256);
   return (size_t)(p - chunk) + 256;
 }
 inline size_t image_from_chunk(char* chunk, int W, int H, ImageState& s) {
@@ -186,7 +189,7 @@ void launch_render_forward(int F, const Cam& cam, const GeomState& g, const BinS
                            float* out_objects, cudaStream_t s);
 void launch_render_backward(int F, const Cam& cam, const GeomState& g, const BinState& b,
                             const ImageState& img, const float* sh_objs, const float* dL_dpix_depth,
-                            const float* dL_dpix, const float* dL_dpix_obj, cudaStream_t s);
+                            const float* dL_dpix, const float* dL_dpix_obj, uint8_t* touched, cudaStream_t s);
 void launch_count_pairs(const Cam& cam, const GeomState& g, const BinState& b, const ImageState& img,
                         unsigned long long* counts, cudaStream_t s);
 struct BwdOutputs {

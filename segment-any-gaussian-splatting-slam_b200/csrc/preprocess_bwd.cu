@@ -32,7 +32,8 @@ template <int F, bool POSE>
 __global__ void __launch_bounds__(PB_THREADS)
 preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restrict__ tiles_touched,
                       const uint8_t* __restrict__ clampedb, const int* __restrict__ radii,
-                      const float* __restrict__ grad_rows, const float4* __restrict__ rec, double* __restrict__ pose_acc,
+                      const float* __restrict__ grad_rows, const uint8_t* __restrict__ touched,
+                      const float4* __restrict__ rec, double* __restrict__ pose_acc,
                       const BwdOutputs out) {
   constexpr int ROW = (F == 16) ? 32 : 64;
   __shared__ CamS cs;
@@ -44,11 +45,15 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
   const int idx = first + threadIdx.x;
   const bool valid = idx < in.P;
   const int M = in.M, D = in.D;
-  const bool visible = valid && radii[idx] > 0;
+  // Gaussians the backward blend never reached have all-zero rows, hence all-zero gradients: only zeros are written
+  const bool visible = valid && radii[idx] > 0 && touched[idx] != 0;
+  const bool any_visible = __syncthreads_or(visible);
   const int SS = (3 * M) | 1;  // odd row stride -> conflict-free per-thread rows
   // SH coefficients of the block's Gaussians: coalesced load into the tile
   const bool sh16 = in.shs != nullptr && M == 16 && (((uintptr_t)in.shs | (uintptr_t)out.dL_dsh) & 15) == 0;
-  if (sh16) {
+  if (!any_visible) {
+    // nothing to read for this block
+  } else if (sh16) {
     const int n = min(PB_THREADS, in.P - first) * 12;
     const float4* src = reinterpret_cast<const float4*>(in.shs) + (size_t)first * 12;
     for (int i = threadIdx.x; i < n; i += PB_THREADS) tile4[(i / 12) * 13 + i % 12] = src[i];
@@ -405,7 +410,7 @@ void launch_preprocess_backward(const FwdInputs& in, const Cam& cam, const GeomS
   const int nb = (in.P + PB_THREADS - 1) / PB_THREADS;
   if (out.dL_dviewmatrix) cudaMemsetAsync(g.pose_acc, 0, 32 * sizeof(double), s);
 #define GSR_LAUNCH_PB(FF, PP)                                                                                      \
-  preprocess_bwd_kernel<FF, PP><<<nb, PB_THREADS, 0, s>>>(in, cam, g.tiles_touched, g.clamped, radii, g.grad_rows, \
+  preprocess_bwd_kernel<FF, PP><<<nb, PB_THREADS, 0, s>>>(in, cam, g.tiles_touched, g.clamped, radii, g.grad_rows, g.touched, \
                                                           g.rec, g.pose_acc, out)
   const bool pose = out.dL_dviewmatrix != nullptr;
   if (in.F == 16) { if (pose) GSR_LAUNCH_PB(16, true); else GSR_LAUNCH_PB(16, false); }

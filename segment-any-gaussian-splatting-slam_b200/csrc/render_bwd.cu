@@ -108,7 +108,8 @@ __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, 
 template <int F>
 __device__ __forceinline__ void flush_slots(float* __restrict__ wbuf, const float4* __restrict__ meta,
                                             const float (*__restrict__ bfrag)[32], int ns, int lane,
-                                            float* __restrict__ grad_rows) {
+                                            float* __restrict__ grad_rows, uint8_t* __restrict__ touched,
+                                            uint8_t* __restrict__ touched_ext) {
   using Cfg = BwdCfg<F>;
   constexpr int NT = Cfg::NT, NC = Cfg::NC, DS = Cfg::DSTRIDE, ROW = Cfg::ROW;
   const int gid = lane >> 2, tig = lane & 3;
@@ -180,6 +181,10 @@ __device__ __forceinline__ void flush_slots(float* __restrict__ wbuf, const floa
       for (int i = 16; i < NC / 2; i++) v[i - 4] = v[i];      // F = 32: features 0..7 follow the 12 specials
     }
     float* row = grad_rows + (size_t)__float_as_uint(m.x) * ROW + (half ? NC / 2 - 4 : 0);
+    if (half == 0) {  // this Gaussian has a non-zero gradient row (K7 skips the others; see also gsr_set_touched_mask)
+      touched[__float_as_uint(m.x)] = 1;
+      if (touched_ext) touched_ext[__float_as_uint(m.x)] = 1;
+    }
 #pragma unroll
     for (int i = 0; i < NC / 8; i++)
       if (half || i + 1 < NC / 8) red_add_v4(row + 4 * i, v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
@@ -194,7 +199,8 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   const float* __restrict__ feats, int W, int H, const float* __restrict__ bg,
                   const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib,
                   const float* __restrict__ dL_dpix_depth, const float* __restrict__ dL_dpix,
-                  const float* __restrict__ dL_dpix_obj, float* __restrict__ grad_rows) {
+                  const float* __restrict__ dL_dpix_obj, float* __restrict__ grad_rows,
+                  uint8_t* __restrict__ touched, uint8_t* __restrict__ touched_ext) {
   using Cfg = BwdCfg<F>;
   constexpr int BB = Cfg::BB;
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -306,7 +312,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         // two hits per iteration (the second may be absent): their geometry / alpha / dot-product chains are
         // independent, only the T and S recurrences are serial
         if (ns > SLOTS - 2) {
-          flush_slots<F>(wbuf, sm.meta[warp], sm.bfrag[warp], ns, lane, grad_rows);
+          flush_slots<F>(wbuf, sm.meta[warp], sm.bfrag[warp], ns, lane, grad_rows, touched, touched_ext);
           ns = 0;
           wp = wbuf + lane;
         }
@@ -376,12 +382,12 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     }
     __syncthreads();  // release stage st for the copy issued at the top of the next iteration
   }
-  if (ns > 0) flush_slots<F>(wbuf, sm.meta[warp], sm.bfrag[warp], ns, lane, grad_rows);
+  if (ns > 0) flush_slots<F>(wbuf, sm.meta[warp], sm.bfrag[warp], ns, lane, grad_rows, touched, touched_ext);
 }
 
 void launch_render_backward(int F, const Cam& cam, const GeomState& g, const BinState& b, const ImageState& img,
                             const float* sh_objs, const float* dL_dpix_depth, const float* dL_dpix,
-                            const float* dL_dpix_obj, cudaStream_t s) {
+                            const float* dL_dpix_obj, uint8_t* touched, cudaStream_t s) {
   dim3 grid(cam.gx, cam.gy), block(256);
   static bool attr_set = false;
   if (!attr_set) {
@@ -392,11 +398,11 @@ void launch_render_backward(int F, const Cam& cam, const GeomState& g, const Bin
   if (F == 16)
     render_bwd_kernel<16><<<grid, block, sizeof(BwdSmem<16>), s>>>(
         img.ranges, b.point_list, b.hitw, g.rec, sh_objs, cam.W, cam.H, cam.bg, img.final_T, img.n_contrib,
-        dL_dpix_depth, dL_dpix, dL_dpix_obj, g.grad_rows);
+        dL_dpix_depth, dL_dpix, dL_dpix_obj, g.grad_rows, g.touched, touched);
   else
     render_bwd_kernel<32><<<grid, block, sizeof(BwdSmem<32>), s>>>(
         img.ranges, b.point_list, b.hitw, g.rec, sh_objs, cam.W, cam.H, cam.bg, img.final_T, img.n_contrib,
-        dL_dpix_depth, dL_dpix, dL_dpix_obj, g.grad_rows);
+        dL_dpix_depth, dL_dpix, dL_dpix_obj, g.grad_rows, g.touched, touched);
 }
 
 }  // namespace gsr

@@ -49,6 +49,7 @@ def lib():
         L.gsr_count_pairs.argtypes = [C.POINTER(Params), C.c_int] + [C.c_void_p] * 3 + [C.POINTER(C.c_ulonglong)]
         L.gsr_get_stage_times.argtypes = [C.POINTER(C.c_float)]
         L.gsr_get_stage_gaps.argtypes = [C.POINTER(C.c_float)]
+        L.gsr_set_touched_mask.argtypes = [C.c_void_p]
         L.gsr_last_forward_stats.argtypes = [C.POINTER(C.c_ulonglong)]
         L.gsr_set_stage_timing.argtypes = [C.c_int]
         _lib = L
@@ -281,6 +282,13 @@ def get_stage_times():
     ms = (C.c_float * len(STAGES))()
     _check(lib().gsr_get_stage_times(ms))
     return dict(zip(STAGES, [float(v) for v in ms]))
+
+
+def set_touched_mask(mask):
+    """mask: CUDA uint8 tensor of P elements (zeroed by the caller) or None; see gsr_set_touched_mask."""
+    if mask is not None and (mask.dtype != torch.uint8 or not mask.is_cuda or not mask.is_contiguous()):
+        raise RuntimeError("touched mask must be a contiguous CUDA uint8 tensor")
+    _check(lib().gsr_set_touched_mask(None if mask is None else mask.data_ptr()))
 
 
 def get_stage_gaps():

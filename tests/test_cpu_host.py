@@ -143,6 +143,45 @@ def test_mapping_step_gloo_world2():
     assert res[0][2] == res[1][2]
 
 
+def _sparse_worker(rank, world, port, q):
+    import torch.distributed as dist
+    from gsraster_b200 import mapping
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    P, M, F = 1000, 4, 16
+    g = torch.Generator().manual_seed(100 + rank)
+    bucket = mapping.GradBucket(P, M, F, "cpu")
+    ex = mapping.SparseGradExchange(bucket)
+    ex.begin_step()
+    rows = torch.randperm(P, generator=g)[:150 + 50 * rank]  # each rank touches its own subset
+    for k, n in ex.sizes:
+        bucket.views[k].view(P, n)[rows] = torch.randn(len(rows), n, generator=g)
+    ex.touched[rows] = 1
+    dense = bucket.flat.clone()
+    dist.all_reduce(dense)                       # the dense exchange is the oracle
+    idx, views = ex.exchange()
+    ex.scatter_dense(idx, views)
+    q.put((rank, int(idx.numel()), float((bucket.flat - dense).abs().max()), float(dense.abs().max()),
+           bool((idx[1:] > idx[:-1]).all())))
+    dist.destroy_process_group()
+
+
+def test_sparse_grad_exchange_matches_dense_allreduce_gloo_world2():
+    import torch.multiprocessing as mp
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_sparse_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert res[0][1] == res[1][1] and 200 <= res[0][1] <= 350   # union of 150 and 200 random rows out of 1000
+    for rank, U, err, mx, sorted_ in res:
+        assert sorted_ and mx > 0 and err <= 1e-6 * mx, (rank, err, mx)
+
+
 def test_dropin_modules_import_and_validate_like_the_reference():
     from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer, rasterize_gaussians  # noqa: F401
     import simple_knn._C as knn

@@ -447,3 +447,31 @@ def test_knn_config5_5M_points():
     mine = capi.distCUDA2(torch.from_numpy(pts).cuda())
     ref = h.run_ref_knn(pts)
     assert torch.equal(mine.view(torch.int32), ref.view(torch.int32))
+
+
+@pytest.mark.gpu
+def test_touched_mask_marks_exactly_the_nonzero_gradient_rows():
+    """gsr_set_touched_mask: Gaussians the backward blend did not reach have exactly-zero parameter gradients
+    (that is what lets the multi-GPU exchange skip them); touched ones are a small part of the scene."""
+    import torch
+    from gsraster_b200 import capi
+    W, H, P = 640, 512, 60000
+    sc = scenes.make_scene(P, sh_degree=3, F=16, seed=21, W=W, H=H)
+    cam = scenes.make_camera(W, H, 1)
+    grads = scenes.make_upstream_grads(W, H, 16)
+    mask = torch.zeros(P, dtype=torch.uint8, device="cuda")
+    capi.set_touched_mask(mask)
+    try:
+        mine = h.run_mine(sc, cam, grads)
+    finally:
+        capi.set_touched_mask(None)
+    m = mask.bool()
+    assert 0 < int(m.sum()) < P
+    for k in h.GRAD_KEYS:
+        gk = mine[k].reshape(P, -1)
+        assert float(gk[~m].abs().max()) == 0.0, k
+    # and every row with a non-zero gradient is flagged
+    nz = torch.zeros(P, dtype=torch.bool, device="cuda")
+    for k in h.GRAD_KEYS:
+        nz |= mine[k].reshape(P, -1).abs().sum(1) > 0
+    assert bool((nz & ~m).sum() == 0)
