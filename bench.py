@@ -188,7 +188,8 @@ def run_mine(args, rank, world, local_rank):
                 a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 a.record()
             if sparse:
-                ex.exchange()      # flags MAX-reduce, nonzero (host sync), row gather, SUM-reduce of the touched rows
+                ex.exchange()      # flags all-gather, union scan, row gather, SUM-reduce of the touched rows: all queued
+                ex.finish()        # count read-back (dense fallback if the capacity guess was too small)
             else:
                 dist.all_reduce(bucket.flat)
             if ar_events is not None:
@@ -327,6 +328,7 @@ def run_e2e(args, cam, d, g, fwd, bwd, bucket, world, dev, sync_all, ex=None):
         if world > 1:
             if ex is not None:
                 ex.exchange()
+                ex.finish()
             else:
                 dist.all_reduce(bucket.flat)
         h_loss[k].copy_(loss.reshape(1), non_blocking=True)  # 4-byte D2H of the step's result
@@ -481,7 +483,7 @@ def main():
                                "same pose, per-rank upstream gradients: equal work per rank",
                                "1 NCCL all-reduce of the dense %d MB bucket/step" % (r["bucket_bytes"] // 1000000)
                                if args.dense_allreduce else
-                               "sparse gradient exchange: NCCL MAX-reduce of the touched flags + SUM-reduce of the "
+                               "sparse gradient exchange: NCCL all-gather of the touched flags + SUM-reduce of the "
                                "%d touched rows (of %d) = %d MB/step" % (
                                    r["exchange_rows"], args.P,
                                    r["exchange_rows"] * (r["bucket_bytes"] // args.P) // 1000000)) if world > 1 else "single GPU",

@@ -146,6 +146,18 @@ int gsr_get_stage_gaps(float* ms);
  * bytes, zeroed by the caller) for every Gaussian i that received a contribution from the backward blend. All other
  * Gaussians have exactly-zero parameter gradients, so an exchange over ranks can skip them. NULL disables. */
 int gsr_set_touched_mask(uint8_t* mask);
+/* Union + compaction of the all-gathered flags: flags = nranks rows of Ppad bytes (Ppad >= P, multiple of 4, 4-byte
+ * aligned). Writes the ascending indices of the Gaussians flagged by any rank to idx[0 : min(count, cap)] and the union
+ * size to *count (device memory, stays on the device). Every rank computes the same list from the same gathered flags.
+ * scratch: gsr_exchange_scratch_bytes(P) bytes of device memory. Stream-ordered, no host synchronisation. */
+size_t gsr_exchange_scratch_bytes(int P);
+int gsr_exchange_compact(const uint8_t* flags, int nranks, int P, int Ppad, int cap, int* idx, int* count, char* scratch,
+                         void* stream);
+/* Row gather (scatter = 0): compact[t][r][:] = dense[t][idx[r]][:] for r < min(*count, cap), zeros up to cap; or row
+ * scatter (scatter = 1): dense[t][idx[r]][:] = compact[t][r][:]. t < ntensors <= 8 tensors of floats_per_row[t] floats per
+ * Gaussian; the pointer arrays are HOST arrays of device pointers. */
+int gsr_exchange_rows(int scatter, int ntensors, const float* const* dense, float* const* compact,
+                      const int* floats_per_row, const int* idx, const int* count, int cap, void* stream);
 
 /* Work counters of a finished forward pass, for the FP32 roofline of the blend kernels
  * (SURVEY.md 8d "N_eval / N_contrib"): replays the blend tests (no blending) and returns on the

@@ -13,6 +13,11 @@
 #include "common.cuh"
 
 namespace gsr {
+size_t exchange_scratch_bytes(int P);
+void launch_union_compact(const uint8_t* flags, int nranks, int P, int Ppad, int cap, int* idx, int* count, char* scratch,
+                          cudaStream_t s);
+void launch_rows(bool scatter, int ntensors, const float* const* src, float* const* dst, const int* n, const int* idx,
+                 const int* count, int cap, cudaStream_t s);
 void launch_export_keys(int T, const uint2* ranges, const uint32_t* point_list, const float4* rec, uint64_t* keys,
                         cudaStream_t s);
 }
@@ -331,6 +336,35 @@ int gsr_get_stage_times(float* ms) {
 
 int gsr_set_touched_mask(uint8_t* mask) {
   g_touched = mask;
+  return GSR_OK;
+}
+
+size_t gsr_exchange_scratch_bytes(int P) { return gsr::exchange_scratch_bytes(P > 0 ? P : 1); }
+
+int gsr_exchange_compact(const uint8_t* flags, int nranks, int P, int Ppad, int cap, int* idx, int* count, char* scratch,
+                         void* stream_) {
+  if (!flags || !idx || !count || !scratch || nranks <= 0 || P <= 0 || Ppad < P || (Ppad & 3) || cap < 0 ||
+      ((uintptr_t)flags & 3))
+    return fail(GSR_ERR_INVALID_ARGUMENT, "exchange_compact: bad argument");
+  gsr::launch_union_compact(flags, nranks, P, Ppad, cap, idx, count, scratch, (cudaStream_t)stream_);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "exchange_compact: %s", cudaGetErrorString(e));
+  return GSR_OK;
+}
+
+int gsr_exchange_rows(int scatter, int ntensors, const float* const* dense, float* const* compact, const int* floats_per_row,
+                      const int* idx, const int* count, int cap, void* stream_) {
+  if (ntensors <= 0 || ntensors > 8 || !dense || !compact || !floats_per_row || !idx || !count || cap < 0)
+    return fail(GSR_ERR_INVALID_ARGUMENT, "exchange_rows: bad argument");
+  if (scatter) {  // compact -> dense
+    const float* src[8]; float* dst[8];
+    for (int k = 0; k < ntensors; k++) { src[k] = compact[k]; dst[k] = const_cast<float*>(dense[k]); }
+    gsr::launch_rows(true, ntensors, src, dst, floats_per_row, idx, count, cap, (cudaStream_t)stream_);
+  } else {
+    gsr::launch_rows(false, ntensors, dense, compact, floats_per_row, idx, count, cap, (cudaStream_t)stream_);
+  }
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "exchange_rows: %s", cudaGetErrorString(e));
   return GSR_OK;
 }
 

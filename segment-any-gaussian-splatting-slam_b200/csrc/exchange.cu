@@ -1,0 +1,158 @@
+// Sparse gradient exchange helpers for the view-data-parallel mapping step (no reference equivalent;
+// gsraster_b200/mapping.py: SparseGradExchange). The backward blend flags the Gaussians it reached;
+// after an all-gather of the flags every rank builds the same sorted index list of the union and packs
+// the union's rows of the dense gradient bucket into a compact tensor-major buffer for the all-reduce.
+// All of it is stream-ordered, the count stays on the device.
+#include "common.cuh"
+
+namespace gsr {
+
+constexpr int XC_THREADS = 256;
+constexpr int XC_PER_T = 4;
+constexpr int XC_TILE = XC_THREADS * XC_PER_T;  // Gaussians per block
+
+__device__ __forceinline__ uint32_t union4(const uint8_t* __restrict__ flags, int nranks, size_t P, size_t g) {
+  // 4 consecutive flag bytes, OR over ranks (P % 4 == 0 is not required: callers bound-check per byte)
+  uint32_t u = 0;
+  for (int r = 0; r < nranks; r++) u |= *reinterpret_cast<const uint32_t*>(flags + (size_t)r * P + g);
+  return u;
+}
+
+// pass 1: per-block union counts
+__global__ void __launch_bounds__(XC_THREADS)
+xc_count_kernel(const uint8_t* __restrict__ flags, int nranks, int P, int Ppad, uint32_t* __restrict__ block_cnt) {
+  __shared__ uint32_t wsum[XC_THREADS / 32];
+  const int g0 = blockIdx.x * XC_TILE + threadIdx.x * XC_PER_T;
+  uint32_t c = 0;
+  if (g0 < P) {
+    const uint32_t u = union4(flags, nranks, (size_t)Ppad, (size_t)g0);
+#pragma unroll
+    for (int k = 0; k < 4; k++) c += (g0 + k < P && ((u >> (8 * k)) & 0xffu)) ? 1u : 0u;
+  }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = c;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t t = 0;
+    for (int w = 0; w < XC_THREADS / 32; w++) t += wsum[w];
+    block_cnt[blockIdx.x] = t;
+  }
+}
+// pass 2: exclusive scan of the block counts (one block), total -> count
+__global__ void __launch_bounds__(1024)
+xc_scan_kernel(uint32_t* __restrict__ block_cnt, int nb, int* __restrict__ count) {
+  __shared__ uint32_t wsum[32];
+  __shared__ uint32_t carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int base = 0; base < nb; base += 1024) {
+    const int i = base + threadIdx.x;
+    const uint32_t v = i < nb ? block_cnt[i] : 0u;
+    uint32_t incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    if (lane == 31) wsum[warp] = incl;
+    __syncthreads();
+    uint32_t woff = 0;
+    for (int k = 0; k < warp; k++) woff += wsum[k];
+    const uint32_t c = carry;
+    if (i < nb) block_cnt[i] = c + woff + incl - v;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry = c + woff + incl;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *count = (int)carry;
+}
+// pass 3: ranked writes of the union's indices (ascending), entries >= cap are dropped
+__global__ void __launch_bounds__(XC_THREADS)
+xc_write_kernel(const uint8_t* __restrict__ flags, int nranks, int P, int Ppad, const uint32_t* __restrict__ block_off,
+                int cap, int* __restrict__ idx) {
+  __shared__ uint32_t wsum[XC_THREADS / 32];
+  const int g0 = blockIdx.x * XC_TILE + threadIdx.x * XC_PER_T;
+  uint32_t u = 0, c = 0;
+  if (g0 < P) {
+    u = union4(flags, nranks, (size_t)Ppad, (size_t)g0);
+#pragma unroll
+    for (int k = 0; k < 4; k++) c += (g0 + k < P && ((u >> (8 * k)) & 0xffu)) ? 1u : 0u;
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t incl = c;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  if (lane == 31) wsum[warp] = incl;
+  __syncthreads();
+  uint32_t pos = block_off[blockIdx.x] + incl - c;
+  for (int k = 0; k < warp; k++) pos += wsum[k];
+#pragma unroll
+  for (int k = 0; k < 4; k++)
+    if (g0 + k < P && ((u >> (8 * k)) & 0xffu)) {
+      if ((int)pos < cap) idx[pos] = g0 + k;
+      pos++;
+    }
+}
+
+// compact[t][r][:] = dense[t][idx[r]][:] for r < min(count, cap), zeros for the other rows up to cap.
+// One warp per row; tensors are listed by (dense base, compact base, floats per row).
+struct XcTensors {
+  const float* src[8];
+  float* dst[8];
+  int n[8];
+  int count;
+};
+__global__ void __launch_bounds__(256)
+xc_gather_kernel(XcTensors t, const int* __restrict__ idx, const int* __restrict__ count, int cap) {
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (row >= cap) return;
+  const bool live = row < *count;
+  const size_t g = live ? (size_t)idx[row] : 0;
+  for (int k = 0; k < t.count; k++) {
+    const int n = t.n[k];
+    const float* s = t.src[k] + g * n;
+    float* d = t.dst[k] + (size_t)row * n;
+    for (int i = lane; i < n; i += 32) d[i] = live ? s[i] : 0.f;
+  }
+}
+// dense[t][idx[r]][:] = compact[t][r][:] for r < min(count, cap) (the caller zeroes dense first)
+__global__ void __launch_bounds__(256)
+xc_scatter_kernel(XcTensors t, const int* __restrict__ idx, const int* __restrict__ count, int cap) {
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (row >= cap || row >= *count) return;
+  const size_t g = (size_t)idx[row];
+  for (int k = 0; k < t.count; k++) {
+    const int n = t.n[k];
+    const float* s = t.src[k] + (size_t)row * n;
+    float* d = const_cast<float*>(t.dst[k]) + g * n;
+    for (int i = lane; i < n; i += 32) d[i] = s[i];
+  }
+}
+
+size_t exchange_scratch_bytes(int P) { return ((size_t)(P + XC_TILE - 1) / XC_TILE + 8) * sizeof(uint32_t); }
+
+void launch_union_compact(const uint8_t* flags, int nranks, int P, int Ppad, int cap, int* idx, int* count,
+                          char* scratch, cudaStream_t s) {
+  const int nb = (P + XC_TILE - 1) / XC_TILE;
+  uint32_t* block_cnt = reinterpret_cast<uint32_t*>(scratch);
+  xc_count_kernel<<<nb, XC_THREADS, 0, s>>>(flags, nranks, P, Ppad, block_cnt);
+  xc_scan_kernel<<<1, 1024, 0, s>>>(block_cnt, nb, count);
+  xc_write_kernel<<<nb, XC_THREADS, 0, s>>>(flags, nranks, P, Ppad, block_cnt, cap, idx);
+}
+void launch_rows(bool scatter, int ntensors, const float* const* src, float* const* dst, const int* n, const int* idx,
+                 const int* count, int cap, cudaStream_t s) {
+  XcTensors t;
+  t.count = ntensors;
+  for (int k = 0; k < ntensors; k++) { t.src[k] = src[k]; t.dst[k] = dst[k]; t.n[k] = n[k]; }
+  if (cap <= 0) return;
+  const int nb = (cap + 7) / 8;
+  if (scatter) xc_scatter_kernel<<<nb, 256, 0, s>>>(t, idx, count, cap);
+  else xc_gather_kernel<<<nb, 256, 0, s>>>(t, idx, count, cap);
+}
+
+}  // namespace gsr

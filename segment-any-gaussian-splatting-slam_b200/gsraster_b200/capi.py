@@ -36,7 +36,7 @@ def lib():
         L = C.CDLL(LIB_PATH)
         L.gsr_last_error.restype = C.c_char_p
         L.gsr_version.restype = C.c_char_p
-        for n in ("gsr_geom_bytes", "gsr_image_bytes", "gsr_binning_bytes", "gsr_knn_scratch_bytes"):
+        for n in ("gsr_exchange_scratch_bytes", "gsr_geom_bytes", "gsr_image_bytes", "gsr_binning_bytes", "gsr_knn_scratch_bytes"):
             getattr(L, n).restype = C.c_size_t
         L.gsr_binning_bytes.argtypes = [C.c_int64]
         L.gsr_forward.argtypes = [C.POINTER(Params), ALLOC_FN, C.c_void_p, ALLOC_FN, C.c_void_p, ALLOC_FN,
@@ -50,6 +50,11 @@ def lib():
         L.gsr_get_stage_times.argtypes = [C.POINTER(C.c_float)]
         L.gsr_get_stage_gaps.argtypes = [C.POINTER(C.c_float)]
         L.gsr_set_touched_mask.argtypes = [C.c_void_p]
+        L.gsr_exchange_scratch_bytes.argtypes = [C.c_int]
+        L.gsr_exchange_compact.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                           C.c_void_p, C.c_void_p]
+        L.gsr_exchange_rows.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                                        C.POINTER(C.c_int), C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.gsr_last_forward_stats.argtypes = [C.POINTER(C.c_ulonglong)]
         L.gsr_set_stage_timing.argtypes = [C.c_int]
         _lib = L
@@ -289,6 +294,28 @@ def set_touched_mask(mask):
     if mask is not None and (mask.dtype != torch.uint8 or not mask.is_cuda or not mask.is_contiguous()):
         raise RuntimeError("touched mask must be a contiguous CUDA uint8 tensor")
     _check(lib().gsr_set_touched_mask(None if mask is None else mask.data_ptr()))
+
+
+def exchange_scratch_bytes(P):
+    return int(lib().gsr_exchange_scratch_bytes(int(P)))
+
+
+def exchange_compact(flags, nranks, P, Ppad, cap, idx, count, scratch):
+    """Union + compaction of all-gathered touched flags (gsr_exchange_compact); everything stays on the device."""
+    with torch.cuda.device(flags.device):
+        _check(lib().gsr_exchange_compact(flags.data_ptr(), int(nranks), int(P), int(Ppad), int(cap), idx.data_ptr(),
+                                          count.data_ptr(), scratch.data_ptr(), _stream_ptr()))
+
+
+def exchange_rows(scatter, dense, compact, floats_per_row, idx, count, cap):
+    """Row gather (dense -> compact) or scatter (compact -> dense) of the bucket tensors (gsr_exchange_rows)."""
+    n = len(dense)
+    dp = (C.c_void_p * n)(*[t.data_ptr() for t in dense])
+    cp = (C.c_void_p * n)(*[t.data_ptr() for t in compact])
+    fp = (C.c_int * n)(*[int(v) for v in floats_per_row])
+    with torch.cuda.device(idx.device):
+        _check(lib().gsr_exchange_rows(int(bool(scatter)), n, dp, cp, fp, idx.data_ptr(), count.data_ptr(), int(cap),
+                                       _stream_ptr()))
 
 
 def get_stage_gaps():

@@ -147,21 +147,26 @@ def _sparse_worker(rank, world, port, q):
     import torch.distributed as dist
     from gsraster_b200 import mapping
     dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
-    P, M, F = 1000, 4, 16
+    P, M, F = 5000, 4, 16
     g = torch.Generator().manual_seed(100 + rank)
     bucket = mapping.GradBucket(P, M, F, "cpu")
     ex = mapping.SparseGradExchange(bucket)
-    ex.begin_step()
-    rows = torch.randperm(P, generator=g)[:150 + 50 * rank]  # each rank touches its own subset
-    for k, n in ex.sizes:
-        bucket.views[k].view(P, n)[rows] = torch.randn(len(rows), n, generator=g)
-    ex.touched[rows] = 1
-    dense = bucket.flat.clone()
-    dist.all_reduce(dense)                       # the dense exchange is the oracle
-    idx, views = ex.exchange()
-    ex.scatter_dense(idx, views)
-    q.put((rank, int(idx.numel()), float((bucket.flat - dense).abs().max()), float(dense.abs().max()),
-           bool((idx[1:] > idx[:-1]).all())))
+    out = []
+    for step, nrows in enumerate((150, 150, 2000)):   # step 0: cap = P; step 1: guessed cap; step 2: overflow -> dense fallback
+        ex.begin_step()
+        bucket.flat.zero_()
+        rows = torch.randperm(P, generator=g)[:nrows + 50 * rank]  # each rank touches its own subset
+        for k, n in ex.sizes:
+            bucket.views[k].view(P, n)[rows] = torch.randn(len(rows), n, generator=g)
+        ex.touched[rows] = 1
+        dense = bucket.flat.clone()
+        dist.all_reduce(dense)                       # the dense exchange is the oracle
+        ex.exchange()
+        idx, views = ex.finish()
+        ex.scatter_dense(idx, views)
+        out.append((int(idx.numel()), float((bucket.flat - dense).abs().max()), float(dense.abs().max()),
+                    bool((idx[1:] > idx[:-1]).all()), ex.fallbacks, ex.cap))
+    q.put((rank, out))
     dist.destroy_process_group()
 
 
@@ -177,9 +182,15 @@ def test_sparse_grad_exchange_matches_dense_allreduce_gloo_world2():
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
-    assert res[0][1] == res[1][1] and 200 <= res[0][1] <= 350   # union of 150 and 200 random rows out of 1000
-    for rank, U, err, mx, sorted_ in res:
-        assert sorted_ and mx > 0 and err <= 1e-6 * mx, (rank, err, mx)
+    a, b = sorted(res)[0][1], sorted(res)[1][1]
+    for sa, sb in zip(a, b):
+        assert sa[0] == sb[0]                       # same union on both ranks
+    assert 300 <= a[0][0] <= 350 and a[2][0] > 2500
+    assert [s_[4] for s_ in a] == [0, 0, 1]         # only the third step overflowed its guessed capacity
+    assert a[0][5] == 1024                          # the capacity guess shrank after the first step
+    for out in (a, b):
+        for U, err, mx, sorted_, _, _ in out:
+            assert sorted_ and mx > 0 and err <= 1e-6 * mx, (err, mx)
 
 
 def test_dropin_modules_import_and_validate_like_the_reference():

@@ -475,3 +475,38 @@ def test_touched_mask_marks_exactly_the_nonzero_gradient_rows():
     for k in h.GRAD_KEYS:
         nz |= mine[k].reshape(P, -1).abs().sum(1) > 0
     assert bool((nz & ~m).sum() == 0)
+
+
+@pytest.mark.gpu
+def test_exchange_kernels_match_torch_reference():
+    """csrc/exchange.cu: union + compaction of gathered flags and the row gather / scatter, against torch ops."""
+    import torch
+    from gsraster_b200 import capi
+    torch.manual_seed(5)
+    for P, nranks, dens in ((1, 1, 1.0), (4099, 3, 0.02), (250001, 8, 0.3), (100000, 2, 0.0)):
+        Ppad = (P + 3) // 4 * 4
+        flags = torch.zeros(nranks, Ppad, dtype=torch.uint8, device="cuda")
+        flags[:, :P] = (torch.rand(nranks, P, device="cuda") < dens).to(torch.uint8)
+        ref_idx = torch.nonzero(flags[:, :P].amax(0)).squeeze(1)
+        U = int(ref_idx.numel())
+        for cap in (P, max(U // 2, 1)):
+            idx = torch.full((P + 1,), -1, dtype=torch.int32, device="cuda")
+            count = torch.zeros(1, dtype=torch.int32, device="cuda")
+            scratch = torch.empty(capi.exchange_scratch_bytes(P) + 256, dtype=torch.uint8, device="cuda")
+            capi.exchange_compact(flags.view(-1), nranks, P, Ppad, cap, idx, count, scratch)
+            assert int(count) == U
+            k = min(U, cap)
+            assert (idx[:k].long() == ref_idx[:k]).all()
+            assert (idx[k:] == -1).all()            # nothing written past min(count, cap)
+            sizes = (3, 48, 16, 1)
+            dense = [torch.randn(P, n, device="cuda") for n in sizes]
+            comp = [torch.full((cap, n), 7.0, device="cuda") for n in sizes]
+            capi.exchange_rows(False, dense, comp, sizes, idx, count, cap)
+            for d_, c_ in zip(dense, comp):
+                assert (c_[:k] == d_[ref_idx[:k]]).all() and (c_[k:] == 0).all()
+            back = [torch.zeros(P, n, device="cuda") for n in sizes]
+            capi.exchange_rows(True, back, comp, sizes, idx, count, cap)
+            for d_, b_ in zip(dense, back):
+                exp = torch.zeros_like(d_)
+                exp[ref_idx[:k]] = d_[ref_idx[:k]]
+                assert (b_ == exp).all()
