@@ -25,7 +25,12 @@ sort_hist_kernel(const uint64_t* __restrict__ in, int64_t n, int shift, uint32_t
 #pragma unroll 4
   for (int k = 0; k < SORT_IPT; k++) {
     int64_t i = base + (int64_t)k * SORT_THREADS + threadIdx.x;
-    if (i < n) atomicAdd(&hist[(uint32_t)(in[i] >> shift) & mask], 1u);
+    // depth digits are heavily skewed (the top bytes of nearby floats coincide): aggregate equal digits inside the
+    // warp first, one shared-memory atomic per distinct digit instead of 32 serialised ones on the same address
+    const bool ok = i < n;
+    const uint32_t d = ok ? (uint32_t)(in[i] >> shift) & mask : 0xffffffffu;
+    const unsigned peers = __match_any_sync(0xffffffffu, d);
+    if (ok && (threadIdx.x & 31) == (unsigned)__ffs(peers) - 1) atomicAdd(&hist[d], (uint32_t)__popc(peers));
   }
   __syncthreads();
   block_hist[(size_t)threadIdx.x * nblk + blockIdx.x] = hist[threadIdx.x];

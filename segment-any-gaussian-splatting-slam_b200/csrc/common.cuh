@@ -28,8 +28,8 @@ constexpr int TILE_X = 16, TILE_Y = 16;  // fixed by parity: reference config.h:
 // ---------------------------------------------------------------------------------------------
 constexpr int REC4 = 4;  // float4 per Gaussian record
 constexpr int SORT_THREADS = 256;
-constexpr int SORT_IPT = 16;                           // items per thread
-constexpr int SORT_TILE = SORT_THREADS * SORT_IPT;     // 4096 items per block
+constexpr int SORT_IPT = 8;                            // items per thread
+constexpr int SORT_TILE = SORT_THREADS * SORT_IPT;     // 2048 items per block
 constexpr int RADIX = 256;
 constexpr int EMIT_THREADS = 256;
 
