@@ -159,6 +159,32 @@ int gsr_exchange_compact(const uint8_t* flags, int nranks, int P, int Ppad, int 
 int gsr_exchange_rows(int scatter, int ntensors, const float* const* dense, float* const* compact,
                       const int* floats_per_row, const int* idx, const int* count, int cap, void* stream);
 
+/* ---- activation + Adam fused around the rasterizer ---------------------------------------------------
+ * Replaces, for the seven parameter groups of the reference's GaussianModel (scene/gaussian_model.py:247-257:
+ * xyz, f_dc, f_rest, opacity, scaling, rotation, obj_dc; torch.optim.Adam, eps 1e-15), the chain
+ *   activations (gaussian_model.py:109-133) -> rasterizer -> autograd through the activations -> optimizer.step().
+ * All pointers are device memory, fp32, contiguous, in the reference's shapes. */
+typedef struct gsr_adam_tensors {
+  /* raw parameters and Adam moments (same shapes): (P,3) (P,1,3) (P,M-1,3) (P,1) (P,3) (P,4) (P,1,F) */
+  float *xyz, *f_dc, *f_rest, *opacity, *scaling, *rotation, *objects;
+  float *m_xyz, *m_f_dc, *m_f_rest, *m_opacity, *m_scaling, *m_rotation, *m_objects;
+  float *v_xyz, *v_f_dc, *v_f_rest, *v_opacity, *v_scaling, *v_rotation, *v_objects;
+  /* gradients w.r.t. the ACTIVATED values as the rasterizer returns them: dL_dmeans3D (R,3), dL_dsh (R,M,3),
+   * dL_dobjects (R,F), dL_dopacity (R,1), dL_dscales (R,3), dL_drotations (R,4); R = P (dense) or cap (sparse) rows */
+  const float *g_means3D, *g_sh, *g_objects, *g_opacity, *g_scales, *g_rotations;
+  /* activated values the next gsr_forward reads: shs (P,M,3) = cat(f_dc, f_rest), sigmoid(opacity) (P,1),
+   * exp(scaling) (P,3), normalize(rotation) (P,4); xyz and objects are passed to the rasterizer as they are */
+  float *a_shs, *a_opacities, *a_scales, *a_rotations;
+} gsr_adam_tensors;
+/* a_* of all P Gaussians from the raw parameters (first iteration, after map growth). */
+int gsr_activate(const gsr_adam_tensors* t, int P, int M, void* stream);
+/* One Adam step (step = 1, 2, ...; lr[7] in the group order above) + re-activation of the stepped rows.
+ * idx == NULL: dense, every Gaussian is stepped with its gradient row (zero rows included) = torch.optim.Adam.
+ * idx != NULL: sparse, rows r < min(*count, cap) step Gaussian idx[r] with gradient row r (the output of
+ * gsr_exchange_rows + all-reduce); the moments of all other Gaussians are left alone (torch.optim.SparseAdam). */
+int gsr_adam_step(const gsr_adam_tensors* t, int P, int M, int F, const float* lr, float beta1, float beta2, float eps,
+                  int step, const int* idx, const int* count, int cap, void* stream);
+
 /* Work counters of a finished forward pass, for the FP32 roofline of the blend kernels
  * (SURVEY.md 8d "N_eval / N_contrib"): replays the blend tests (no blending) and returns on the
  * HOST counts[0] = (pixel, Gaussian) pairs evaluated by a per-pixel early-exit walk,

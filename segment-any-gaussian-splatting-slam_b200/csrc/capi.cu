@@ -13,6 +13,9 @@
 #include "common.cuh"
 
 namespace gsr {
+void launch_adam(const gsr_adam_tensors& t, int P, int M, int F, const float* lr, float beta1, float beta2, float eps,
+                 int step, const int* idx, const int* count, int cap, cudaStream_t s);
+void launch_activate(const gsr_adam_tensors& t, int P, int M, cudaStream_t s);
 size_t exchange_scratch_bytes(int P);
 void launch_union_compact(const uint8_t* flags, int nranks, int P, int Ppad, int cap, int* idx, int* count, char* scratch,
                           cudaStream_t s);
@@ -365,6 +368,31 @@ int gsr_exchange_rows(int scatter, int ntensors, const float* const* dense, floa
   }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "exchange_rows: %s", cudaGetErrorString(e));
+  return GSR_OK;
+}
+
+int gsr_activate(const gsr_adam_tensors* t, int P, int M, void* stream_) {
+  if (!t || P < 0 || M < 1 || M > 16) return fail(GSR_ERR_INVALID_ARGUMENT, "activate: bad argument");
+  if (!t->f_dc || (M > 1 && !t->f_rest) || !t->opacity || !t->scaling || !t->rotation || !t->a_shs || !t->a_opacities ||
+      !t->a_scales || !t->a_rotations)
+    return fail(GSR_ERR_INVALID_ARGUMENT, "activate: NULL tensor");
+  gsr::launch_activate(*t, P, M, (cudaStream_t)stream_);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "activate: %s", cudaGetErrorString(e));
+  return GSR_OK;
+}
+
+int gsr_adam_step(const gsr_adam_tensors* t, int P, int M, int F, const float* lr, float beta1, float beta2, float eps,
+                  int step, const int* idx, const int* count, int cap, void* stream_) {
+  if (!t || !lr || P < 0 || M < 1 || M > 16 || F < 1 || step < 1 || (idx && (!count || cap < 0)))
+    return fail(GSR_ERR_INVALID_ARGUMENT, "adam_step: bad argument");
+  const float* const* q = reinterpret_cast<const float* const*>(t);
+  for (int i = 0; i < (int)(sizeof(gsr_adam_tensors) / sizeof(float*)); i++)
+    if (!q[i] && !(M == 1 && (i == 2 || i == 9 || i == 16)))  // f_rest and its moments are empty at SH degree 0
+      return fail(GSR_ERR_INVALID_ARGUMENT, "adam_step: NULL tensor (field %d)", i);
+  gsr::launch_adam(*t, P, M, F, lr, beta1, beta2, eps, step, idx, count, cap, (cudaStream_t)stream_);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "adam_step: %s", cudaGetErrorString(e));
   return GSR_OK;
 }
 
