@@ -216,6 +216,12 @@ def run_mine(args, rank, world, local_rank):
                  n_blend=cp["blended"], n_eval_bwd=int(st["n_contrib"].to(torch.int64).sum()),
                  warp_blended=cp["warp_blended"], l1_total=l1_total)
     del st
+    tm = torch.zeros(P, dtype=torch.uint8, device=dev)
+    capi.set_touched_mask(tm)
+    bwd(d, res, g[0], g[1], g[2])
+    capi.set_touched_mask(ex.touched if sparse else None)
+    touched_rows = int(tm.sum())
+    del tm
     clocks = ClockSampler(local_rank)
     clocks.start()  # started a few steps early: nvidia-smi needs tens of ms before its first sample
     for _ in range(3):  # settle the caching allocator again after the statistics pass (untimed, in addition to W)
@@ -273,7 +279,7 @@ def run_mine(args, rank, world, local_rank):
             e2e["ms"] = float(t[1])
     return dict(ms=ms, ms_instr=ms_instr, gap_ms=gap_ms, stage_ms=stage_ms, stats=stats, launches=n_launch, e2e=e2e, clocks=clk,
                 bucket_bytes=bucket.nbytes, allreduce_ms=allreduce_ms, rank_ms=rank_ms,
-                exchange_rows=(ex.last_rows if sparse else P))
+                exchange_rows=(ex.last_rows if sparse else P), touched_rows=touched_rows)
 
 
 def run_e2e(args, cam, d, g, fwd, bwd, bucket, world, dev, sync_all, ex=None):
@@ -351,6 +357,46 @@ def run_e2e(args, cam, d, g, fwd, bwd, bucket, world, dev, sync_all, ex=None):
     ev1.record()
     sync_all()
     return dict(ms=ev0.elapsed_time(ev1), h2d=h2d, d2h=4, loss=loss)
+
+
+def optimizer_leg(args, touched_rows, hbm_gbs):
+    """SURVEY 8f N1 (next row, measured beside the headline): fused activation + Adam on the headline shapes.
+    dense = torch.optim.Adam semantics over all P rows; sparse = only the rows a view's backward pass reached."""
+    import torch
+    from gsraster_b200 import optim
+    P, F, M = args.P, args.F, (args.deg + 1) ** 2
+    dev = torch.device("cuda", torch.cuda.current_device())
+    g = torch.Generator(device=dev).manual_seed(3)
+    r = lambda *s: torch.randn(*s, generator=g, device=dev)
+    raw = dict(xyz=r(P, 3), f_dc=r(P, 1, 3), f_rest=r(P, M - 1, 3), opacity=r(P, 1), scaling=r(P, 3) - 3.0,
+               rotation=r(P, 4), objects=r(P, 1, F))
+    fa = optim.FusedGaussianAdam(raw)
+    grads = dict(means3D=r(P, 3), sh=r(P, M, 3), objects=r(P, F), opacity=r(P, 1), scales=r(P, 3), rotations=r(P, 4))
+    U = max(int(touched_rows), 1)
+    idx = torch.sort(torch.randperm(P, device=dev)[:U])[0].to(torch.int32)
+    cnt = torch.tensor([U], dtype=torch.int32, device=dev)
+
+    def timed(fn, n=20):
+        for _ in range(3):
+            fn()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / n
+
+    dense_ms = timed(lambda: fa.step(grads))
+    sparse_ms = timed(lambda: fa.step(grads, idx=idx, count=cnt))
+    nfl = 11 + 3 * M + F
+    dense_bytes = P * 4 * (7 * nfl + 3 * M + 8)   # p, m, v read + written, gradient read, activated values written
+    return dict(dense_ms=round(dense_ms, 4), dense_gbs=round(dense_bytes / dense_ms / 1e6, 1),
+                dense_frac_of_hbm=round(dense_bytes / dense_ms / 1e6 / hbm_gbs, 3), sparse_rows=U,
+                sparse_ms=round(sparse_ms, 4),
+                note="fused activation + Adam (gsr_adam_step): dense = torch.optim.Adam over all P rows, "
+                     "sparse = the rows one view's backward pass reached; not part of `value`")
 
 
 def cpu_baseline(args, threads=None):
@@ -502,6 +548,11 @@ def main():
         e = r["e2e"]
         out["e2e"] = dict(value=round(world * K / (e["ms"] * 1e-3), 4), unit=UNIT, h2d_bytes_per_step=e["h2d"],
                           d2h_bytes_per_step=e["d2h"], ms_per_step=round(e["ms"] / K, 4))
+    if world == 1:
+        try:
+            out["optimizer_n1"] = optimizer_leg(args, r["touched_rows"], pk["hbm_gbs"])
+        except Exception as ex:  # the leg is informative only; the headline line must still be printed
+            out["optimizer_n1"] = dict(error=repr(ex)[:200])
     if world == 1 and not args.no_cpu_baseline:
         cb = cpu_baseline(args)
         out["cpu_baseline"] = {k: (round(cb[k], 5) if k == "value" else cb[k]) for k in ("value", "unit", "cores", "kind", "sample")}

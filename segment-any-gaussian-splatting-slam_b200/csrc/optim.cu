@@ -98,6 +98,63 @@ adam_step_kernel(const AdamArgs a) {
   }
 }
 
+// Dense mode, part 1: the groups without an activation (xyz, f_dc, f_rest, objects) as ONE flat element range,
+// a thread per element, consecutive threads on consecutive addresses of every stream (p, m, v, gradient, and the
+// concatenated SH output).
+__global__ void __launch_bounds__(256)
+adam_flat_kernel(const AdamArgs a) {
+  const gsr_adam_tensors& t = a.t;
+  const size_t P = (size_t)a.P;
+  const int M = a.M, F = a.F, R = 3 * (M - 1);
+  const size_t e0 = 3 * P, e1 = e0 + 3 * P, e2 = e1 + (size_t)R * P, e3 = e2 + (size_t)F * P;
+  for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < e3; e += (size_t)gridDim.x * blockDim.x) {
+    if (e < e0) {
+      adam_update(t.xyz, t.m_xyz, t.v_xyz, e, t.g_means3D[e], a.lr[0], a);
+    } else if (e < e1) {
+      const size_t i = e - e0, g = i / 3, c = i - 3 * g;
+      t.a_shs[g * 3 * M + c] = adam_update(t.f_dc, t.m_f_dc, t.v_f_dc, i, t.g_sh[g * 3 * M + c], a.lr[1], a);
+    } else if (e < e2) {
+      const size_t i = e - e1, g = i / R, c = i - (size_t)R * g;
+      t.a_shs[g * 3 * M + 3 + c] = adam_update(t.f_rest, t.m_f_rest, t.v_f_rest, i, t.g_sh[g * 3 * M + 3 + c], a.lr[2], a);
+    } else {
+      const size_t i = e - e2;
+      adam_update(t.objects, t.m_objects, t.v_objects, i, t.g_objects[i], a.lr[6], a);
+    }
+  }
+}
+// Dense mode, part 2: opacity, scaling, rotation (8 floats per Gaussian, activations with Jacobians): a thread per Gaussian
+__global__ void __launch_bounds__(256)
+adam_geom_kernel(const AdamArgs a) {
+  const gsr_adam_tensors& t = a.t;
+  const size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= (size_t)a.P) return;
+  {
+    const float o = 1.f / (1.f + expf(-t.opacity[g]));
+    const float pn = adam_update(t.opacity, t.m_opacity, t.v_opacity, g, t.g_opacity[g] * o * (1.f - o), a.lr[3], a);
+    t.a_opacities[g] = 1.f / (1.f + expf(-pn));
+  }
+#pragma unroll
+  for (int c = 0; c < 3; c++) {
+    const float sc = expf(t.scaling[g * 3 + c]);
+    const float pn = adam_update(t.scaling, t.m_scaling, t.v_scaling, g * 3 + c, t.g_scales[g * 3 + c] * sc, a.lr[4], a);
+    t.a_scales[g * 3 + c] = expf(pn);
+  }
+  const float4 x4 = reinterpret_cast<const float4*>(t.rotation)[g];
+  const float4 g4 = reinterpret_cast<const float4*>(t.g_rotations)[g];
+  const float x[4] = {x4.x, x4.y, x4.z, x4.w}, gy[4] = {g4.x, g4.y, g4.z, g4.w};
+  const float n = fmaxf(sqrtf(x[0] * x[0] + x[1] * x[1] + x[2] * x[2] + x[3] * x[3]), 1e-12f);
+  const float inv = 1.f / n;
+  float dot = 0.f;
+#pragma unroll
+  for (int c = 0; c < 4; c++) dot += x[c] * inv * gy[c];
+  float xn[4];
+#pragma unroll
+  for (int c = 0; c < 4; c++)
+    xn[c] = adam_update(t.rotation, t.m_rotation, t.v_rotation, g * 4 + c, (gy[c] - x[c] * inv * dot) * inv, a.lr[5], a);
+  const float n2 = fmaxf(sqrtf(xn[0] * xn[0] + xn[1] * xn[1] + xn[2] * xn[2] + xn[3] * xn[3]), 1e-12f);
+  reinterpret_cast<float4*>(t.a_rotations)[g] = make_float4(xn[0] / n2, xn[1] / n2, xn[2] / n2, xn[3] / n2);
+}
+
 // activated values of every Gaussian from the raw parameters (first iteration / after map growth)
 __global__ void __launch_bounds__(256)
 activate_kernel(const gsr_adam_tensors t, int P, int M) {
@@ -126,9 +183,18 @@ void launch_adam(const gsr_adam_tensors& t, int P, int M, int F, const float* lr
   a.bc1 = (float)(1.0 - pow((double)beta1, (double)step));
   a.bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, (double)step));
   a.P = P; a.M = M; a.F = F; a.idx = idx; a.count = count; a.cap = cap;
-  const int rows = idx ? cap : P;
-  if (rows <= 0) return;
-  adam_step_kernel<<<(rows + 7) / 8, 256, 0, s>>>(a);
+  if (idx) {  // sparse: a warp per listed row
+    if (cap > 0) adam_step_kernel<<<(cap + 7) / 8, 256, 0, s>>>(a);
+    return;
+  }
+  if (P <= 0) return;
+  const bool rot16 = (((uintptr_t)t.rotation | (uintptr_t)t.g_rotations | (uintptr_t)t.a_rotations) & 15) == 0;
+  if (!rot16) {  // unaligned rotation tensors: the generic warp-per-row kernel
+    adam_step_kernel<<<(P + 7) / 8, 256, 0, s>>>(a);
+    return;
+  }
+  adam_flat_kernel<<<148 * 16, 256, 0, s>>>(a);
+  adam_geom_kernel<<<(P + 255) / 256, 256, 0, s>>>(a);
 }
 void launch_activate(const gsr_adam_tensors& t, int P, int M, cudaStream_t s) {
   if (P <= 0) return;
