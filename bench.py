@@ -285,7 +285,7 @@ def run_mine(args, rank, world, local_rank):
 def run_e2e(args, cam, d, g, fwd, bwd, bucket, world, dev, sync_all, ex=None):
     """Same step through the public API with HOST buffers: per step the keyframe (view matrix,
     projection matrix, camera centre, ground-truth RGB image) is copied from pinned host memory, an
-    L1 photometric loss on the rendered colour produces dL/dcolour on the device, and the loss
+    the reference's masked L1 photometric loss (gsr_photometric_loss, lambda_dssim = 0) on the rendered colour produces dL/dcolour on the device, and the loss
     scalar is read back. Gaussian parameters stay resident (they are the optimiser's state)."""
     import torch
     import torch.distributed as dist
@@ -301,7 +301,10 @@ def run_e2e(args, cam, d, g, fwd, bwd, bucket, world, dev, sync_all, ex=None):
     gt = [torch.empty(3, H, W, device=dev) for _ in range(2)]  # double-buffered: the copy of step i overlaps step i's forward
     h_loss = [torch.zeros(1).pin_memory() for _ in range(2)]
     h2d = sum(t.numel() * 4 for t in (h_view, h_proj, h_campos, h_gt))
-    inv_n = 1.0 / (3 * H * W)
+    from gsraster_b200 import losses
+    ploss = losses.PhotometricLoss(H, W, 0.0, device=dev)  # lambda_dssim = 0: masked L1 (the SSIM kernels are measured in loss_n2)
+    loss3 = [torch.empty(3, device=dev) for _ in range(2)]
+    grad_buf = torch.empty(3, H, W, device=dev)
     copy_stream = torch.cuda.Stream(device=dev)
     ev_gt = [torch.cuda.Event() for _ in range(2)]
     ev_free = [torch.cuda.Event() for _ in range(2)]
@@ -324,9 +327,9 @@ def run_e2e(args, cam, d, g, fwd, bwd, bucket, world, dev, sync_all, ex=None):
         dd["campos"].copy_(h_campos, non_blocking=True)
         res = fwd(dd)
         main.wait_event(ev_gt[k])
-        diff = res[2] - gt[k]
-        loss = diff.abs().sum() * inv_n
-        grad_c = torch.sign(diff) * inv_n
+        # masked L1 photometric loss (loss_utils.py:17-20), value and dL/dcolour in one fused pass
+        out3, grad_c = ploss(res[2], gt[k], out=loss3[k], grad_out=grad_buf)
+        loss = out3[0:1]
         ev_free[k].record(main)
         if ex is not None:
             ex.begin_step()
@@ -397,6 +400,32 @@ def optimizer_leg(args, touched_rows, hbm_gbs):
                 sparse_ms=round(sparse_ms, 4),
                 note="fused activation + Adam (gsr_adam_step): dense = torch.optim.Adam over all P rows, "
                      "sparse = the rows one view's backward pass reached; not part of `value`")
+
+
+def loss_leg(args, hbm_gbs):
+    """SURVEY 8f N2 (next row): fused photometric loss (value + gradient) on the headline image size."""
+    import torch
+    from gsraster_b200 import losses
+    H, W = args.height, args.width
+    dev = torch.device("cuda", torch.cuda.current_device())
+    gt = torch.rand(3, H, W, device=dev)
+    img = (gt + 0.1 * torch.randn(3, H, W, device=dev)).clamp(0, 1)
+    pl = losses.PhotometricLoss(H, W, 0.2, device=dev)
+    out3, grad = torch.empty(3, device=dev), torch.empty_like(img)
+    for _ in range(3):
+        pl(img, gt, out=out3, grad_out=grad)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(20):
+        pl(img, gt, out=out3, grad_out=grad)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 20
+    nbytes = 3 * H * W * 4 * (2 + 3 + 3 + 2 + 1)  # img, gt read; 3 maps written; 3 maps read; img, gt read; gradient written
+    return dict(ms=round(ms, 4), gbs=round(nbytes / ms / 1e6, 1), frac_of_hbm=round(nbytes / ms / 1e6 / hbm_gbs, 3),
+                note="gsr_photometric_loss: (1 - 0.2) L1 + 0.2 (1 - SSIM) with the reference's masks, value + dL/dimage; "
+                     "part of the e2e leg, not of `value`")
 
 
 def cpu_baseline(args, threads=None):
@@ -553,6 +582,10 @@ def main():
             out["optimizer_n1"] = optimizer_leg(args, r["touched_rows"], pk["hbm_gbs"])
         except Exception as ex:  # the leg is informative only; the headline line must still be printed
             out["optimizer_n1"] = dict(error=repr(ex)[:200])
+        try:
+            out["loss_n2"] = loss_leg(args, pk["hbm_gbs"])
+        except Exception as ex:
+            out["loss_n2"] = dict(error=repr(ex)[:200])
     if world == 1 and not args.no_cpu_baseline:
         cb = cpu_baseline(args)
         out["cpu_baseline"] = {k: (round(cb[k], 5) if k == "value" else cb[k]) for k in ("value", "unit", "cores", "kind", "sample")}

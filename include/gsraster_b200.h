@@ -176,6 +176,15 @@ typedef struct gsr_adam_tensors {
    * exp(scaling) (P,3), normalize(rotation) (P,4); xyz and objects are passed to the rasterizer as they are */
   float *a_shs, *a_opacities, *a_scales, *a_rotations;
 } gsr_adam_tensors;
+/* ---- photometric loss of the mapping step, value + gradient fused ----------------------------------
+ * loss_rgb = (1 - lambda) * l1_loss(img, gt) + lambda * (1 - ssim(img, gt)) exactly as the reference composes it
+ * (utils/loss_utils.py:17-20, 36-69 with its `gt != 0` masks; scripts/gaussian_splatting.py:805-807).
+ * img, gt: (3, H, W) fp32 device; dL_dimg (3, H, W) = d loss_rgb / d img (may be NULL: value only);
+ * out3 (device float[3]) = {loss_rgb, Ll1, L_ssim} (lambda_dssim == 0: one elementwise pass, L_ssim reported as 0); scratch: gsr_photometric_loss_scratch_bytes(H, W) bytes. */
+size_t gsr_photometric_loss_scratch_bytes(int H, int W);
+int gsr_photometric_loss(const float* img, const float* gt, int H, int W, float lambda_dssim, float* dL_dimg, float* out3,
+                         char* scratch, void* stream);
+
 /* a_* of all P Gaussians from the raw parameters (first iteration, after map growth). */
 int gsr_activate(const gsr_adam_tensors* t, int P, int M, void* stream);
 /* One Adam step (step = 1, 2, ...; lr[7] in the group order above) + re-activation of the stepped rows.

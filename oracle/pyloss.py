@@ -1,0 +1,23 @@
+"""TEST INFRASTRUCTURE (oracle): torch restatement of the reference's photometric loss
+(src/gaussian_splatting/gaussian_splatting/utils/loss_utils.py:17-20 l1_loss, :27-69 gaussian / create_window / ssim /
+_ssim; composed as at scripts/gaussian_splatting.py:805-807). Pinned against golden vectors produced by importing the
+reference module itself (tests/golden/make_golden_loss.py). Only tests/ may import this; the product path is
+csrc/loss.cu."""
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+
+def photometric_loss(img, gt, lam):
+    """-> (loss_rgb, Ll1, L_ssim) as 0-d tensors; differentiable w.r.t. img."""
+    l1 = torch.where(gt != 0, (img - gt).abs(), torch.zeros_like(img)).mean()            # loss_utils.py:17-20
+    x = torch.where(gt != 0, img, torch.zeros_like(img))                                  # :37
+    g = torch.tensor([np.exp(-(i - 5) ** 2 / (2 * 1.5 ** 2)) for i in range(11)], dtype=torch.float32, device=img.device)
+    g = g / g.sum()                                                                       # :27-29
+    w = (g[:, None] @ g[None, :]).expand(3, 1, 11, 11).contiguous()                       # :31-35
+    conv = lambda t: F.conv2d(t[None], w, padding=5, groups=3)[0]
+    mu1, mu2 = conv(x), conv(gt)                                                          # :49-50
+    s1, s2, s12 = conv(x * x) - mu1 * mu1, conv(gt * gt) - mu2 * mu2, conv(x * gt) - mu1 * mu2   # :56-58
+    C1, C2 = 0.01 ** 2, 0.03 ** 2
+    ssim = (((2 * mu1 * mu2 + C1) * (2 * s12 + C2)) / ((mu1 * mu1 + mu2 * mu2 + C1) * (s1 + s2 + C2))).mean()  # :63-66
+    return (1 - lam) * l1 + lam * (1 - ssim), l1, ssim

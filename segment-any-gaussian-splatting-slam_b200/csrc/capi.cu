@@ -13,6 +13,9 @@
 #include "common.cuh"
 
 namespace gsr {
+size_t photometric_scratch_bytes(int H, int W);
+void launch_photometric_loss(const float* img, const float* gt, int H, int W, float lambda, float* dL_dimg, float* out3,
+                             char* scratch, cudaStream_t s);
 void launch_adam(const gsr_adam_tensors& t, int P, int M, int F, const float* lr, float beta1, float beta2, float eps,
                  int step, const int* idx, const int* count, int cap, cudaStream_t s);
 void launch_activate(const gsr_adam_tensors& t, int P, int M, cudaStream_t s);
@@ -368,6 +371,17 @@ int gsr_exchange_rows(int scatter, int ntensors, const float* const* dense, floa
   }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "exchange_rows: %s", cudaGetErrorString(e));
+  return GSR_OK;
+}
+
+size_t gsr_photometric_loss_scratch_bytes(int H, int W) { return gsr::photometric_scratch_bytes(H > 0 ? H : 1, W > 0 ? W : 1); }
+
+int gsr_photometric_loss(const float* img, const float* gt, int H, int W, float lambda_dssim, float* dL_dimg, float* out3,
+                         char* scratch, void* stream_) {
+  if (!img || !gt || !out3 || !scratch || H <= 0 || W <= 0) return fail(GSR_ERR_INVALID_ARGUMENT, "photometric_loss: bad argument");
+  gsr::launch_photometric_loss(img, gt, H, W, lambda_dssim, dL_dimg, out3, scratch, (cudaStream_t)stream_);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "photometric_loss: %s", cudaGetErrorString(e));
   return GSR_OK;
 }
 

@@ -12,7 +12,7 @@ from helpers import scenes
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 CASES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "*.npz"))
-               if not os.path.basename(p).startswith("knn"))
+               if not os.path.basename(p).startswith(("knn", "loss_")))
 
 
 def test_golden_fixtures_present():
@@ -118,3 +118,19 @@ def test_oracle_quirks():
     assert np.allclose(st["out_color"][:, empty], sc.bg[:, None])
     assert (st["out_objects"][:, empty] == 0).all()
     assert (po.mark_visible(sc.means3D, cam.viewmatrix) == (z > 0.2)).all()
+
+
+def test_loss_oracle_matches_golden_vectors_from_the_reference_loss_code():
+    """oracle/pyloss.py against tests/golden/loss_*.npz (generated by importing the reference's utils/loss_utils.py)."""
+    import glob
+    import torch
+    from oracle import pyloss
+    files = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "loss_*.npz")))
+    assert len(files) >= 3
+    for f in files:
+        z = np.load(f)
+        img = torch.from_numpy(z["img"]).requires_grad_(True)
+        loss, l1, ss = pyloss.photometric_loss(img, torch.from_numpy(z["gt"]), float(z["lam"]))
+        loss.backward()
+        assert abs(float(loss) - z["loss"]) <= 1e-6 and abs(float(l1) - z["Ll1"]) <= 1e-6 and abs(float(ss) - z["Lssim"]) <= 1e-6
+        assert np.abs(img.grad.numpy() - z["grad"]).max() <= 1e-6 * np.abs(z["grad"]).max() + 1e-9
