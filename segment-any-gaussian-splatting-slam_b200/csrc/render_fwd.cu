@@ -153,6 +153,27 @@ render_fwd_kernel(const uint2* __restrict__ ranges, uint32_t* __restrict__ point
           const float ddx = fmaxf(fmaxf(bxlo - xy.x, xy.x - bxhi), 0.f);
           const float ddy = fmaxf(fmaxf(bylo - xy.y, xy.y - byhi), 0.f);
           c = ddx <= hh.x && ddy <= hh.y;
+          if (c && (ddx > 0.f || ddy > 0.f)) {
+            // The box is loose for elongated, tilted splats. Tighter: alpha >= 1/255 needs Q(d) = a dx^2 + 2 b dx dy +
+            // c dy^2 <= tau = 2 ln(255 o); the minimum of the convex Q over the block's (continuous) rectangle is on
+            // one of its four edges when the centre is outside, and it bounds Q at every pixel from below. Margins as
+            // in preprocess.cu; a NaN anywhere keeps the instance (the comparison is written to fail open).
+            const float4 r0 = sm.rec[st][j][0];
+            const float2 co = *reinterpret_cast<const float2*>(&sm.rec[st][j][1].x);  // conic c, opacity
+            const float qa = r0.z, qb = r0.w, qc = co.x;
+            const float X0 = xy.x - bxhi, X1 = xy.x - bxlo, Y0 = xy.y - byhi, Y1 = xy.y - bylo;  // d = centre - pixel
+            auto edge_x = [&](float X) {  // dx = X fixed, dy in [Y0, Y1]
+              const float dy = fminf(fmaxf(-qb * X / qc, Y0), Y1);
+              return qa * X * X + 2.f * qb * X * dy + qc * dy * dy;
+            };
+            auto edge_y = [&](float Y) {
+              const float dx = fminf(fmaxf(-qb * Y / qa, X0), X1);
+              return qa * dx * dx + 2.f * qb * dx * Y + qc * Y * Y;
+            };
+            const float qmin = fminf(fminf(edge_x(X0), edge_x(X1)), fminf(edge_y(Y0), edge_y(Y1)));
+            const float tau = 2.0f * __logf(255.0f * co.y);
+            c = !(qmin > tau * 1.001f + 0.05f);
+          }
         }
         candw[k] = __ballot_sync(0xffffffffu, c);
       }
