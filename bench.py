@@ -428,6 +428,52 @@ def loss_leg(args, hbm_gbs):
                      "part of the e2e leg, not of `value`")
 
 
+def feature_loss_leg(args, hbm_gbs):
+    """SURVEY 8f N2 (next row): fused classifier + cross-entropy + argmax on the headline feature image, with the torch
+    module composition the reference runs (Conv2d 1x1 + CrossEntropyLoss + autograd) timed beside it."""
+    import torch
+    from gsraster_b200 import losses
+    H, W, F, C = args.height, args.width, args.F, 100
+    dev = torch.device("cuda", torch.cuda.current_device())
+    torch.manual_seed(7)
+    classifier = torch.nn.Conv2d(F, C, kernel_size=1).to(dev)
+    objects = torch.randn(F, H, W, device=dev)
+    gt = torch.randint(0, C, (H, W), device=dev)
+    fl = losses.FeatureLoss(classifier, device=dev)
+    out2, grad = torch.empty(2, device=dev), torch.empty_like(objects)
+
+    def timed(fn, n):
+        for _ in range(3):
+            fn()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / n
+
+    ms = timed(lambda: fl(objects, gt, need_pred=True, out=out2, grad_out=grad), 20)
+    crit = torch.nn.CrossEntropyLoss(reduction='none')
+    xo = objects.clone().requires_grad_(True)
+
+    def torch_modules():
+        xo.grad = None
+        logits = classifier(xo)
+        torch.argmax(logits, dim=0)
+        (crit(logits.unsqueeze(0), gt.unsqueeze(0)).squeeze().mean() / 4.605170186).backward()
+
+    tms = timed(torch_modules, 5)
+    flops = 2.0 * 3 * 2 * F * 104 * H * W  # two products, 3xTF32, classes padded to 104
+    nbytes = H * W * (4 * F + 8 + 4 * F + 4)
+    return dict(ms=round(ms, 4), torch_modules_ms=round(tms, 4), tensor_tflops=round(flops / ms / 1e9, 1),
+                gbs=round(nbytes / ms / 1e6, 1), frac_of_hbm=round(nbytes / ms / 1e6 / hbm_gbs, 3),
+                note="gsr_feature_loss: Conv2d(F,100,1) + cross-entropy / ln C + argmax, value + dL/dobjects, logits kept in "
+                     "registers (mma.sync 3xTF32); torch_modules_ms = the same through torch.nn + autograd on this GPU; "
+                     "not part of `value`")
+
+
 def cpu_baseline(args, threads=None):
     """CPU oracle port (oracle/oracle.cpp, OpenMP) timed on the host cores on a bounded sample."""
     import numpy as np
@@ -586,6 +632,10 @@ def main():
             out["loss_n2"] = loss_leg(args, pk["hbm_gbs"])
         except Exception as ex:
             out["loss_n2"] = dict(error=repr(ex)[:200])
+        try:
+            out["feature_loss_n2"] = feature_loss_leg(args, pk["hbm_gbs"])
+        except Exception as ex:
+            out["feature_loss_n2"] = dict(error=repr(ex)[:200])
     if world == 1 and not args.no_cpu_baseline:
         cb = cpu_baseline(args)
         out["cpu_baseline"] = {k: (round(cb[k], 5) if k == "value" else cb[k]) for k in ("value", "unit", "cores", "kind", "sample")}

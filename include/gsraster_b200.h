@@ -185,6 +185,20 @@ size_t gsr_photometric_loss_scratch_bytes(int H, int W);
 int gsr_photometric_loss(const float* img, const float* gt, int H, int W, float lambda_dssim, float* dL_dimg, float* out3,
                          char* scratch, void* stream);
 
+/* ---- segmentation-feature loss of the mapping step, value + gradient + argmax fused ----------------
+ * logits = classifier(objects) (torch.nn.Conv2d(F, C, kernel_size=1): weight (C, F), bias (C)),
+ * loss_obj = CrossEntropyLoss(reduction='none')(logits, gt).mean() / ln C, pred = argmax_c logits
+ * (scripts/gaussian_splatting.py:215-216, 798-803). objects (F, H, W) fp32 device (the rasterizer's out_objects);
+ * gt (H*W) int64 labels, a label outside [0, C) contributes neither loss nor gradient (torch's ignore_index = -100)
+ * while the mean still runs over all H*W pixels; dL_dobjects (F, H, W) = grad_weight * d loss_obj / d objects (may be
+ * NULL: value only); pred (H*W) int32 (may be NULL); out2 (device float[2]) = {loss_obj, mean cross-entropy};
+ * scratch: gsr_feature_loss_scratch_bytes() bytes. F in {16, 32}, 2 <= C <= 256. The logits never reach HBM.
+ * The classifier's own gradient is not produced (the reference never steps cls_optimizer, :217). */
+size_t gsr_feature_loss_scratch_bytes(void);
+int gsr_feature_loss(const float* objects, const long long* gt, int H, int W, int F, int C, const float* weight,
+                     const float* bias, float grad_weight, float* dL_dobjects, int* pred, float* out2, char* scratch,
+                     void* stream);
+
 /* a_* of all P Gaussians from the raw parameters (first iteration, after map growth). */
 int gsr_activate(const gsr_adam_tensors* t, int P, int M, void* stream);
 /* One Adam step (step = 1, 2, ...; lr[7] in the group order above) + re-activation of the stepped rows.

@@ -21,3 +21,28 @@ def photometric_loss(img, gt, lam):
     C1, C2 = 0.01 ** 2, 0.03 ** 2
     ssim = (((2 * mu1 * mu2 + C1) * (2 * s12 + C2)) / ((mu1 * mu1 + mu2 * mu2 + C1) * (s1 + s2 + C2))).mean()  # :63-66
     return (1 - lam) * l1 + lam * (1 - ssim), l1, ssim
+
+
+def feature_loss(objects, gt, weight, bias):
+    """TEST INFRASTRUCTURE. The segmentation-feature loss of the mapping step, restated without torch.nn:
+    logits = Conv2d(F, C, 1)(objects) = weight (C,F) @ objects (F,HW) + bias; CrossEntropyLoss(reduction='none') =
+    logsumexp_c(logits) - logits[gt] (0 where gt == ignore_index -100), mean over ALL pixels, / ln C
+    (scripts/gaussian_splatting.py:215-216, 798-803). numpy float64.
+    -> (loss_obj, mean_ce, d loss_obj / d objects (F,H,W), argmax (H,W))."""
+    Fd, H, W = objects.shape
+    Cn = weight.shape[0]
+    x = objects.reshape(Fd, -1).astype(np.float64)
+    z = weight.reshape(Cn, Fd).astype(np.float64) @ x + bias.astype(np.float64)[:, None]
+    m = z.max(0)
+    e = np.exp(z - m)
+    s = e.sum(0)
+    g = gt.reshape(-1).astype(np.int64)
+    use = (g >= 0) & (g < Cn)
+    gi = np.where(use, g, 0)
+    ce = np.where(use, np.log(s) + m - z[gi, np.arange(z.shape[1])], 0.0)
+    mean_ce = ce.mean()
+    d = e / s
+    d[gi, np.arange(z.shape[1])] -= 1.0
+    d *= use[None, :] / (z.shape[1] * np.log(Cn))
+    dobj = weight.reshape(Cn, Fd).astype(np.float64).T @ d
+    return mean_ce / np.log(Cn), mean_ce, dobj.reshape(Fd, H, W), z.argmax(0).reshape(H, W)

@@ -14,6 +14,9 @@
 
 namespace gsr {
 size_t photometric_scratch_bytes(int H, int W);
+size_t feature_loss_scratch_bytes();
+bool launch_feature_loss(const float* obj, const long long* gt, int HW, int F, int C, const float* weight, const float* bias,
+                         float grad_weight, float* dobj, int* pred, float* out2, char* scratch, cudaStream_t s);
 void launch_photometric_loss(const float* img, const float* gt, int H, int W, float lambda, float* dL_dimg, float* out3,
                              char* scratch, cudaStream_t s);
 void launch_adam(const gsr_adam_tensors& t, int P, int M, int F, const float* lr, float beta1, float beta2, float eps,
@@ -382,6 +385,21 @@ int gsr_photometric_loss(const float* img, const float* gt, int H, int W, float 
   gsr::launch_photometric_loss(img, gt, H, W, lambda_dssim, dL_dimg, out3, scratch, (cudaStream_t)stream_);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "photometric_loss: %s", cudaGetErrorString(e));
+  return GSR_OK;
+}
+
+size_t gsr_feature_loss_scratch_bytes(void) { return gsr::feature_loss_scratch_bytes(); }
+
+int gsr_feature_loss(const float* objects, const long long* gt, int H, int W, int F, int C, const float* weight,
+                     const float* bias, float grad_weight, float* dL_dobjects, int* pred, float* out2, char* scratch,
+                     void* stream_) {
+  if (!objects || !gt || !weight || !bias || !out2 || !scratch || H <= 0 || W <= 0)
+    return fail(GSR_ERR_INVALID_ARGUMENT, "feature_loss: bad argument");
+  if (!gsr::launch_feature_loss(objects, gt, H * W, F, C, weight, bias, grad_weight, dL_dobjects, pred, out2, scratch,
+                                (cudaStream_t)stream_))
+    return fail(GSR_ERR_INVALID_ARGUMENT, "feature_loss: F must be 16 or 32 and 2 <= C <= 256 (got F=%d C=%d)", F, C);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "feature_loss: %s", cudaGetErrorString(e));
   return GSR_OK;
 }
 

@@ -44,3 +44,50 @@ class PhotometricLoss:
                                                      None if grad is None else grad.data_ptr(), out3.data_ptr(),
                                                      self.scratch.data_ptr(), capi._stream_ptr()))
         return out3, grad
+
+
+def _bind_feat():
+    L = capi.lib()
+    if not getattr(L, "_featloss_bound", False):
+        L.gsr_feature_loss_scratch_bytes.restype = C.c_size_t
+        L.gsr_feature_loss_scratch_bytes.argtypes = []
+        L.gsr_feature_loss.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                       C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L._featloss_bound = True
+    return L
+
+
+class FeatureLoss:
+    """Segmentation-feature loss of the mapping step (csrc/featloss.cu): the reference's
+    `logits = classifier(objects); loss_obj = cls_criterion(logits[None], gt[None]).squeeze().mean() / log(num_classes)`
+    and `pred_obj = argmax(logits, 0)` (scripts/gaussian_splatting.py:215-216, 798-803) in one kernel that never writes
+    the logits. `classifier` is a torch.nn.Conv2d(F, C, kernel_size=1) (or any object with .weight (C,F,1,1) / .bias).
+
+    __call__(objects (F,H,W), gt (H,W) int64) -> (out2, dL_dobjects, pred); out2 = device tensor [loss_obj, mean CE]."""
+
+    def __init__(self, classifier, device="cuda"):
+        self.classifier = classifier
+        n = _bind_feat().gsr_feature_loss_scratch_bytes()
+        self.scratch = torch.empty(int(n) + 256, dtype=torch.uint8, device=device)
+
+    def __call__(self, objects, gt, grad_weight=1.0, need_grad=True, need_pred=False, out=None, grad_out=None):
+        w, b = self.classifier.weight.detach(), self.classifier.bias.detach()
+        Cn, F = int(w.shape[0]), int(w.shape[1])
+        w = w.reshape(Cn, F)
+        if not objects.is_cuda or objects.dtype != torch.float32 or not objects.is_contiguous() or objects.dim() != 3 \
+                or objects.shape[0] != F:
+            raise RuntimeError("gsraster_b200.losses: objects must be a contiguous CUDA float32 (F, H, W) tensor (no CPU fallback)")
+        H, W = int(objects.shape[1]), int(objects.shape[2])
+        if not gt.is_cuda or gt.dtype != torch.int64 or not gt.is_contiguous() or gt.numel() != H * W:
+            raise RuntimeError("gsraster_b200.losses: gt must be a contiguous CUDA int64 (H, W) tensor")
+        if not (w.is_cuda and w.is_contiguous() and w.dtype == torch.float32 and b.is_cuda and b.dtype == torch.float32):
+            raise RuntimeError("gsraster_b200.losses: classifier weight / bias must be CUDA float32")
+        out2 = out if out is not None else torch.empty(2, dtype=torch.float32, device=objects.device)
+        grad = (grad_out if grad_out is not None else torch.empty_like(objects)) if need_grad else None
+        pred = torch.empty((H, W), dtype=torch.int32, device=objects.device) if need_pred else None
+        with torch.cuda.device(objects.device):
+            capi._check(_bind_feat().gsr_feature_loss(
+                objects.data_ptr(), gt.data_ptr(), H, W, F, Cn, w.data_ptr(), b.data_ptr(), float(grad_weight),
+                None if grad is None else grad.data_ptr(), None if pred is None else pred.data_ptr(), out2.data_ptr(),
+                self.scratch.data_ptr(), capi._stream_ptr()))
+        return out2, grad, pred

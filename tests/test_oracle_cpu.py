@@ -12,7 +12,7 @@ from helpers import scenes
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 CASES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "*.npz"))
-               if not os.path.basename(p).startswith(("knn", "loss_")))
+               if not os.path.basename(p).startswith(("knn", "loss_", "featloss_")))
 
 
 def test_golden_fixtures_present():
@@ -134,3 +134,17 @@ def test_loss_oracle_matches_golden_vectors_from_the_reference_loss_code():
         loss.backward()
         assert abs(float(loss) - z["loss"]) <= 1e-6 and abs(float(l1) - z["Ll1"]) <= 1e-6 and abs(float(ss) - z["Lssim"]) <= 1e-6
         assert np.abs(img.grad.numpy() - z["grad"]).max() <= 1e-6 * np.abs(z["grad"]).max() + 1e-9
+
+
+def test_feature_loss_oracle_matches_golden_vectors_from_the_reference_call_sequence():
+    """oracle/pyloss.feature_loss against tests/golden/featloss_*.npz (torch Conv2d + CrossEntropyLoss, the modules
+    and call sequence of scripts/gaussian_splatting.py:215-216, 798-803)."""
+    from oracle import pyloss
+    files = sorted(glob.glob(os.path.join(GOLDEN, "featloss_*.npz")))
+    assert len(files) >= 3
+    for f in files:
+        z = np.load(f)
+        loss, ce, dobj, pred = pyloss.feature_loss(z["objects"], z["gt"], z["weight"], z["bias"])
+        assert abs(loss - z["loss"]) <= 2e-6 and abs(ce - z["mean_ce"]) <= 1e-5
+        assert np.abs(dobj - z["grad"]).max() <= 1e-5 * np.abs(z["grad"]).max()
+        assert (pred == z["pred"]).mean() >= 0.999  # fp32 vs fp64 ties
