@@ -45,6 +45,11 @@ def parse_args():
     ap.add_argument("--deg", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--nccl-exchange", action="store_true",
+                    help="N > 1, sparse exchange: NCCL all-gather + all-reduce instead of the peer-memory kernels")
+    ap.add_argument("--no-exchange-overlap", action="store_true",
+                    help="N > 1, sparse exchange: run the flag all-gather + compaction after the per-Gaussian backward "
+                         "instead of beside it")
     ap.add_argument("--dense-allreduce", action="store_true",
                     help="N > 1: sum the full 4(11+3M+F) B/Gaussian bucket instead of the sparse (touched-rows) exchange")
     ap.add_argument("--distinct-views", action="store_true", help="rank r renders keyframe pose r (unequal work)")
@@ -157,12 +162,13 @@ def run_mine(args, rank, world, local_rank):
     P, W, H, F, deg = args.P, args.width, args.height, args.F, args.deg
     M = (deg + 1) ** 2
     e = torch.empty(0, device=dev)
-    bucket = mapping.GradBucket(P, M, F, dev)
-    launches = [0]
     sparse = world > 1 and not args.dense_allreduce
-    ex = mapping.SparseGradExchange(bucket) if sparse else None
+    peer = sparse and not args.nccl_exchange
+    bucket = mapping.GradBucket(P, M, F, dev, symmetric=peer)
+    launches = [0]
+    ex = mapping.SparseGradExchange(bucket, peer_memory=peer) if sparse else None
     if sparse:
-        capi.set_touched_mask(ex.touched)
+        ex.arm(overlap=not args.no_exchange_overlap)   # touched flags + blend-done event registered with the library
 
     def fwd(dd):
         return capi.rasterize_gaussians(dd["bg"], dd["means3D"], e, dd["opacities"], dd["scales"], dd["rotations"],
@@ -187,7 +193,10 @@ def run_mine(args, rank, world, local_rank):
             if ar_events is not None:
                 a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 a.record()
-            if sparse:
+            if peer:
+                ex.exchange()      # barrier, union of the peers' flags, rank-ordered row sums out of the peers' buckets,
+                                   # barrier: all queued, nothing to read back (capacity = P; consumers take device count)
+            elif sparse:
                 ex.exchange()      # flags all-gather, union scan, row gather, SUM-reduce of the touched rows: all queued
                 ex.finish()        # count read-back (dense fallback if the capacity guess was too small)
             else:
@@ -261,6 +270,8 @@ def run_mine(args, rank, world, local_rank):
     capi.set_stage_timing(False)
     allreduce_ms = sum(a.elapsed_time(b) for a, b in ar_events) / len(ar_events) if ar_events else 1e-9
     ar_events = None
+    if peer and ex._pending is not None:
+        ex.finish()   # outside every timed region: the union size of the last step, for the report
 
     # ---- timed region 2: end to end with host buffers ----
     e2e = None
@@ -337,7 +348,8 @@ def run_e2e(args, cam, d, g, fwd, bwd, bucket, world, dev, sync_all, ex=None):
         if world > 1:
             if ex is not None:
                 ex.exchange()
-                ex.finish()
+                if not ex.peer:
+                    ex.finish()
             else:
                 dist.all_reduce(bucket.flat)
         h_loss[k].copy_(loss.reshape(1), non_blocking=True)  # 4-byte D2H of the step's result
@@ -604,7 +616,10 @@ def main():
                                "same pose, per-rank upstream gradients: equal work per rank",
                                "1 NCCL all-reduce of the dense %d MB bucket/step" % (r["bucket_bytes"] // 1000000)
                                if args.dense_allreduce else
-                               "sparse gradient exchange: NCCL all-gather of the touched flags + SUM-reduce of the "
+                               ("sparse gradient exchange: NCCL all-gather of the touched flags + SUM-reduce of the " if args.nccl_exchange else
+                                "sparse gradient exchange over peer memory (no collective library call: barrier, union of the "
+                                "peers' touched flags read in place, rank-ordered sum of the union's rows out of the peers' "
+                                "buckets over NVLink): ") +
                                "%d touched rows (of %d) = %d MB/step" % (
                                    r["exchange_rows"], args.P,
                                    r["exchange_rows"] * (r["bucket_bytes"] // args.P) // 1000000)) if world > 1 else "single GPU",

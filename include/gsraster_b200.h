@@ -146,6 +146,11 @@ int gsr_get_stage_gaps(float* ms);
  * bytes, zeroed by the caller) for every Gaussian i that received a contribution from the backward blend. All other
  * Gaussians have exactly-zero parameter gradients, so an exchange over ranks can skip them. NULL disables. */
 int gsr_set_touched_mask(uint8_t* mask);
+/* While an event (a cudaEvent_t) is set, every gsr_backward / gsr_backward_pose call of this thread records it on its
+ * stream right after the backward blend, i.e. once the touched flags and the gradient rows of the blend are final and
+ * before the per-Gaussian backward runs: a second stream can wait on it and start the flag exchange (all-gather + union
+ * compaction) while the per-Gaussian backward is still running. NULL disables. */
+int gsr_set_blend_done_event(void* event);
 /* Union + compaction of the all-gathered flags: flags = nranks rows of Ppad bytes (Ppad >= P, multiple of 4, 4-byte
  * aligned). Writes the ascending indices of the Gaussians flagged by any rank to idx[0 : min(count, cap)] and the union
  * size to *count (device memory, stays on the device). Every rank computes the same list from the same gathered flags.
@@ -158,6 +163,21 @@ int gsr_exchange_compact(const uint8_t* flags, int nranks, int P, int Ppad, int 
  * Gaussian; the pointer arrays are HOST arrays of device pointers. */
 int gsr_exchange_rows(int scatter, int ntensors, const float* const* dense, float* const* compact,
                       const int* floats_per_row, const int* idx, const int* count, int cap, void* stream);
+/* Peer-memory version of the exchange (one process per GPU, buffers mapped into every rank, e.g. CUDA VMM / symmetric
+ * memory over NVLink): no collective library call on the data path.
+ * gsr_exchange_compact_peers: as gsr_exchange_compact, but flags[r] (HOST array of nranks <= 16 device pointers, 4-byte
+ * aligned, P bytes readable rounded up to 4) is rank r's own flag buffer read in place.
+ * gsr_exchange_sum_rows_peers: compact[t][r][:] = sum over ranks q (ascending, so every rank gets bitwise the same sum)
+ * of buckets[q][tensor_offset[t] + idx[r] * floats_per_row[t] + :] for r < min(*count, cap) (rows beyond are left
+ * untouched; with cap = P the list can never overflow and no host read-back of *count is needed); buckets =
+ * HOST array of the nranks bucket base pointers as mapped in THIS process. The caller orders the calls between ranks:
+ * a cross-rank barrier after the last backward pass (flags and buckets final) and one after this call (before any rank
+ * overwrites its bucket or flags). */
+int gsr_exchange_compact_peers(const uint8_t* const* flags, int nranks, int P, int cap, int* idx, int* count, char* scratch,
+                               void* stream);
+int gsr_exchange_sum_rows_peers(const float* const* buckets, int nranks, int ntensors, const long long* tensor_offset,
+                                float* const* compact, const int* floats_per_row, const int* idx, const int* count, int cap,
+                                void* stream);
 
 /* ---- activation + Adam fused around the rasterizer ---------------------------------------------------
  * Replaces, for the seven parameter groups of the reference's GaussianModel (scene/gaussian_model.py:247-257:

@@ -25,6 +25,10 @@ void launch_activate(const gsr_adam_tensors& t, int P, int M, cudaStream_t s);
 size_t exchange_scratch_bytes(int P);
 void launch_union_compact(const uint8_t* flags, int nranks, int P, int Ppad, int cap, int* idx, int* count, char* scratch,
                           cudaStream_t s);
+void launch_union_compact_peers(const uint8_t* const* flags, int nranks, int P, int cap, int* idx, int* count, char* scratch,
+                                cudaStream_t s);
+void launch_sum_rows_peers(const float* const* buckets, int nranks, int ntensors, const long long* off, float* const* dst,
+                           const int* n, const int* idx, const int* count, int cap, cudaStream_t s);
 void launch_rows(bool scatter, int ntensors, const float* const* src, float* const* dst, const int* n, const int* idx,
                  const int* count, int cap, cudaStream_t s);
 void launch_export_keys(int T, const uint2* ranges, const uint32_t* point_list, const float4* rec, uint64_t* keys,
@@ -45,6 +49,7 @@ thread_local int* g_pinned = nullptr;  // 8 ints of pinned host memory for the n
 struct StageSpan { int stage; cudaEvent_t a, b; };
 thread_local bool g_timing = false;
 thread_local uint8_t* g_touched = nullptr;  // gsr_set_touched_mask
+thread_local cudaEvent_t g_blend_done = nullptr;  // gsr_set_blend_done_event
 thread_local std::vector<StageSpan> g_spans;
 thread_local std::vector<cudaEvent_t> g_free_events;
 thread_local float g_gaps[GSR_NUM_STAGES] = {0, 0, 0, 0, 0, 0};  // idle time on the stream before each stage
@@ -270,6 +275,7 @@ static int backward_impl(const gsr_params* p, int num_rendered, const float* bac
       g_launches += 1;
     }
   }
+  if (g_blend_done) CUDA_TRY(cudaEventRecord(g_blend_done, stream));  // the touched flags are final from here on
   STAGE_CHECK("render_backward");
   const gsr::FwdInputs in = make_inputs(p, means3D, shs, colors_precomp, nullptr, scales, rotations, cov3D_precomp);
   gsr::BwdOutputs out{dL_dmean2D, dL_dconic, dL_dopacity, dL_ddepths, dL_dcolor, dL_dobjects,
@@ -348,11 +354,16 @@ int gsr_set_touched_mask(uint8_t* mask) {
   return GSR_OK;
 }
 
+int gsr_set_blend_done_event(void* event) {
+  g_blend_done = (cudaEvent_t)event;
+  return GSR_OK;
+}
+
 size_t gsr_exchange_scratch_bytes(int P) { return gsr::exchange_scratch_bytes(P > 0 ? P : 1); }
 
 int gsr_exchange_compact(const uint8_t* flags, int nranks, int P, int Ppad, int cap, int* idx, int* count, char* scratch,
                          void* stream_) {
-  if (!flags || !idx || !count || !scratch || nranks <= 0 || P <= 0 || Ppad < P || (Ppad & 3) || cap < 0 ||
+  if (!flags || !idx || !count || !scratch || nranks <= 0 || nranks > 16 || P <= 0 || Ppad < P || (Ppad & 3) || cap < 0 ||
       ((uintptr_t)flags & 3))
     return fail(GSR_ERR_INVALID_ARGUMENT, "exchange_compact: bad argument");
   gsr::launch_union_compact(flags, nranks, P, Ppad, cap, idx, count, scratch, (cudaStream_t)stream_);
@@ -374,6 +385,31 @@ int gsr_exchange_rows(int scatter, int ntensors, const float* const* dense, floa
   }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "exchange_rows: %s", cudaGetErrorString(e));
+  return GSR_OK;
+}
+
+int gsr_exchange_compact_peers(const uint8_t* const* flags, int nranks, int P, int cap, int* idx, int* count, char* scratch,
+                               void* stream_) {
+  if (!flags || !idx || !count || !scratch || nranks <= 0 || nranks > 16 || P <= 0 || cap < 0)
+    return fail(GSR_ERR_INVALID_ARGUMENT, "exchange_compact_peers: bad argument");
+  for (int r = 0; r < nranks; r++)
+    if (!flags[r] || ((uintptr_t)flags[r] & 3)) return fail(GSR_ERR_INVALID_ARGUMENT, "exchange_compact_peers: bad flag pointer");
+  gsr::launch_union_compact_peers(flags, nranks, P, cap, idx, count, scratch, (cudaStream_t)stream_);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "exchange_compact_peers: %s", cudaGetErrorString(e));
+  return GSR_OK;
+}
+
+int gsr_exchange_sum_rows_peers(const float* const* buckets, int nranks, int ntensors, const long long* tensor_offset,
+                                float* const* compact, const int* floats_per_row, const int* idx, const int* count, int cap,
+                                void* stream_) {
+  if (!buckets || nranks <= 0 || nranks > 16 || ntensors <= 0 || ntensors > 8 || !tensor_offset || !compact ||
+      !floats_per_row || !idx || !count || cap < 0)
+    return fail(GSR_ERR_INVALID_ARGUMENT, "exchange_sum_rows_peers: bad argument");
+  gsr::launch_sum_rows_peers(buckets, nranks, ntensors, tensor_offset, compact, floats_per_row, idx, count, cap,
+                             (cudaStream_t)stream_);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "exchange_sum_rows_peers: %s", cudaGetErrorString(e));
   return GSR_OK;
 }
 

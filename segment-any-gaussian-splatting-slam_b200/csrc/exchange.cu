@@ -11,21 +11,26 @@ constexpr int XC_THREADS = 256;
 constexpr int XC_PER_T = 4;
 constexpr int XC_TILE = XC_THREADS * XC_PER_T;  // Gaussians per block
 
-__device__ __forceinline__ uint32_t union4(const uint8_t* __restrict__ flags, int nranks, size_t P, size_t g) {
+// flag arrays of the ranks: rows of one all-gathered buffer, or the peers' own buffers mapped over NVLink
+struct XcPeers {
+  const void* p[16];
+  int n;
+};
+__device__ __forceinline__ uint32_t union4(const XcPeers& f, size_t g) {
   // 4 consecutive flag bytes, OR over ranks (P % 4 == 0 is not required: callers bound-check per byte)
   uint32_t u = 0;
-  for (int r = 0; r < nranks; r++) u |= *reinterpret_cast<const uint32_t*>(flags + (size_t)r * P + g);
+  for (int r = 0; r < f.n; r++) u |= *reinterpret_cast<const uint32_t*>(static_cast<const uint8_t*>(f.p[r]) + g);
   return u;
 }
 
 // pass 1: per-block union counts
 __global__ void __launch_bounds__(XC_THREADS)
-xc_count_kernel(const uint8_t* __restrict__ flags, int nranks, int P, int Ppad, uint32_t* __restrict__ block_cnt) {
+xc_count_kernel(XcPeers flags, int P, uint32_t* __restrict__ block_cnt) {
   __shared__ uint32_t wsum[XC_THREADS / 32];
   const int g0 = blockIdx.x * XC_TILE + threadIdx.x * XC_PER_T;
   uint32_t c = 0;
   if (g0 < P) {
-    const uint32_t u = union4(flags, nranks, (size_t)Ppad, (size_t)g0);
+    const uint32_t u = union4(flags, (size_t)g0);
 #pragma unroll
     for (int k = 0; k < 4; k++) c += (g0 + k < P && ((u >> (8 * k)) & 0xffu)) ? 1u : 0u;
   }
@@ -70,13 +75,12 @@ xc_scan_kernel(uint32_t* __restrict__ block_cnt, int nb, int* __restrict__ count
 }
 // pass 3: ranked writes of the union's indices (ascending), entries >= cap are dropped
 __global__ void __launch_bounds__(XC_THREADS)
-xc_write_kernel(const uint8_t* __restrict__ flags, int nranks, int P, int Ppad, const uint32_t* __restrict__ block_off,
-                int cap, int* __restrict__ idx) {
+xc_write_kernel(XcPeers flags, int P, const uint32_t* __restrict__ block_off, int cap, int* __restrict__ idx) {
   __shared__ uint32_t wsum[XC_THREADS / 32];
   const int g0 = blockIdx.x * XC_TILE + threadIdx.x * XC_PER_T;
   uint32_t u = 0, c = 0;
   if (g0 < P) {
-    u = union4(flags, nranks, (size_t)Ppad, (size_t)g0);
+    u = union4(flags, (size_t)g0);
 #pragma unroll
     for (int k = 0; k < 4; k++) c += (g0 + k < P && ((u >> (8 * k)) & 0xffu)) ? 1u : 0u;
   }
@@ -120,6 +124,33 @@ xc_gather_kernel(XcTensors t, const int* __restrict__ idx, const int* __restrict
     for (int i = lane; i < n; i += 32) d[i] = live ? s[i] : 0.f;
   }
 }
+// Peer-memory version of gather + all-reduce: compact[t][r][:] = sum over ranks of bucket_rank[off_t + idx[r] * n_t + :],
+// every rank reading the union's rows straight out of its peers' buckets (NVLink loads) and summing in rank order, so
+// all ranks obtain bitwise the same sums. The caller brackets it with cross-rank barriers.
+struct XcPeerTensors {
+  long long off[8];  // float offset of tensor t inside a bucket
+  float* dst[8];
+  int n[8];
+  int count;
+};
+__global__ void __launch_bounds__(256)
+xc_gather_sum_kernel(XcPeerTensors t, XcPeers buckets, const int* __restrict__ idx, const int* __restrict__ count, int cap) {
+  const int lane = threadIdx.x & 31;
+  const int nrows = min(*count, cap);  // rows beyond are left untouched: consumers read idx / compact only below *count
+  for (int row = blockIdx.x * 8 + (threadIdx.x >> 5); row < nrows; row += gridDim.x * 8) {
+    const size_t g = (size_t)idx[row];
+    for (int k = 0; k < t.count; k++) {
+      const int n = t.n[k];
+      float* d = t.dst[k] + (size_t)row * n;
+      const long long base = t.off[k] + (long long)(g * n);
+      for (int i = lane; i < n; i += 32) {
+        float s = 0.f;
+        for (int r = 0; r < buckets.n; r++) s += static_cast<const float*>(buckets.p[r])[base + i];
+        d[i] = s;
+      }
+    }
+  }
+}
 // dense[t][idx[r]][:] = compact[t][r][:] for r < min(count, cap) (the caller zeroes dense first)
 __global__ void __launch_bounds__(256)
 xc_scatter_kernel(XcTensors t, const int* __restrict__ idx, const int* __restrict__ count, int cap) {
@@ -136,13 +167,39 @@ xc_scatter_kernel(XcTensors t, const int* __restrict__ idx, const int* __restric
 
 size_t exchange_scratch_bytes(int P) { return ((size_t)(P + XC_TILE - 1) / XC_TILE + 8) * sizeof(uint32_t); }
 
-void launch_union_compact(const uint8_t* flags, int nranks, int P, int Ppad, int cap, int* idx, int* count,
-                          char* scratch, cudaStream_t s) {
+static void union_compact(const XcPeers& f, int P, int cap, int* idx, int* count, char* scratch, cudaStream_t s) {
   const int nb = (P + XC_TILE - 1) / XC_TILE;
   uint32_t* block_cnt = reinterpret_cast<uint32_t*>(scratch);
-  xc_count_kernel<<<nb, XC_THREADS, 0, s>>>(flags, nranks, P, Ppad, block_cnt);
+  xc_count_kernel<<<nb, XC_THREADS, 0, s>>>(f, P, block_cnt);
   xc_scan_kernel<<<1, 1024, 0, s>>>(block_cnt, nb, count);
-  xc_write_kernel<<<nb, XC_THREADS, 0, s>>>(flags, nranks, P, Ppad, block_cnt, cap, idx);
+  xc_write_kernel<<<nb, XC_THREADS, 0, s>>>(f, P, block_cnt, cap, idx);
+}
+void launch_union_compact(const uint8_t* flags, int nranks, int P, int Ppad, int cap, int* idx, int* count,
+                          char* scratch, cudaStream_t s) {
+  // more than 16 rows: fold them 16 at a time is not needed in practice (one node = 8 GPUs); callers check nranks <= 16
+  XcPeers f;
+  f.n = nranks;
+  for (int r = 0; r < nranks; r++) f.p[r] = flags + (size_t)r * Ppad;
+  union_compact(f, P, cap, idx, count, scratch, s);
+}
+void launch_union_compact_peers(const uint8_t* const* flags, int nranks, int P, int cap, int* idx, int* count, char* scratch,
+                                cudaStream_t s) {
+  XcPeers f;
+  f.n = nranks;
+  for (int r = 0; r < nranks; r++) f.p[r] = flags[r];
+  union_compact(f, P, cap, idx, count, scratch, s);
+}
+void launch_sum_rows_peers(const float* const* buckets, int nranks, int ntensors, const long long* off, float* const* dst,
+                           const int* n, const int* idx, const int* count, int cap, cudaStream_t s) {
+  if (cap <= 0) return;
+  XcPeers b;
+  b.n = nranks;
+  for (int r = 0; r < nranks; r++) b.p[r] = buckets[r];
+  XcPeerTensors t;
+  t.count = ntensors;
+  for (int k = 0; k < ntensors; k++) { t.off[k] = off[k]; t.dst[k] = dst[k]; t.n[k] = n[k]; }
+  const int nb = (cap + 7) / 8;
+  xc_gather_sum_kernel<<<nb < 148 * 8 ? nb : 148 * 8, 256, 0, s>>>(t, b, idx, count, cap);
 }
 void launch_rows(bool scatter, int ntensors, const float* const* src, float* const* dst, const int* n, const int* idx,
                  const int* count, int cap, cudaStream_t s) {

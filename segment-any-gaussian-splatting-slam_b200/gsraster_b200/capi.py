@@ -296,6 +296,19 @@ def set_touched_mask(mask):
     _check(lib().gsr_set_touched_mask(None if mask is None else mask.data_ptr()))
 
 
+def set_blend_done_event(event):
+    """event: a torch.cuda.Event that has been recorded at least once (so its handle exists) or None; see
+    gsr_set_blend_done_event."""
+    h = None
+    if event is not None:
+        h = event.cuda_event
+        h = getattr(h, "value", h)
+        if not h:
+            raise RuntimeError("blend-done event has no CUDA handle yet: record it once before passing it")
+    lib().gsr_set_blend_done_event.argtypes = [C.c_void_p]
+    _check(lib().gsr_set_blend_done_event(h))
+
+
 def exchange_scratch_bytes(P):
     return int(lib().gsr_exchange_scratch_bytes(int(P)))
 
@@ -316,6 +329,33 @@ def exchange_rows(scatter, dense, compact, floats_per_row, idx, count, cap):
     with torch.cuda.device(idx.device):
         _check(lib().gsr_exchange_rows(int(bool(scatter)), n, dp, cp, fp, idx.data_ptr(), count.data_ptr(), int(cap),
                                        _stream_ptr()))
+
+
+def exchange_compact_peers(flag_ptrs, P, cap, idx, count, scratch):
+    """gsr_exchange_compact_peers: flag_ptrs = the ranks' flag buffers as mapped in this process (ints)."""
+    n = len(flag_ptrs)
+    fp = (C.c_void_p * n)(*[int(p) for p in flag_ptrs])
+    L = lib()
+    L.gsr_exchange_compact_peers.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                             C.c_void_p]
+    with torch.cuda.device(idx.device):
+        _check(L.gsr_exchange_compact_peers(fp, n, int(P), int(cap), idx.data_ptr(), count.data_ptr(), scratch.data_ptr(),
+                                            _stream_ptr()))
+
+
+def exchange_sum_rows_peers(bucket_ptrs, tensor_offsets, compact, floats_per_row, idx, count, cap):
+    """gsr_exchange_sum_rows_peers: compact rows = sum over ranks of the union's rows, read from the peers' buckets."""
+    n, k = len(bucket_ptrs), len(compact)
+    bp = (C.c_void_p * n)(*[int(p) for p in bucket_ptrs])
+    off = (C.c_longlong * k)(*[int(o) for o in tensor_offsets])
+    cp = (C.c_void_p * k)(*[t.data_ptr() for t in compact])
+    fp = (C.c_int * k)(*[int(v) for v in floats_per_row])
+    L = lib()
+    L.gsr_exchange_sum_rows_peers.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                              C.c_void_p, C.c_int, C.c_void_p]
+    with torch.cuda.device(idx.device):
+        _check(L.gsr_exchange_sum_rows_peers(bp, n, k, off, cp, fp, idx.data_ptr(), count.data_ptr(), int(cap),
+                                             _stream_ptr()))
 
 
 def get_stage_gaps():

@@ -510,3 +510,30 @@ def test_exchange_kernels_match_torch_reference():
                 exp = torch.zeros_like(d_)
                 exp[ref_idx[:k]] = d_[ref_idx[:k]]
                 assert (b_ == exp).all()
+
+
+def test_sparse_exchange_with_overlapped_flag_exchange_single_rank_nccl():
+    """The overlapped exchange (blend-done event -> side stream all-gather + compaction beside the per-Gaussian
+    backward) on a 1-rank NCCL group: stream plumbing + result against the dense bucket. The N-rank version is
+    tests/gpu_exchange_check.py (torchrun)."""
+    import socket
+    import torch
+    import torch.distributed as dist
+    import gpu_exchange_check as gx
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    created = not dist.is_initialized()
+    if created:
+        dist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{port}", rank=0, world_size=1,
+                                device_id=torch.device("cuda", 0))
+    try:
+        worst, rows, fb = gx.run_check(P=50000, W=320, H=256, steps=3)
+        assert worst <= 1e-6 and rows > 0 and fb <= 1, (worst, rows, fb)
+    finally:
+        from gsraster_b200 import capi
+        capi.set_touched_mask(None)
+        capi.set_blend_done_event(None)
+        if created:
+            dist.destroy_process_group()
