@@ -70,11 +70,15 @@ class ClockSampler:
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+    def __init__(self, index, enabled=True):
+        self.index, self.rows, self.proc, self.first, self.enabled = index, [], None, 0, enabled
+
+    def mark(self):
+        """Call right before the timed region: only samples taken from here on are reported."""
+        self.first = len(self.rows)
 
     def start(self):
-        if os.environ.get("GSR_BENCH_NO_CLOCKS"):
+        if os.environ.get("GSR_BENCH_NO_CLOCKS") or not self.enabled:
             return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
@@ -82,6 +86,11 @@ class ClockSampler:
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
+            # nvidia-smi needs up to seconds before its first line on a multi-GPU box: wait for it here (untimed), so
+            # that the sampler is running during the timed region
+            t0 = time.time()
+            while not self.rows and time.time() - t0 < 10.0 and self.proc.poll() is None:
+                time.sleep(0.02)
         except OSError:
             self.proc = None
 
@@ -96,7 +105,8 @@ class ClockSampler:
         self.th.join(timeout=2)
         sm, mx, reasons = [], [], set()
         names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
-        for r in self.rows:
+        rows = self.rows[self.first:] or self.rows
+        for r in rows:
             try:
                 sm.append(float(r[0])); mx.append(float(r[1]))
             except (ValueError, IndexError):
@@ -231,8 +241,9 @@ def run_mine(args, rank, world, local_rank):
     capi.set_touched_mask(ex.touched if sparse else None)
     touched_rows = int(tm.sum())
     del tm
-    clocks = ClockSampler(local_rank)
-    clocks.start()  # started a few steps early: nvidia-smi needs tens of ms before its first sample
+    clocks = ClockSampler(local_rank, enabled=(rank == 0))  # rank 0 prints the line; 8 concurrent nvidia-smi slow each other
+    clocks.start()  # waits (untimed) for nvidia-smi's first sample, so the sampler is live during the timed region
+    sync_all()      # the other ranks wait here, not inside a device-side barrier
     for _ in range(3):  # settle the caching allocator again after the statistics pass (untimed, in addition to W)
         step()
     sync_all()
@@ -241,6 +252,7 @@ def run_mine(args, rank, world, local_rank):
     launches[0] = 0
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sync_all()
+    clocks.mark()
     ev0.record()
     for _ in range(args.steps):
         step()
@@ -539,6 +551,7 @@ def run_reference(args):
     clocks = ClockSampler(0)
     clocks.start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    clocks.mark()
     ev0.record()
     for _ in range(args.steps):
         step()
