@@ -98,27 +98,73 @@ adam_step_kernel(const AdamArgs a) {
   }
 }
 
-// Dense mode, part 1: the groups without an activation (xyz, f_dc, f_rest, objects) as ONE flat element range,
-// a thread per element, consecutive threads on consecutive addresses of every stream (p, m, v, gradient, and the
-// concatenated SH output).
+// Dense mode, part 1: the groups without an activation (xyz, f_dc, f_rest, objects) as ONE range of 4-float chunks:
+// a thread per chunk, 128-bit loads / stores on p, m, v (and on the gradient where its layout is the parameter's),
+// 32-bit index arithmetic. The SH gradient / output rows interleave f_dc and f_rest (3M floats per Gaussian), so those
+// two streams are addressed per element (still consecutive across the warp).
+__device__ __forceinline__ void adam_update4(float* p, float* m, float* v, size_t i, const float (&g)[4], float lr,
+                                             const AdamArgs& a, float (&pn)[4]) {
+  float4 m4 = *reinterpret_cast<const float4*>(m + i), v4 = *reinterpret_cast<const float4*>(v + i);
+  const float4 p4 = *reinterpret_cast<const float4*>(p + i);
+  float mi[4] = {m4.x, m4.y, m4.z, m4.w}, vi[4] = {v4.x, v4.y, v4.z, v4.w};
+  const float pi[4] = {p4.x, p4.y, p4.z, p4.w};
+  const float step = lr / a.bc1;
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    mi[k] = mi[k] + (g[k] - mi[k]) * (1.f - a.beta1);
+    vi[k] = a.beta2 * vi[k] + (1.f - a.beta2) * g[k] * g[k];
+    const float denom = sqrtf(vi[k]) / a.bc2_sqrt + a.eps;
+    pn[k] = pi[k] - step * (mi[k] / denom);
+  }
+  *reinterpret_cast<float4*>(m + i) = make_float4(mi[0], mi[1], mi[2], mi[3]);
+  *reinterpret_cast<float4*>(v + i) = make_float4(vi[0], vi[1], vi[2], vi[3]);
+  *reinterpret_cast<float4*>(p + i) = make_float4(pn[0], pn[1], pn[2], pn[3]);
+}
 __global__ void __launch_bounds__(256)
 adam_flat_kernel(const AdamArgs a) {
   const gsr_adam_tensors& t = a.t;
-  const size_t P = (size_t)a.P;
-  const int M = a.M, F = a.F, R = 3 * (M - 1);
-  const size_t e0 = 3 * P, e1 = e0 + 3 * P, e2 = e1 + (size_t)R * P, e3 = e2 + (size_t)F * P;
-  for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < e3; e += (size_t)gridDim.x * blockDim.x) {
-    if (e < e0) {
-      adam_update(t.xyz, t.m_xyz, t.v_xyz, e, t.g_means3D[e], a.lr[0], a);
-    } else if (e < e1) {
-      const size_t i = e - e0, g = i / 3, c = i - 3 * g;
-      t.a_shs[g * 3 * M + c] = adam_update(t.f_dc, t.m_f_dc, t.v_f_dc, i, t.g_sh[g * 3 * M + c], a.lr[1], a);
-    } else if (e < e2) {
-      const size_t i = e - e1, g = i / R, c = i - (size_t)R * g;
-      t.a_shs[g * 3 * M + 3 + c] = adam_update(t.f_rest, t.m_f_rest, t.v_f_rest, i, t.g_sh[g * 3 * M + 3 + c], a.lr[2], a);
+  const uint32_t P = (uint32_t)a.P, M3 = 3u * (uint32_t)a.M, R = M3 - 3u;
+  // chunk ranges (4 floats each; a group's tail of < 4 floats is handled per element by the chunk that holds it)
+  const uint32_t n0 = (3u * P + 3u) / 4u, n1 = n0, n2 = (R * P + 3u) / 4u, n3 = ((uint32_t)a.F * P + 3u) / 4u;
+  const uint32_t c0 = n0, c1 = c0 + n1, c2 = c1 + n2, c3 = c2 + n3;
+  for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < c3; c += gridDim.x * blockDim.x) {
+    float* p; float* m; float* v;
+    uint32_t i, n, grp;
+    float lr;
+    if (c < c0)      { grp = 0; i = 4u * c;        n = 3u * P;             p = t.xyz;     m = t.m_xyz;     v = t.v_xyz;     lr = a.lr[0]; }
+    else if (c < c1) { grp = 1; i = 4u * (c - c0); n = 3u * P;             p = t.f_dc;    m = t.m_f_dc;    v = t.v_f_dc;    lr = a.lr[1]; }
+    else if (c < c2) { grp = 2; i = 4u * (c - c1); n = R * P;              p = t.f_rest;  m = t.m_f_rest;  v = t.v_f_rest;  lr = a.lr[2]; }
+    else             { grp = 3; i = 4u * (c - c2); n = (uint32_t)a.F * P;  p = t.objects; m = t.m_objects; v = t.v_objects; lr = a.lr[6]; }
+    // SH rows: element e of f_dc (grp 1) / f_rest (grp 2) lives at g_sh / a_shs [gauss * 3M + (grp 1: c, grp 2: 3 + c)]
+    uint32_t sh[4] = {0, 0, 0, 0};
+    if (grp == 1 || grp == 2) {
+      const uint32_t w = grp == 1 ? 3u : R, add = grp == 1 ? 0u : 3u;
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        const uint32_t e = min(i + k, n - 1), gi = e / w;
+        sh[k] = gi * M3 + add + (e - gi * w);
+      }
+    }
+    if (i + 4u <= n) {
+      float g[4], pn[4];
+      if (grp == 0 || grp == 3) {
+        const float4 g4 = *reinterpret_cast<const float4*>((grp == 0 ? t.g_means3D : t.g_objects) + i);
+        g[0] = g4.x, g[1] = g4.y, g[2] = g4.z, g[3] = g4.w;
+      } else {
+#pragma unroll
+        for (int k = 0; k < 4; k++) g[k] = t.g_sh[sh[k]];
+      }
+      adam_update4(p, m, v, i, g, lr, a, pn);
+      if (grp == 1 || grp == 2) {
+#pragma unroll
+        for (int k = 0; k < 4; k++) t.a_shs[sh[k]] = pn[k];
+      }
     } else {
-      const size_t i = e - e2;
-      adam_update(t.objects, t.m_objects, t.v_objects, i, t.g_objects[i], a.lr[6], a);
+      for (uint32_t k = 0; i + k < n; k++) {
+        const float g = grp == 0 ? t.g_means3D[i + k] : grp == 3 ? t.g_objects[i + k] : t.g_sh[sh[k]];
+        const float pn = adam_update(p, m, v, i + k, g, lr, a);
+        if (grp == 1 || grp == 2) t.a_shs[sh[k]] = pn;
+      }
     }
   }
 }
@@ -188,8 +234,12 @@ void launch_adam(const gsr_adam_tensors& t, int P, int M, int F, const float* lr
     return;
   }
   if (P <= 0) return;
-  const bool rot16 = (((uintptr_t)t.rotation | (uintptr_t)t.g_rotations | (uintptr_t)t.a_rotations) & 15) == 0;
-  if (!rot16) {  // unaligned rotation tensors: the generic warp-per-row kernel
+  uintptr_t al = (uintptr_t)t.rotation | (uintptr_t)t.g_rotations | (uintptr_t)t.a_rotations;
+  const float* const vec[] = {t.xyz, t.m_xyz, t.v_xyz, t.f_dc, t.m_f_dc, t.v_f_dc, t.f_rest, t.m_f_rest, t.v_f_rest,
+                              t.objects, t.m_objects, t.v_objects, t.g_means3D, t.g_objects};
+  for (const float* q : vec) al |= (uintptr_t)q;
+  const bool rot16 = (al & 15) == 0 && (unsigned long long)P * (unsigned long long)(3 * M + F + 8) < (1ull << 31);
+  if (!rot16) {  // unaligned tensors (or an index range beyond 32 bits): the generic warp-per-row kernel
     adam_step_kernel<<<(P + 7) / 8, 256, 0, s>>>(a);
     return;
   }
