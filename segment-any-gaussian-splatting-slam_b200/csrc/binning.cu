@@ -212,11 +212,25 @@ coverage_kernel(int P, int gx, int gy, SuperGrid sg, int use_smem, const uint32_
 
 // single block: 2-D prefix sums of the coverage grids, then exclusive scans -> offsets
 __global__ void __launch_bounds__(1024)
-offsets_kernel(int gx, int gy, SuperGrid sg, int* __restrict__ sat, int* __restrict__ ssat, uint2* __restrict__ ranges,
-               uint32_t* __restrict__ tile_off, uint32_t* __restrict__ l1_off, int* __restrict__ flags) {
+offsets_kernel(int gx, int gy, SuperGrid sg, int use_smem, int* __restrict__ sat_g, int* __restrict__ ssat_g,
+               uint2* __restrict__ ranges, uint32_t* __restrict__ tile_off, uint32_t* __restrict__ l1_off,
+               int* __restrict__ flags) {
+  extern __shared__ int off_s[];
   __shared__ unsigned long long warp_sums[32];
   __shared__ unsigned long long carry_s;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  // The serial prefix walks below are chains of dependent read-modify-writes: in global memory each link costs a DRAM/L2
+  // round trip (35 us for an 81 x 65 grid, on the critical path of the num_rendered read-back); staged in shared
+  // memory the same walks take ~2 us. Nothing reads the grids after this kernel, so they are not written back.
+  int* sat = sat_g;
+  int* ssat = ssat_g;
+  if (use_smem) {
+    const int n1 = (gx + 1) * (gy + 1), n2 = (sg.sgx + 1) * (sg.sgy + 1);
+    for (int i = tid; i < n1 + n2; i += blockDim.x) off_s[i] = sat_g[i];  // sat and ssat are contiguous
+    sat = off_s;
+    ssat = off_s + n1;
+    __syncthreads();
+  }
   // row-wise then column-wise inclusive prefix (grids are small: <= 257 x 257)
   for (int pass = 0; pass < 2; pass++) {
     int* g = pass == 0 ? sat : ssat;
@@ -304,8 +318,17 @@ void launch_depth_sort_and_offsets(int P, const Cam& cam, GeomState& g, ImageSta
                                                          img.sat, img.ssat);
   }
   launches += 1;
-  offsets_kernel<<<1, 1024, 0, s>>>(cam.gx, cam.gy, sg, img.sat, img.ssat, img.ranges, img.tile_off, img.l1_off,
-                                   g.flags);
+  {
+    const size_t smem = sat_ints(cam.gx, cam.gy) * sizeof(int);
+    const int use_smem = smem <= 160 * 1024;
+    static bool attr_set = false;
+    if (!attr_set) {
+      cudaFuncSetAttribute(offsets_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+      attr_set = true;
+    }
+    offsets_kernel<<<1, 1024, use_smem ? smem : 0, s>>>(cam.gx, cam.gy, sg, use_smem, img.sat, img.ssat, img.ranges,
+                                                        img.tile_off, img.l1_off, g.flags);
+  }
   launches += 1;
 }
 
