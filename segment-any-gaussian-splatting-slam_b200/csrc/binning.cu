@@ -338,16 +338,16 @@ __device__ __forceinline__ uint32_t super_rect(uint32_t rc, int shift) {
   return (x0 >> shift) | ((y0 >> shift) << 8) | ((((x1 - 1) >> shift) + 1) << 16) | ((((y1 - 1) >> shift) + 1) << 24);
 }
 
-// Supertile lists. One block = 256 consecutive depth ranks = 8 warps. For every supertile s the
-// ballot of "rect overlaps s" ranks the lanes of a warp; per-warp popcounts go to shared memory,
-// an 8-way prefix orders the warps, and a scan over per-(supertile, block) counters (l1_scan_kernel)
-// orders the blocks. WRITE = false produces the block counters, WRITE = true the ranked writes.
+// Supertile lists. One block = 256 consecutive depth ranks = 8 warps. Per (warp, supertile) a lane mask in shared
+// memory ranks the lanes of a warp (lane order = depth order); an 8-way prefix of the mask popcounts orders the warps,
+// and a scan over per-(supertile, block) counters (l1_scan_kernel) orders the blocks. WRITE = false produces the block counters, WRITE = true the ranked writes.
 constexpr int L1_WARPS = 8;
 template <bool WRITE>
 __global__ void __launch_bounds__(256)
 l1_kernel(int P, SuperGrid sg, int shift, const uint64_t* __restrict__ dkeys, const uint32_t* __restrict__ tiles_touched,
           const uint32_t* __restrict__ rect, uint32_t* __restrict__ blk_cnt, int NB, uint2* __restrict__ l1) {
-  __shared__ uint32_t cnt[L1_WARPS][256];  // [warp][supertile]; NS <= 256
+  __shared__ uint32_t cnt[L1_WARPS][256];   // [warp][supertile] write offsets; NS <= 256
+  __shared__ uint32_t mask[L1_WARPS][256];  // [warp][supertile] lanes of the warp that overlap the supertile
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   uint32_t idx = 0, rc = 0, src = 0;
@@ -357,38 +357,34 @@ l1_kernel(int P, SuperGrid sg, int shift, const uint64_t* __restrict__ dkeys, co
     vis = tiles_touched[idx] != 0;
     if (vis) { rc = rect[idx]; src = super_rect(rc, shift); }
   }
-  const bool warp_vis = __any_sync(0xffffffffu, vis);
-  if (!warp_vis) {
-    for (int s = lane; s < sg.NS; s += 32) cnt[w][s] = 0;
-  } else {
-    for (int sy = 0, s = 0; sy < sg.sgy; sy++)
-      for (int sx = 0; sx < sg.sgx; sx++, s++) {
-        const uint32_t pxy = (uint32_t)sx | ((uint32_t)sy << 8);
-        const unsigned m = __ballot_sync(0xffffffffu, vis && rect_has(src, pxy | (pxy << 16)));
-        if (lane == 0) cnt[w][s] = __popc(m);
-      }
-  }
+  // Lane-centric: every visible lane walks its OWN supertile rect (1-4 supertiles for almost every Gaussian) and sets
+  // its bit in the (warp, supertile) lane mask; a lane's rank inside the warp is then the popcount of the lower mask
+  // bits. (A ballot per supertile costs NS votes per warp no matter how few of them anybody overlaps.)
+  for (int s = lane; s < sg.NS; s += 32) mask[w][s] = 0;
+  __syncwarp();
+  const int sx0 = src & 255u, sy0 = (src >> 8) & 255u, sx1 = (src >> 16) & 255u, sy1 = src >> 24;
+  if (vis)
+    for (int sy = sy0; sy < sy1; sy++)
+      for (int sx = sx0; sx < sx1; sx++) atomicOr(&mask[w][sy * sg.sgx + sx], 1u << lane);
   __syncthreads();
   if (threadIdx.x < sg.NS) {  // exclusive prefix over the 8 warps (+ block offset when writing)
     const int s = threadIdx.x;
     uint32_t run = WRITE ? blk_cnt[(size_t)s * NB + blockIdx.x] : 0u;
 #pragma unroll
     for (int q = 0; q < L1_WARPS; q++) {
-      const uint32_t c = cnt[q][s];
       cnt[q][s] = run;
-      run += c;
+      run += (uint32_t)__popc(mask[q][s]);
     }
     if (!WRITE) blk_cnt[(size_t)s * NB + blockIdx.x] = run;
   }
   if (!WRITE) return;
   __syncthreads();
-  if (!warp_vis) return;
-  for (int sy = 0, s = 0; sy < sg.sgy; sy++)
-    for (int sx = 0; sx < sg.sgx; sx++, s++) {
-      const uint32_t pxy = (uint32_t)sx | ((uint32_t)sy << 8);
-      const bool in = vis && rect_has(src, pxy | (pxy << 16));
-      const unsigned m = __ballot_sync(0xffffffffu, in);
-      if (in) l1[cnt[w][s] + __popc(m & ((1u << lane) - 1))] = make_uint2(rc, idx);
+  if (!vis) return;
+  const uint32_t lt = (1u << lane) - 1;
+  for (int sy = sy0; sy < sy1; sy++)
+    for (int sx = sx0; sx < sx1; sx++) {
+      const int s = sy * sg.sgx + sx;
+      l1[cnt[w][s] + __popc(mask[w][s] & lt)] = make_uint2(rc, idx);
     }
 }
 
