@@ -389,15 +389,16 @@ l1_kernel(int P, SuperGrid sg, int shift, const uint64_t* __restrict__ dkeys, co
 }
 
 // one block per supertile: exclusive scan of its row of block counters, offset by the list base
-__global__ void __launch_bounds__(256)
+constexpr int L1_SCAN_THREADS = 1024;
+__global__ void __launch_bounds__(L1_SCAN_THREADS)
 l1_scan_kernel(uint32_t* __restrict__ warp_cnt, int NW, const uint32_t* __restrict__ l1_off) {
-  __shared__ uint32_t warp_sums[8];
+  __shared__ uint32_t warp_sums[32];
   __shared__ uint32_t carry_s;
   uint32_t* row = warp_cnt + (size_t)blockIdx.x * NW;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (threadIdx.x == 0) carry_s = l1_off[blockIdx.x];
   __syncthreads();
-  for (int base = 0; base < NW; base += 256) {
+  for (int base = 0; base < NW; base += L1_SCAN_THREADS) {
     const int i = base + threadIdx.x;
     const uint32_t v = i < NW ? row[i] : 0;
     uint32_t incl = v;
@@ -408,12 +409,22 @@ l1_scan_kernel(uint32_t* __restrict__ warp_cnt, int NW, const uint32_t* __restri
     }
     if (lane == 31) warp_sums[warp] = incl;
     __syncthreads();
-    uint32_t woff = 0;
-    for (int k = 0; k < warp; k++) woff += warp_sums[k];
+    if (warp == 0) {  // exclusive scan of the 32 warp sums
+      const uint32_t ws = warp_sums[lane];
+      uint32_t wi = ws;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, wi, o);
+        if (lane >= o) wi += t;
+      }
+      warp_sums[lane] = wi - ws;
+    }
+    __syncthreads();
     const uint32_t carry = carry_s;
+    const uint32_t woff = warp_sums[warp];
     if (i < NW) row[i] = carry + woff + incl - v;
     __syncthreads();
-    if (threadIdx.x == 255) carry_s = carry + woff + incl;
+    if (threadIdx.x == L1_SCAN_THREADS - 1) carry_s = carry + woff + incl;
     __syncthreads();
   }
 }
@@ -475,7 +486,7 @@ void launch_binning(int P, int64_t R, const Cam& cam, GeomState& g, BinState& b,
   const int shift = sg.S == 8 ? 3 : 4;
   const int nb = (P + 255) / 256;
   l1_kernel<false><<<nb, 256, 0, s>>>(P, sg, shift, g.dkeys_a, g.tiles_touched, g.rect, b.warp_cnt, nb, b.l1);
-  l1_scan_kernel<<<sg.NS, 256, 0, s>>>(b.warp_cnt, nb, img.l1_off);
+  l1_scan_kernel<<<sg.NS, L1_SCAN_THREADS, 0, s>>>(b.warp_cnt, nb, img.l1_off);
   l1_kernel<true><<<nb, 256, 0, s>>>(P, sg, shift, g.dkeys_a, g.tiles_touched, g.rect, b.warp_cnt, nb, b.l1);
   launches += 3;
 }
