@@ -294,8 +294,7 @@ offsets_kernel(int gx, int gy, SuperGrid sg, int use_smem, int* __restrict__ sat
   }
 }
 
-void launch_depth_sort_and_offsets(int P, const Cam& cam, GeomState& g, ImageState& img, cudaStream_t s,
-                                   int& launches) {
+void launch_depth_sort(int P, GeomState& g, cudaStream_t s, int& launches) {
   // 4 stable 8-bit passes over the depth bits (item bits 32..63); a -> b -> a -> b -> a
   uint64_t* a = g.dkeys_a;
   uint64_t* b = g.dkeys_b;
@@ -303,6 +302,11 @@ void launch_depth_sort_and_offsets(int P, const Cam& cam, GeomState& g, ImageSta
     radix_pass(a, b, P, 32 + 8 * pass, 8, g.block_hist, g.digit_total, s, launches);
     uint64_t* t = a; a = b; b = t;
   }
+}
+
+// coverage grids -> list lengths, offsets, ranges, R: independent of the depth order, so it is queued BEFORE the sort and
+// the host reads R back while the sort is still running
+void launch_offsets(int P, const Cam& cam, GeomState& g, ImageState& img, cudaStream_t s, int& launches) {
   const SuperGrid sg = super_grid(cam.gx, cam.gy);
   {
     const size_t smem = sat_ints(cam.gx, cam.gy) * sizeof(int);

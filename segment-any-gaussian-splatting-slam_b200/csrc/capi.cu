@@ -49,6 +49,7 @@ thread_local int* g_pinned = nullptr;  // 8 ints of pinned host memory for the n
 struct StageSpan { int stage; cudaEvent_t a, b; };
 thread_local bool g_timing = false;
 thread_local uint8_t* g_touched = nullptr;  // gsr_set_touched_mask
+thread_local cudaEvent_t g_ev_R = nullptr;  // num_rendered read-back
 thread_local cudaEvent_t g_blend_done = nullptr;  // gsr_set_blend_done_event
 thread_local std::vector<StageSpan> g_spans;
 thread_local std::vector<cudaEvent_t> g_free_events;
@@ -189,17 +190,22 @@ int gsr_forward(const gsr_params* p, gsr_alloc_fn geom_alloc, void* geom_ctx, gs
   }
   g_launches += 1;
   STAGE_CHECK("preprocess");
+  // The one data-dependent host sync of the path (reference: rasterizer_impl.cu:289-290). num_rendered comes out of the
+  // coverage grids, not out of the sort: offsets first, their read-back queued, then the depth sort -- the host waits
+  // for the read-back event only and sizes / allocates / enqueues the next stages while the sort is still running.
+  if (!g_pinned) CUDA_TRY(cudaHostAlloc(&g_pinned, 8 * sizeof(int), cudaHostAllocDefault));
+  if (!g_ev_R) CUDA_TRY(cudaEventCreateWithFlags(&g_ev_R, cudaEventDisableTiming));
+  unsigned long long t_enq;
   {
     StageTimer tm(1, stream);
-    gsr::launch_depth_sort_and_offsets(P, cam, g, img, stream, g_launches);
+    gsr::launch_offsets(P, cam, g, img, stream, g_launches);
+    t_enq = now_us();
+    CUDA_TRY(cudaMemcpyAsync(g_pinned, g.flags, 4 * sizeof(int), cudaMemcpyDeviceToHost, stream));
+    CUDA_TRY(cudaEventRecord(g_ev_R, stream));
+    gsr::launch_depth_sort(P, g, stream, g_launches);
   }
   STAGE_CHECK("depth_sort");
-
-  // the one data-dependent host sync of the path (reference: rasterizer_impl.cu:289-290)
-  if (!g_pinned) CUDA_TRY(cudaHostAlloc(&g_pinned, 8 * sizeof(int), cudaHostAllocDefault));
-  const unsigned long long t_enq = now_us();
-  CUDA_TRY(cudaMemcpyAsync(g_pinned, g.flags, 4 * sizeof(int), cudaMemcpyDeviceToHost, stream));
-  CUDA_TRY(cudaStreamSynchronize(stream));
+  CUDA_TRY(cudaEventSynchronize(g_ev_R));
   const unsigned long long t_sync = now_us();
   const int64_t R = (int64_t)(uint32_t)g_pinned[0];
   const uint64_t l1_total = (uint64_t)(uint32_t)g_pinned[2] | ((uint64_t)(uint32_t)g_pinned[3] << 32);

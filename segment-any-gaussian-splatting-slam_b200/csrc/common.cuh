@@ -178,7 +178,8 @@ void launch_preprocess(const FwdInputs& in, const Cam& cam, GeomState& g, ImageS
                        uint8_t* is_used, cudaStream_t s);
 // depth sort (leaves depth-ordered keys in g.dkeys_a) + tile / supertile offsets from the coverage
 // grids: ranges, tile_off, l1_off, R -> g.flags[0], L1 total -> g.flags[2..3]
-void launch_depth_sort_and_offsets(int P, const Cam& cam, GeomState& g, ImageState& img, cudaStream_t s, int& launches);
+void launch_offsets(int P, const Cam& cam, GeomState& g, ImageState& img, cudaStream_t s, int& launches);
+void launch_depth_sort(int P, GeomState& g, cudaStream_t s, int& launches);
 // supertile lists (the forward blend pulls each tile's list out of its supertile's list as it goes)
 void launch_binning(int P, int64_t R, const Cam& cam, GeomState& g, BinState& b, ImageState& img, cudaStream_t s,
                     int& launches);
