@@ -5,6 +5,7 @@
 #include <chrono>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -50,6 +51,11 @@ struct StageSpan { int stage; cudaEvent_t a, b; };
 thread_local bool g_timing = false;
 thread_local uint8_t* g_touched = nullptr;  // gsr_set_touched_mask
 thread_local cudaEvent_t g_ev_R = nullptr;  // num_rendered read-back
+// side stream of this thread for the depth sort (created on first use, lives with the thread)
+thread_local cudaStream_t g_side = nullptr;
+thread_local cudaEvent_t g_fork = nullptr, g_join = nullptr;
+thread_local int g_side_dev = -1;
+const bool g_no_side_sort = getenv("GSR_NO_SIDE_SORT") != nullptr;  // diagnostics: everything on the caller's stream
 thread_local cudaEvent_t g_blend_done = nullptr;  // gsr_set_blend_done_event
 thread_local std::vector<StageSpan> g_spans;
 thread_local std::vector<cudaEvent_t> g_free_events;
@@ -198,11 +204,29 @@ int gsr_forward(const gsr_params* p, gsr_alloc_fn geom_alloc, void* geom_ctx, gs
   unsigned long long t_enq;
   {
     StageTimer tm(1, stream);
+    // The depth sort (twelve small latency-bound launches) and the coverage / offsets kernels only share their input
+    // (the preprocess outputs): the sort runs on this thread's side stream beside them and joins before binning.
+    cudaStream_t sort_stream = stream;
+    if (!g_no_side_sort) {
+      int dev = 0;
+      CUDA_TRY(cudaGetDevice(&dev));
+      if (!g_side || g_side_dev != dev) {  // one side stream per (thread, device)
+        g_side_dev = dev;
+        CUDA_TRY(cudaStreamCreateWithFlags(&g_side, cudaStreamNonBlocking));
+        CUDA_TRY(cudaEventCreateWithFlags(&g_fork, cudaEventDisableTiming));
+        CUDA_TRY(cudaEventCreateWithFlags(&g_join, cudaEventDisableTiming));
+      }
+      CUDA_TRY(cudaEventRecord(g_fork, stream));
+      CUDA_TRY(cudaStreamWaitEvent(g_side, g_fork, 0));
+      sort_stream = g_side;
+    }
+    gsr::launch_depth_sort(P, g, sort_stream, g_launches);
+    if (sort_stream != stream) CUDA_TRY(cudaEventRecord(g_join, g_side));
     gsr::launch_offsets(P, cam, g, img, stream, g_launches);
     t_enq = now_us();
     CUDA_TRY(cudaMemcpyAsync(g_pinned, g.flags, 4 * sizeof(int), cudaMemcpyDeviceToHost, stream));
     CUDA_TRY(cudaEventRecord(g_ev_R, stream));
-    gsr::launch_depth_sort(P, g, stream, g_launches);
+    if (sort_stream != stream) CUDA_TRY(cudaStreamWaitEvent(stream, g_join, 0));
   }
   STAGE_CHECK("depth_sort");
   CUDA_TRY(cudaEventSynchronize(g_ev_R));
