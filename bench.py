@@ -498,6 +498,55 @@ def feature_loss_leg(args, hbm_gbs):
                      "not part of `value`")
 
 
+def cls3d_leg(args):
+    """SURVEY 8f N4 (next row): fused 3-D feature-consistency regulariser at the reference's call-site sizes (300 000-point
+    subset, 1 000 samples, k = 5, C = 100) on the headline map, with the torch composition the reference runs (classifier
+    + softmax over ALL Gaussians, cdist, topk, KL, autograd) timed beside it."""
+    import torch
+    from gsraster_b200 import losses
+    P, F, C = args.P, args.F, 100
+    dev = torch.device("cuda", torch.cuda.current_device())
+    torch.manual_seed(11)
+    classifier = torch.nn.Conv2d(F, C, kernel_size=1).to(dev)
+    xyz = torch.randn(P, 3, device=dev) * 4
+    objects_dc = torch.randn(P, 1, F, device=dev)
+    fn = losses.Cls3DLoss(classifier, device=dev)
+    subset, sample = losses.Cls3DLoss.draw_indices(P, 300000, 1000, device=dev, generator=torch.Generator().manual_seed(2))
+    grad, out1 = torch.zeros(P, F, device=dev), torch.empty(1, device=dev)
+
+    def timed(f, n):
+        for _ in range(2):
+            f()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(n):
+            f()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / n
+
+    ms = timed(lambda: fn(xyz, objects_dc.view(P, F), subset, sample, grad_out=grad, out=out1), 10)
+    xo = objects_dc.clone().requires_grad_(True)
+    sub64 = None if subset is None else subset.long()
+    smp64 = sample.long()
+
+    def torch_composition():   # scripts/gaussian_splatting.py:812-814 + utils/loss_utils.py:86-112 with the draws fixed
+        xo.grad = None
+        prob = torch.softmax(classifier(xo.permute(2, 0, 1)), dim=0).squeeze().permute(1, 0)
+        feats, preds = (xyz, prob) if sub64 is None else (xyz[sub64], prob[sub64])
+        sp = preds[smp64]
+        nb = torch.cdist(feats[smp64], feats).topk(5, largest=False).indices
+        kl = sp.unsqueeze(1) * (torch.log(sp.unsqueeze(1) + 1e-10) - torch.log(preds[nb] + 1e-10))
+        (2.0 * kl.sum(dim=-1).mean() / C).backward()
+
+    tms = timed(torch_composition, 3)
+    return dict(ms=round(ms, 4), torch_composition_ms=round(tms, 4), subset=int(300000 if subset is not None else P), samples=1000,
+                note="gsr_cls3d_loss: kNN (k=5) of 1 000 samples in a 300 000-point subset + classifier/softmax/KL of the "
+                     "1 + k points of each sample + gradient scattered to dL/dobjects; torch_composition_ms = the "
+                     "reference's lines in torch on this GPU; every 5th mapping iteration, not part of `value`")
+
+
 def cpu_baseline(args, threads=None):
     """CPU oracle port (oracle/oracle.cpp, OpenMP) timed on the host cores on a bounded sample."""
     import numpy as np
@@ -664,6 +713,10 @@ def main():
             out["feature_loss_n2"] = feature_loss_leg(args, pk["hbm_gbs"])
         except Exception as ex:
             out["feature_loss_n2"] = dict(error=repr(ex)[:200])
+        try:
+            out["cls3d_n4"] = cls3d_leg(args)
+        except Exception as ex:
+            out["cls3d_n4"] = dict(error=repr(ex)[:200])
     if world == 1 and not args.no_cpu_baseline:
         cb = cpu_baseline(args)
         out["cpu_baseline"] = {k: (round(cb[k], 5) if k == "value" else cb[k]) for k in ("value", "unit", "cores", "kind", "sample")}

@@ -219,6 +219,22 @@ int gsr_feature_loss(const float* objects, const long long* gt, int H, int W, in
                      const float* bias, float grad_weight, float* dL_dobjects, int* pred, float* out2, char* scratch,
                      void* stream);
 
+/* ---- 3-D feature-consistency regulariser (every 5th mapping iteration) ------------------------------
+ * loss_cls_3d(xyz, softmax(classifier(objects_dc)), k, lambda, max_points, sample_size) of utils/loss_utils.py:71-112 as
+ * called at scripts/gaussian_splatting.py:812-814: for each of S sample points the k nearest of n subset points (the
+ * point itself included, as torch.cdist + topk does), KL(p_sample || p_neighbour) summed over the C classes, mean over
+ * (sample, neighbour), / C, * lambda. The two random index sets the reference draws with torch.randperm are INPUTS:
+ * subset (n indices into the N Gaussians, NULL = all N) and sample (S indices into the subset). xyz (N,3), objects (N,F)
+ * fp32 device; weight (C,F), bias (C) of the classifier. out1 (device float) = the loss; neighbors (S*k device ints) =
+ * the neighbour lists (subset indices, ascending distance; ties by index); dL_dobjects (N,F), may be NULL:
+ * grad_weight * d loss / d objects is ADDED to it (float atomics: a Gaussian can serve several samples).
+ * scratch: gsr_cls3d_loss_scratch_bytes(S, n) bytes, 16-byte aligned (n = N when subset is NULL). k in {1,3,5,8}, 2 <= C <= 256, F <= 64. Only the 1 + k points of each sample
+ * go through classifier and softmax; no (C,N) probability tensor and no S x n distance matrix exist. */
+size_t gsr_cls3d_loss_scratch_bytes(int S, int n);
+int gsr_cls3d_loss(const float* xyz, const float* objects, int N, int F, int C, const float* weight, const float* bias,
+                   const int* subset, int n, const int* sample, int S, int k, float lambda_val, float grad_weight,
+                   float* dL_dobjects, float* out1, int* neighbors, char* scratch, void* stream);
+
 /* a_* of all P Gaussians from the raw parameters (first iteration, after map growth). */
 int gsr_activate(const gsr_adam_tensors* t, int P, int M, void* stream);
 /* One Adam step (step = 1, 2, ...; lr[7] in the group order above) + re-activation of the stepped rows.

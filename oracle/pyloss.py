@@ -46,3 +46,27 @@ def feature_loss(objects, gt, weight, bias):
     d *= use[None, :] / (z.shape[1] * np.log(Cn))
     dobj = weight.reshape(Cn, Fd).astype(np.float64).T @ d
     return mean_ce / np.log(Cn), mean_ce, dobj.reshape(Fd, H, W), z.argmax(0).reshape(H, W)
+
+
+def cls3d_loss(xyz, objects, weight, bias, subset, sample, k=5, lambda_val=2.0):
+    """TEST INFRASTRUCTURE. loss_cls_3d (utils/loss_utils.py:71-112) on prob = softmax(classifier(objects)) as called at
+    scripts/gaussian_splatting.py:812-814, restated in torch float64 with the two random index sets given (subset: indices
+    into the P points or None; sample: indices into the subset). Exact pairwise distances (the reference's torch.cdist may
+    use the |a|^2 + |b|^2 - 2ab form; neighbour sets agree except for near-ties).
+    -> (loss, d loss / d objects (P,F), neighbour indices (S,k) into the subset)."""
+    x = torch.as_tensor(xyz, dtype=torch.float64)
+    o = torch.as_tensor(objects, dtype=torch.float64).reshape(x.shape[0], -1).clone().requires_grad_(True)
+    W = torch.as_tensor(weight, dtype=torch.float64).reshape(-1, o.shape[1])
+    b = torch.as_tensor(bias, dtype=torch.float64)
+    prob = torch.softmax(o @ W.T + b, dim=1)
+    if subset is not None:
+        sub = torch.as_tensor(subset, dtype=torch.int64)
+        x, prob = x[sub], prob[sub]
+    smp = torch.as_tensor(sample, dtype=torch.int64)
+    d = ((x[smp][:, None, :] - x[None, :, :]) ** 2).sum(-1)
+    nb = d.topk(k, largest=False).indices
+    sp, npr = prob[smp], prob[nb]
+    kl = sp[:, None, :] * (torch.log(sp[:, None, :] + 1e-10) - torch.log(npr + 1e-10))
+    loss = lambda_val * kl.sum(-1).mean() / prob.shape[1]
+    loss.backward()
+    return float(loss), o.grad.numpy(), nb.numpy()

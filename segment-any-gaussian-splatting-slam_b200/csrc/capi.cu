@@ -16,6 +16,10 @@
 namespace gsr {
 size_t photometric_scratch_bytes(int H, int W);
 size_t feature_loss_scratch_bytes();
+size_t cls3d_scratch_bytes(int S, int n);
+bool launch_cls3d(const float* xyz, const float* objects, int F, int C, const float* weight, const float* bias,
+                  const int* subset, int n, const int* sample, int S, int k, float lambda_val, float grad_weight,
+                  float* dobj, float* out1, int* neighbors, char* scratch, cudaStream_t s);
 bool launch_feature_loss(const float* obj, const long long* gt, int HW, int F, int C, const float* weight, const float* bias,
                          float grad_weight, float* dobj, int* pred, float* out2, char* scratch, cudaStream_t s);
 void launch_photometric_loss(const float* img, const float* gt, int H, int W, float lambda, float* dL_dimg, float* out3,
@@ -440,6 +444,24 @@ int gsr_exchange_sum_rows_peers(const float* const* buckets, int nranks, int nte
                              (cudaStream_t)stream_);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "exchange_sum_rows_peers: %s", cudaGetErrorString(e));
+  return GSR_OK;
+}
+
+size_t gsr_cls3d_loss_scratch_bytes(int S, int n) { return gsr::cls3d_scratch_bytes(S, n); }
+
+int gsr_cls3d_loss(const float* xyz, const float* objects, int N, int F, int C, const float* weight, const float* bias,
+                   const int* subset, int n, const int* sample, int S, int k, float lambda_val, float grad_weight,
+                   float* dL_dobjects, float* out1, int* neighbors, char* scratch, void* stream_) {
+  if (!xyz || !objects || !weight || !bias || !sample || !out1 || !neighbors || !scratch || N <= 0)
+    return fail(GSR_ERR_INVALID_ARGUMENT, "cls3d_loss: bad argument");
+  if (!subset) n = N;
+  if ((uintptr_t)scratch & 15) return fail(GSR_ERR_INVALID_ARGUMENT, "cls3d_loss: scratch must be 16-byte aligned");
+  if (!gsr::launch_cls3d(xyz, objects, F, C, weight, bias, subset, n, sample, S, k, lambda_val, grad_weight, dL_dobjects,
+                         out1, neighbors, scratch, (cudaStream_t)stream_))
+    return fail(GSR_ERR_INVALID_ARGUMENT, "cls3d_loss: unsupported size (k in {1,3,5,8}, 2 <= C <= 256, F <= 64; got k=%d C=%d F=%d)",
+                k, C, F);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "cls3d_loss: %s", cudaGetErrorString(e));
   return GSR_OK;
 }
 

@@ -49,7 +49,7 @@ def _check_grads(mine, ref, tol=GRAD_TOL, ref_again=None):
 
 def _golden_cases():
     return sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "*.npz"))
-                  if not os.path.basename(p).startswith(("knn", "loss_", "featloss_")))
+                  if not os.path.basename(p).startswith(("knn", "loss_", "featloss_", "cls3d_")))
 
 
 @pytest.mark.parametrize("name", _golden_cases())
