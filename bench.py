@@ -547,6 +547,69 @@ def cls3d_leg(args):
                      "reference's lines in torch on this GPU; every 5th mapping iteration, not part of `value`")
 
 
+def store_leg(args):
+    """SURVEY 8f N3 (next row): map growth and pruning on the capacity-managed store against the reference's torch
+    operations (torch.cat of the 21 parameter / Adam-moment tensors per frame; boolean-mask indexing of them per prune)."""
+    import torch
+    from gsraster_b200 import store
+    from gsraster_b200.optim import GROUPS
+    P, M, F, n_new = args.P, (args.deg + 1) ** 2, args.F, 30000
+    dev = torch.device("cuda", torch.cuda.current_device())
+    g = torch.Generator(device=dev).manual_seed(3)
+    shapes = store.row_shapes(M, F)
+    rows = lambda n: {k: torch.randn((n,) + s, generator=g, device=dev) for k, s in shapes.items()}
+    base, new = rows(P), rows(n_new)
+    base["opacity"] *= 3.0
+
+    def timed(f, n):
+        f()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(n):
+            f()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / n
+
+    st = store.GaussianStore(P + 8 * n_new, M, F, device=dev)
+    st.append(base)
+
+    def grow():
+        st.count = P
+        st.append(new)
+
+    grow_ms = timed(grow, 5)
+    st.count = P
+
+    f0 = st.front
+
+    def prune():
+        st.front, st.count = f0, P      # compaction is out of place: the original rows are still in set f0
+        st.prune_large_and_transparent(0.3, None)
+
+    prune_ms = timed(prune, 3)
+    kept = st.count
+    st.count = 0
+    del st
+    ref = [{k: v.clone() for k, v in base.items()} for _ in range(3)]
+
+    def torch_grow():   # cat_tensors_to_optimizer: parameters + zero moments
+        return [{k: torch.cat((r[k], new[k] if i == 0 else torch.zeros_like(new[k])), dim=0) for k in GROUPS}
+                for i, r in enumerate(ref)]
+
+    def torch_prune():  # prune_large_and_transparent + _prune_optimizer
+        valid = ~(torch.sigmoid(ref[0]["opacity"]) < 0.3).squeeze()
+        return [{k: r[k][valid] for k in GROUPS} for r in ref]
+
+    tg, tp = timed(torch_grow, 3), timed(torch_prune, 3)
+    return dict(grow_ms=round(grow_ms, 4), torch_cat_ms=round(tg, 4), prune_ms=round(prune_ms, 4), torch_mask_index_ms=round(tp, 4),
+                new_rows=n_new, kept_rows=kept,
+                note="GaussianStore.append (new rows written behind the count) / prune_large_and_transparent (flags, "
+                     "compaction list, 3 row-gather launches, count read-back) at P rows vs torch.cat / boolean-mask "
+                     "indexing of the 21 parameter and Adam-moment tensors on this GPU; not part of `value`")
+
+
 def cpu_baseline(args, threads=None):
     """CPU oracle port (oracle/oracle.cpp, OpenMP) timed on the host cores on a bounded sample."""
     import numpy as np
@@ -717,6 +780,10 @@ def main():
             out["cls3d_n4"] = cls3d_leg(args)
         except Exception as ex:
             out["cls3d_n4"] = dict(error=repr(ex)[:200])
+        try:
+            out["store_n3"] = store_leg(args)
+        except Exception as ex:
+            out["store_n3"] = dict(error=repr(ex)[:200])
     if world == 1 and not args.no_cpu_baseline:
         cb = cpu_baseline(args)
         out["cpu_baseline"] = {k: (round(cb[k], 5) if k == "value" else cb[k]) for k in ("value", "unit", "cores", "kind", "sample")}

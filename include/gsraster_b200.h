@@ -219,6 +219,16 @@ int gsr_feature_loss(const float* objects, const long long* gt, int H, int W, in
                      const float* bias, float grad_weight, float* dL_dobjects, int* pred, float* out2, char* scratch,
                      void* stream);
 
+/* ---- map pruning as stream compaction ---------------------------------------------------------------
+ * keep[i] = !(sigmoid(opacity[i]) < min_opacity || max_c exp(scaling[i][c]) > max_scale) -- the mask of
+ * prune_large_and_transparent (scene/gaussian_model.py:624-636; max_scale = 0.1 * extent, <= 0 = no size test) on the RAW
+ * parameters. The rows are then moved with the exchange kernels above: gsr_exchange_compact(keep, 1, P, Ppad, P, idx,
+ * count, ...) builds the ascending list of kept rows, gsr_exchange_rows(0, ...) gathers up to 8 tensors per call into a
+ * second buffer (parameters and both Adam moments: the reference indexes all 21 tensors with a boolean mask,
+ * :443-470). keep: P bytes padded to a multiple of 4. */
+int gsr_prune_flags(const float* opacity, const float* scaling, int P, float min_opacity, float max_scale, uint8_t* keep,
+                    void* stream);
+
 /* ---- 3-D feature-consistency regulariser (every 5th mapping iteration) ------------------------------
  * loss_cls_3d(xyz, softmax(classifier(objects_dc)), k, lambda, max_points, sample_size) of utils/loss_utils.py:71-112 as
  * called at scripts/gaussian_splatting.py:812-814: for each of S sample points the k nearest of n subset points (the

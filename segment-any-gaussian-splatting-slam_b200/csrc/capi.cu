@@ -34,6 +34,8 @@ void launch_union_compact_peers(const uint8_t* const* flags, int nranks, int P, 
                                 cudaStream_t s);
 void launch_sum_rows_peers(const float* const* buckets, int nranks, int ntensors, const long long* off, float* const* dst,
                            const int* n, const int* idx, const int* count, int cap, cudaStream_t s);
+void launch_prune_flags(const float* opacity, const float* scaling, int P, float min_opacity, float max_scale,
+                        uint8_t* keep, cudaStream_t s);
 void launch_rows(bool scatter, int ntensors, const float* const* src, float* const* dst, const int* n, const int* idx,
                  const int* count, int cap, cudaStream_t s);
 void launch_export_keys(int T, const uint2* ranges, const uint32_t* point_list, const float4* rec, uint64_t* keys,
@@ -444,6 +446,15 @@ int gsr_exchange_sum_rows_peers(const float* const* buckets, int nranks, int nte
                              (cudaStream_t)stream_);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "exchange_sum_rows_peers: %s", cudaGetErrorString(e));
+  return GSR_OK;
+}
+
+int gsr_prune_flags(const float* opacity, const float* scaling, int P, float min_opacity, float max_scale, uint8_t* keep,
+                    void* stream_) {
+  if (!opacity || !keep || P < 0 || (max_scale > 0.f && !scaling)) return fail(GSR_ERR_INVALID_ARGUMENT, "prune_flags: bad argument");
+  gsr::launch_prune_flags(opacity, scaling, P, min_opacity, max_scale, keep, (cudaStream_t)stream_);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "prune_flags: %s", cudaGetErrorString(e));
   return GSR_OK;
 }
 

@@ -165,6 +165,25 @@ xc_scatter_kernel(XcTensors t, const int* __restrict__ idx, const int* __restric
   }
 }
 
+// keep flags of prune_large_and_transparent (scene/gaussian_model.py:624-636):
+// prune = sigmoid(opacity) < min_opacity  ||  max_c exp(scaling_c) > max_scale   (max_scale <= 0: no size test)
+__global__ void __launch_bounds__(256)
+prune_flags_kernel(const float* __restrict__ opacity, const float* __restrict__ scaling, int P, float min_opacity,
+                   float max_scale, uint8_t* __restrict__ keep) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= P) return;
+  bool prune = 1.f / (1.f + expf(-opacity[i])) < min_opacity;
+  if (max_scale > 0.f) {
+    const float m = fmaxf(fmaxf(scaling[3 * (size_t)i], scaling[3 * (size_t)i + 1]), scaling[3 * (size_t)i + 2]);
+    prune = prune || expf(m) > max_scale;  // exp is monotonic: max of the exps = exp of the max
+  }
+  keep[i] = prune ? 0 : 1;
+}
+void launch_prune_flags(const float* opacity, const float* scaling, int P, float min_opacity, float max_scale,
+                        uint8_t* keep, cudaStream_t s) {
+  if (P > 0) prune_flags_kernel<<<(P + 255) / 256, 256, 0, s>>>(opacity, scaling, P, min_opacity, max_scale, keep);
+}
+
 size_t exchange_scratch_bytes(int P) { return ((size_t)(P + XC_TILE - 1) / XC_TILE + 8) * sizeof(uint32_t); }
 
 static void union_compact(const XcPeers& f, int P, int cap, int* idx, int* count, char* scratch, cudaStream_t s) {
