@@ -158,7 +158,8 @@ int gsr_set_blend_done_event(void* event);
 size_t gsr_exchange_scratch_bytes(int P);
 int gsr_exchange_compact(const uint8_t* flags, int nranks, int P, int Ppad, int cap, int* idx, int* count, char* scratch,
                          void* stream);
-/* Row gather (scatter = 0): compact[t][r][:] = dense[t][idx[r]][:] for r < min(*count, cap), zeros up to cap; or row
+/* Row gather (scatter = 0): compact[t][r][:] = dense[t][idx[r]][:] for r < min(*count, cap), zeros up to cap (scatter = 2:
+ * the same without the zero fill, rows >= *count are left untouched: stream compaction); or row
  * scatter (scatter = 1): dense[t][idx[r]][:] = compact[t][r][:]. t < ntensors <= 8 tensors of floats_per_row[t] floats per
  * Gaussian; the pointer arrays are HOST arrays of device pointers. */
 int gsr_exchange_rows(int scatter, int ntensors, const float* const* dense, float* const* compact,

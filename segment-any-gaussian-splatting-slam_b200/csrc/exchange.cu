@@ -151,6 +151,26 @@ xc_gather_sum_kernel(XcPeerTensors t, XcPeers buckets, const int* __restrict__ i
     }
   }
 }
+// The same gather with a thread per OUTPUT element (blockIdx.y = tensor): rows of 1-45 floats leave most lanes of a
+// warp-per-row kernel idle, which matters when the list is long (map pruning moves 10^5-10^6 rows x 21 tensors).
+// zero_tail: rows [count, cap) are zero-filled (the all-reduce of the NCCL exchange reads all cap rows).
+__global__ void __launch_bounds__(256)
+xc_gather_flat_kernel(XcTensors t, const int* __restrict__ idx, const int* __restrict__ count, int cap, int zero_tail) {
+  const int k = blockIdx.y;
+  const unsigned n = (unsigned)t.n[k];
+  const float* __restrict__ src = t.src[k];
+  float* __restrict__ dst = t.dst[k];
+  const int nrows = min(*count, cap);
+  const size_t live = (size_t)nrows * n, total = zero_tail ? (size_t)cap * n : live;
+  for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+    float v = 0.f;
+    if (e < live) {
+      const unsigned r = (unsigned)(e / n), i = (unsigned)(e - (size_t)r * n);
+      v = src[(size_t)idx[r] * n + i];
+    }
+    dst[e] = v;
+  }
+}
 // dense[t][idx[r]][:] = compact[t][r][:] for r < min(count, cap) (the caller zeroes dense first)
 __global__ void __launch_bounds__(256)
 xc_scatter_kernel(XcTensors t, const int* __restrict__ idx, const int* __restrict__ count, int cap) {
@@ -220,15 +240,20 @@ void launch_sum_rows_peers(const float* const* buckets, int nranks, int ntensors
   const int nb = (cap + 7) / 8;
   xc_gather_sum_kernel<<<nb < 148 * 8 ? nb : 148 * 8, 256, 0, s>>>(t, b, idx, count, cap);
 }
-void launch_rows(bool scatter, int ntensors, const float* const* src, float* const* dst, const int* n, const int* idx,
+void launch_rows(int scatter, int ntensors, const float* const* src, float* const* dst, const int* n, const int* idx,
                  const int* count, int cap, cudaStream_t s) {
   XcTensors t;
   t.count = ntensors;
   for (int k = 0; k < ntensors; k++) { t.src[k] = src[k]; t.dst[k] = dst[k]; t.n[k] = n[k]; }
   if (cap <= 0) return;
   const int nb = (cap + 7) / 8;
-  if (scatter) xc_scatter_kernel<<<nb, 256, 0, s>>>(t, idx, count, cap);
-  else xc_gather_kernel<<<nb, 256, 0, s>>>(t, idx, count, cap);
+  if (scatter == 1) {
+    xc_scatter_kernel<<<nb, 256, 0, s>>>(t, idx, count, cap);
+  } else if (cap < 16384) {  // short lists (one view's touched rows): a warp per row, one launch, no index division
+    xc_gather_kernel<<<nb, 256, 0, s>>>(t, idx, count, cap);
+  } else {
+    xc_gather_flat_kernel<<<dim3(148 * 8, ntensors), 256, 0, s>>>(t, idx, count, cap, scatter == 0 ? 1 : 0);
+  }
 }
 
 }  // namespace gsr

@@ -327,7 +327,7 @@ def exchange_rows(scatter, dense, compact, floats_per_row, idx, count, cap):
     cp = (C.c_void_p * n)(*[t.data_ptr() for t in compact])
     fp = (C.c_int * n)(*[int(v) for v in floats_per_row])
     with torch.cuda.device(idx.device):
-        _check(lib().gsr_exchange_rows(int(bool(scatter)), n, dp, cp, fp, idx.data_ptr(), count.data_ptr(), int(cap),
+        _check(lib().gsr_exchange_rows(int(scatter), n, dp, cp, fp, idx.data_ptr(), count.data_ptr(), int(cap),
                                        _stream_ptr()))
 
 

@@ -98,7 +98,7 @@ class GaussianStore:
         src, dst = self.sets[self.front], self.sets[self.front ^ 1]
         widths = [int(torch.tensor(self.shapes[k]).prod()) for k in GROUPS]
         for kind in range(3):
-            capi.exchange_rows(False, [src[kind][k] for k in GROUPS], [dst[kind][k] for k in GROUPS], widths, self.idx,
+            capi.exchange_rows(2, [src[kind][k] for k in GROUPS], [dst[kind][k] for k in GROUPS], widths, self.idx,
                                self.count_dev, P)
         self.front ^= 1
         self.count = int(self.count_dev.item())
