@@ -4,6 +4,7 @@
 // kernels stage with TMA bulk copies), the packed tile rect, and the depth-sort key.
 #include "common.cuh"
 #include "math.cuh"
+#include "tma.cuh"
 
 namespace gsr {
 
@@ -81,13 +82,20 @@ preprocess_kernel(const FwdInputs in, const Cam cam, float4* __restrict__ rec, u
   const int first = blockIdx.x * PF_THREADS;
   const int idx = first + threadIdx.x;
   const bool staged_sh = in.colors_precomp == nullptr && in.M == 16 && (((uintptr_t)in.shs & 15) == 0);
+  // Every thread fetches its own 192-byte SH row with one TMA bulk copy into its padded tile row; the copies complete
+  // on one mbarrier and are only waited for right before the colour evaluation, i.e. they fly underneath the geometry
+  // loads and the covariance projection (a plain load + barrier here exposed the full HBM latency up front).
+  __shared__ uint64_t sh_bar;
   if (staged_sh) {
-    const int n = min(PF_THREADS, in.P - first) * 12;
-    const float4* src = reinterpret_cast<const float4*>(in.shs) + (size_t)first * 12;
-    for (int i = threadIdx.x; i < n; i += PF_THREADS) sh_tile[(i / 12) * 13 + i % 12] = src[i];
+    if (threadIdx.x == 0) {
+      mbar_init(&sh_bar, 1);
+      mbar_fence_init();
+    }
     __syncthreads();
+    if (threadIdx.x == 0) mbar_arrive_expect_tx(&sh_bar, (uint32_t)min(PF_THREADS, in.P - first) * 192u);
+    if (idx < in.P) tma_load_1d(&sh_tile[threadIdx.x * 13], in.shs + (size_t)idx * 48, 192, &sh_bar);
   }
-  if (idx >= in.P) return;
+  if (idx >= in.P) return;  // (these threads issued no copy; the block lives on through the threads that wait below)
 
   int my_radius_i = 0;
   uint32_t touched = 0;
@@ -137,6 +145,7 @@ preprocess_kernel(const FwdInputs in, const Cam cam, float4* __restrict__ rec, u
     float rgb[3];
     unsigned cbits = 0;
     if (staged_sh) {
+      mbar_wait(&sh_bar, 0);
       float4 shl[12];
 #pragma unroll
       for (int q = 0; q < 12; q++) shl[q] = sh_tile[threadIdx.x * 13 + q];
@@ -175,6 +184,8 @@ preprocess_kernel(const FwdInputs in, const Cam cam, float4* __restrict__ rec, u
   tiles_touched[idx] = touched;
   dkeys[idx] = key;
   if (is_used) is_used[idx] = touched > 0;
+  // culled threads never looked at the tile, but the block must not retire while bulk copies into it are in flight
+  if (staged_sh) mbar_wait(&sh_bar, 0);
 }
 
 void launch_preprocess(const FwdInputs& in, const Cam& cam, GeomState& g, ImageState& img, int* radii,
