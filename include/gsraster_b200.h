@@ -11,8 +11,14 @@
  * column-major flat, images CHW).
  *
  * Status codes: 0 = ok, negative = error; gsr_last_error() returns a thread-local message.
- * Threading: no global mutable state besides the thread-local error string; safe to call from one
- * host thread per device/stream concurrently. Every call is stream-ordered on params->stream.
+ * Threading: like the reference's static Rasterizer API (rasterizer.h:20-94) the library has NO mode switches and no
+ * state that one call sets for another to read: everything a call does differently from the reference is passed to
+ * THAT call (gsr_params::ext below). What the library keeps is (i) thread-local OUTPUT records of the calling
+ * thread's last call (error string, launch count, forward statistics), (ii) per-(host thread, device) helper
+ * resources created on first use (a side stream, three events, 32 bytes of pinned memory), (iii) a per-device
+ * "opted into large dynamic shared memory" bitmap. Any number of host threads may therefore call concurrently, on
+ * the same or on different devices, each on its own stream. Every call is stream-ordered on params->stream and runs
+ * on the CUDA device that is current on the calling thread.
  */
 #ifndef GSRASTER_B200_H_
 #define GSRASTER_B200_H_
@@ -36,6 +42,55 @@ extern "C" {
  * matching backward call has completed. */
 typedef char* (*gsr_alloc_fn)(void* ctx, size_t bytes);
 
+/* ---- per-call extensions (no reference equivalent) ---------------------------------------------------------------
+ * gsr_params::ext == NULL gives exactly the reference's behaviour. A zero-initialised gsr_ext is the same as NULL. */
+typedef struct gsr_timer gsr_timer; /* opaque: per-stage CUDA-event spans of the calls it was handed to (gsr_timer_*) */
+typedef struct gsr_stats {          /* OUT: filled by gsr_forward / gsr_backward when ext->stats != NULL */
+  unsigned long long num_rendered;  /* forward: R = sum of tiles touched */
+  unsigned long long l1_total;      /* forward: total length of the supertile lists (binning intermediate) */
+  unsigned long long sync_us;       /* forward: host microseconds blocked in the num_rendered read-back */
+  unsigned long long alloc_us;      /* forward: host microseconds inside the binning allocator callback */
+  unsigned long long launch_us;     /* forward: host microseconds launching the post-read-back kernels */
+  int launches;                     /* kernel launches this call issued */
+} gsr_stats;
+typedef struct gsr_ext {
+  /* backward: touched_mask[i] = 1 is stored (device memory, touched_len == P bytes, zeroed by the caller) for every
+   * Gaussian i that received a contribution from the backward blend. All other Gaussians have exactly-zero
+   * parameter gradients, so an exchange over ranks or a sparse optimiser step can skip them. NULL disables. */
+  uint8_t* touched_mask;
+  int touched_len;        /* must equal params->P when touched_mask != NULL (a stale mask of another map size is refused) */
+  /* backward: a cudaEvent_t recorded on params->stream right after the backward blend, i.e. once the touched flags
+   * and the gradient rows of the blend are final and before the per-Gaussian backward runs: a second stream can wait
+   * on it and start the flag exchange while the per-Gaussian backward is still running. NULL disables. */
+  void* blend_done_event;
+  /* backward, camera-tracking mode: only the camera-pose gradient is wanted (gsr_backward_pose).
+   * The backward blend skips the F feature-channel reductions, the per-Gaussian backward writes NONE of the eleven
+   * per-Gaussian gradient tensors (their pointers may be NULL) and only reduces the 27 camera sums. */
+  int tracking;
+  /* backward, sparse outputs: only the rows of Gaussians the backward blend reached (touched_mask[i] == 1, which is
+   * then required) are written to the eleven gradient tensors; all other rows are LEFT UNTOUCHED instead of being
+   * zero-filled (at 1 M Gaussians that is 316 MB of zeros per call that no sparse consumer reads). Consumers:
+   * gsr_exchange_sum_rows_peers (flags != NULL) and gsr_adam_step (dense_rows != 0). */
+  int sparse_rows;
+  /* backward, sparse outputs only: rows whose touched_mask flag is ALREADY set on entry are added to instead of
+   * overwritten, and the per-Gaussian backward (not the blend) sets the flags. That is how the views of one mapping
+   * step accumulate into one set of gradient tensors: zero the mask at the start of the step, then run the views. */
+  int accumulate;
+  /* backward, sparse outputs: if != NULL (device int[P] / device int[1], *touched_count zeroed by the caller) the
+   * per-Gaussian backward appends the index of every Gaussian whose rows it wrote (order unspecified). */
+  int* touched_idx;
+  int* touched_count;
+  /* backward: caller-owned persistent accumulation workspace of gsr_row_workspace_bytes(P, F) bytes that replaces the
+   * gradient-row area of the geometry buffer. Contract: all-zero on entry, all-zero again when the call has completed
+   * (the per-Gaussian backward re-zeroes exactly the rows it consumed), so the 4*32 (F=16) / 4*64 (F=32) + 1
+   * bytes/Gaussian memset per backward call disappears. Zero it once after allocation. NULL = use the geometry buffer. */
+  char* row_workspace;
+  /* forward + backward: per-stage CUDA-event timing into this timer (gsr_timer_create); NULL = no events recorded */
+  gsr_timer* timer;
+  /* forward + backward: OUT statistics of this call; NULL = not wanted */
+  gsr_stats* stats;
+} gsr_ext;
+
 typedef struct gsr_params {
   int P;              /* number of Gaussians */
   int D;              /* active SH degree (0..3) */
@@ -47,6 +102,7 @@ typedef struct gsr_params {
   int prefiltered;    /* reference traps if a prefiltered Gaussian is culled (auxiliary.h:161-165); here: error flag */
   int debug;          /* !=0: synchronise + check after every stage (CHECK_CUDA, auxiliary.h:171-178) */
   void* stream;       /* cudaStream_t; NULL = legacy default stream like the reference */
+  gsr_ext* ext;       /* optional per-call extensions (above); NULL = reference behaviour */
 } gsr_params;
 
 /* Replaces CudaRasterizer::Rasterizer::forward (rasterizer.h:31-59, rasterizer_impl.cu:201-352).
@@ -125,32 +181,26 @@ size_t gsr_geom_bytes(int P);
 size_t gsr_image_bytes(int width, int height);
 size_t gsr_binning_bytes(int64_t num_rendered);
 
-/* Per-stage device timing for the roofline report (bench.py): when enabled, every forward /
- * backward call brackets each stage with CUDA events on params->stream. gsr_get_stage_times
- * synchronises those events, ADDS the elapsed milliseconds since the last call of
- * gsr_get_stage_times into ms[GSR_NUM_STAGES] (caller zero-initialises) and forgets them.
- * Stages: 0 preprocess (K1), 1 depth sort + coverage grids + tile offsets/ranges, 2 binning
- * (supertile lists + per-tile pull into the point list), 3 forward blend (K4), 4 backward blend
- * (K5), 5 backward preprocess (K6+K7). No reference
- * equivalent (the reference has no timers). */
+/* Per-stage device timing for the roofline report (bench.py): a forward / backward call that is handed a timer
+ * (gsr_ext::timer) brackets each of its stages with CUDA events on params->stream. gsr_timer_read synchronises those
+ * events, ADDS the elapsed milliseconds per stage into stage_ms[GSR_NUM_STAGES] and the stream time between the end
+ * of the previously recorded stage and the start of stage i (launch gaps, the num_rendered synchronisation, work of
+ * the caller between forward and backward) into gap_ms[GSR_NUM_STAGES] (either may be NULL; caller zero-initialises)
+ * and forgets the spans. A timer must not be used by two threads at once. Stages: 0 preprocess (K1), 1 depth sort +
+ * coverage grids + tile offsets/ranges, 2 binning (supertile lists), 3 forward blend (K4, incl. the per-tile list
+ * pull), 4 backward blend (K5), 5 backward preprocess (K6+K7). No reference equivalent (the reference has no timers,
+ * SURVEY.md section 5). With the environment variable GSR_NVTX set (or params->debug) every stage is additionally
+ * wrapped in an NVTX range "gsr:<stage>" for timeline tools. */
 #define GSR_NUM_STAGES 6
-int gsr_set_stage_timing(int enable);
-int gsr_get_stage_times(float* ms);
-/* Stream time between the end of the previously recorded stage and the start of stage i (launch gaps, the
- * num_rendered synchronisation, work of the caller between forward and backward), accumulated by the last
- * gsr_get_stage_times call; reading clears it. */
-int gsr_get_stage_gaps(float* ms);
+gsr_timer* gsr_timer_create(void);
+void gsr_timer_destroy(gsr_timer* t);
+int gsr_timer_read(gsr_timer* t, float* stage_ms, float* gap_ms);
 
-/* Sparse gradient exchange (extension for the view-data-parallel mapping step, no reference equivalent): while a
- * mask is set, every gsr_backward / gsr_backward_pose call of this thread stores 1 into mask[i] (device memory, P
- * bytes, zeroed by the caller) for every Gaussian i that received a contribution from the backward blend. All other
- * Gaussians have exactly-zero parameter gradients, so an exchange over ranks can skip them. NULL disables. */
-int gsr_set_touched_mask(uint8_t* mask);
-/* While an event (a cudaEvent_t) is set, every gsr_backward / gsr_backward_pose call of this thread records it on its
- * stream right after the backward blend, i.e. once the touched flags and the gradient rows of the blend are final and
- * before the per-Gaussian backward runs: a second stream can wait on it and start the flag exchange (all-gather + union
- * compaction) while the per-Gaussian backward is still running. NULL disables. */
-int gsr_set_blend_done_event(void* event);
+/* Bytes of the persistent backward accumulation workspace (gsr_ext::row_workspace). */
+size_t gsr_row_workspace_bytes(int P, int F);
+
+/* Sparse gradient exchange (extension for the view-data-parallel mapping step, no reference equivalent): the backward
+ * pass flags the Gaussians its blend reached (gsr_ext::touched_mask); ranks then exchange only those rows. */
 /* Union + compaction of the all-gathered flags: flags = nranks rows of Ppad bytes (Ppad >= P, multiple of 4, 4-byte
  * aligned). Writes the ascending indices of the Gaussians flagged by any rank to idx[0 : min(count, cap)] and the union
  * size to *count (device memory, stays on the device). Every rank computes the same list from the same gathered flags.
@@ -168,7 +218,9 @@ int gsr_exchange_rows(int scatter, int ntensors, const float* const* dense, floa
  * memory over NVLink): no collective library call on the data path.
  * gsr_exchange_compact_peers: as gsr_exchange_compact, but flags[r] (HOST array of nranks <= 16 device pointers, 4-byte
  * aligned, P bytes readable rounded up to 4) is rank r's own flag buffer read in place.
- * gsr_exchange_sum_rows_peers: compact[t][r][:] = sum over ranks q (ascending, so every rank gets bitwise the same sum)
+ * gsr_exchange_sum_rows_peers: compact[t][r][:] = sum over ranks q (ascending, so every rank gets bitwise the same sum;
+ * with flags != NULL only over the ranks q whose flags[q][idx[r]] is set: the buckets of a sparse-row backward,
+ * gsr_ext::sparse_rows, hold stale data in the rows their rank did not reach)
  * of buckets[q][tensor_offset[t] + idx[r] * floats_per_row[t] + :] for r < min(*count, cap) (rows beyond are left
  * untouched; with cap = P the list can never overflow and no host read-back of *count is needed); buckets =
  * HOST array of the nranks bucket base pointers as mapped in THIS process. The caller orders the calls between ranks:
@@ -176,9 +228,19 @@ int gsr_exchange_rows(int scatter, int ntensors, const float* const* dense, floa
  * overwrites its bucket or flags). */
 int gsr_exchange_compact_peers(const uint8_t* const* flags, int nranks, int P, int cap, int* idx, int* count, char* scratch,
                                void* stream);
-int gsr_exchange_sum_rows_peers(const float* const* buckets, int nranks, int ntensors, const long long* tensor_offset,
-                                float* const* compact, const int* floats_per_row, const int* idx, const int* count, int cap,
-                                void* stream);
+int gsr_exchange_sum_rows_peers(const float* const* buckets, const uint8_t* const* flags, int nranks, int ntensors,
+                                const long long* tensor_offset, float* const* compact, const int* floats_per_row,
+                                const int* idx, const int* count, int cap, void* stream);
+/* Cross-rank ready handshake over peer memory in ONE launch, replacing a pair of barriers: pads[r] (HOST array of the
+ * nranks ranks' signal pads as mapped in this process: nranks uint32 each, zero-initialised, 4-byte aligned) -- the
+ * kernel publishes `seq` in slot [rank] of every peer's pad (system-scope release: all earlier work of this stream is
+ * visible to a peer that observes it) and then waits until every slot of its own pad has reached `seq`. Sequence
+ * numbers only grow (use 1, 2, 3, ... per exchange), so nothing is ever reset. With flags and bucket double-buffered
+ * by the parity of seq, observing seq also proves that every peer has finished READING the buffers of seq - 1, which
+ * makes the trailing "everybody is done reading" barrier unnecessary. A peer that does not arrive within timeout_ms
+ * ends the wait and stores 1 + its rank into *status (device int, zeroed by the caller) instead of hanging the GPU. */
+int gsr_exchange_signal_wait(void* const* pads, int nranks, int rank, unsigned int seq, int timeout_ms, int* status,
+                             void* stream);
 
 /* ---- activation + Adam fused around the rasterizer ---------------------------------------------------
  * Replaces, for the seven parameter groups of the reference's GaussianModel (scene/gaussian_model.py:247-257:
@@ -254,6 +316,12 @@ int gsr_activate(const gsr_adam_tensors* t, int P, int M, void* stream);
  * gsr_exchange_rows + all-reduce); the moments of all other Gaussians are left alone (torch.optim.SparseAdam). */
 int gsr_adam_step(const gsr_adam_tensors* t, int P, int M, int F, const float* lr, float beta1, float beta2, float eps,
                   int step, const int* idx, const int* count, int cap, void* stream);
+/* The same with flags. GSR_ADAM_DENSE_GRAD_ROWS (sparse mode only): the g_* tensors are the P-row outputs of a
+ * sparse-row backward (gsr_ext::sparse_rows), i.e. Gaussian idx[r] takes ITS OWN row idx[r] of them instead of row r
+ * (idx / count = gsr_ext::touched_idx / touched_count of that backward, or the list of gsr_exchange_compact). */
+#define GSR_ADAM_DENSE_GRAD_ROWS 1
+int gsr_adam_step_ex(const gsr_adam_tensors* t, int P, int M, int F, const float* lr, float beta1, float beta2, float eps,
+                     int step, const int* idx, const int* count, int cap, int flags, void* stream);
 
 /* Work counters of a finished forward pass, for the FP32 roofline of the blend kernels
  * (SURVEY.md 8d "N_eval / N_contrib"): replays the blend tests (no blending) and returns on the

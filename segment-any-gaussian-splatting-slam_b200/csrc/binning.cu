@@ -311,11 +311,8 @@ void launch_offsets(int P, const Cam& cam, GeomState& g, ImageState& img, cudaSt
   {
     const size_t smem = sat_ints(cam.gx, cam.gy) * sizeof(int);
     const int use_smem = smem <= 160 * 1024;
-    static bool attr_set = false;  // idempotent; a benign race at worst sets it twice
-    if (!attr_set) {
-      cudaFuncSetAttribute(coverage_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
-      attr_set = true;
-    }
+    static std::atomic<unsigned long long> attr_done{0};  // per-device bitmap, see ensure_dyn_smem
+    ensure_dyn_smem(coverage_kernel, 160 * 1024, attr_done);
     int nb = (P + 255) / 256;
     if (use_smem && nb > 296) nb = 296;
     coverage_kernel<<<nb, 256, use_smem ? smem : 0, s>>>(P, cam.gx, cam.gy, sg, use_smem, g.tiles_touched, g.rect,
@@ -325,11 +322,8 @@ void launch_offsets(int P, const Cam& cam, GeomState& g, ImageState& img, cudaSt
   {
     const size_t smem = sat_ints(cam.gx, cam.gy) * sizeof(int);
     const int use_smem = smem <= 160 * 1024;
-    static bool attr_set = false;
-    if (!attr_set) {
-      cudaFuncSetAttribute(offsets_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
-      attr_set = true;
-    }
+    static std::atomic<unsigned long long> attr_done{0};
+    ensure_dyn_smem(offsets_kernel, 160 * 1024, attr_done);
     offsets_kernel<<<1, 1024, use_smem ? smem : 0, s>>>(cam.gx, cam.gy, sg, use_smem, img.sat, img.ssat, img.ranges,
                                                         img.tile_off, img.l1_off, g.flags);
   }

@@ -7,8 +7,11 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <new>
 #include <string>
 #include <vector>
+
+#include <nvtx3/nvToolsExt.h>
 
 #include "../../include/gsraster_b200.h"
 #include "common.cuh"
@@ -25,15 +28,18 @@ bool launch_feature_loss(const float* obj, const long long* gt, int HW, int F, i
 void launch_photometric_loss(const float* img, const float* gt, int H, int W, float lambda, float* dL_dimg, float* out3,
                              char* scratch, cudaStream_t s);
 void launch_adam(const gsr_adam_tensors& t, int P, int M, int F, const float* lr, float beta1, float beta2, float eps,
-                 int step, const int* idx, const int* count, int cap, cudaStream_t s);
+                 int step, const int* idx, const int* count, int cap, int flags, cudaStream_t s);
 void launch_activate(const gsr_adam_tensors& t, int P, int M, cudaStream_t s);
 size_t exchange_scratch_bytes(int P);
 void launch_union_compact(const uint8_t* flags, int nranks, int P, int Ppad, int cap, int* idx, int* count, char* scratch,
                           cudaStream_t s);
 void launch_union_compact_peers(const uint8_t* const* flags, int nranks, int P, int cap, int* idx, int* count, char* scratch,
                                 cudaStream_t s);
-void launch_sum_rows_peers(const float* const* buckets, int nranks, int ntensors, const long long* off, float* const* dst,
-                           const int* n, const int* idx, const int* count, int cap, cudaStream_t s);
+void launch_sum_rows_peers(const float* const* buckets, const uint8_t* const* flags, int nranks, int ntensors,
+                           const long long* off, float* const* dst, const int* n, const int* idx, const int* count, int cap,
+                           cudaStream_t s);
+void launch_signal_wait(void* const* pads, int nranks, int rank, uint32_t seq, unsigned long long timeout_ns, int* status,
+                        cudaStream_t s);
 void launch_prune_flags(const float* opacity, const float* scaling, int P, float min_opacity, float max_scale,
                         uint8_t* keep, cudaStream_t s);
 void launch_rows(int scatter, int ntensors, const float* const* src, float* const* dst, const int* n, const int* idx,
@@ -43,6 +49,7 @@ void launch_export_keys(int T, const uint2* ranges, const uint32_t* point_list, 
 }
 
 namespace {
+// Thread-local OUTPUT records of the calling thread's last call (never read back as an input by any entry point).
 thread_local std::string g_err;
 thread_local int g_launches = 0;
 thread_local unsigned long long g_last_stats[6] = {0, 0, 0, 0, 0, 0};
@@ -50,35 +57,64 @@ inline unsigned long long now_us() {
   return (unsigned long long)std::chrono::duration_cast<std::chrono::microseconds>(
              std::chrono::steady_clock::now().time_since_epoch()).count();
 }
-thread_local int* g_pinned = nullptr;  // 8 ints of pinned host memory for the num_rendered read-back
-
-// ---- optional per-stage event timing (gsr_set_stage_timing) ----
-struct StageSpan { int stage; cudaEvent_t a, b; };
-thread_local bool g_timing = false;
-thread_local uint8_t* g_touched = nullptr;  // gsr_set_touched_mask
-thread_local cudaEvent_t g_ev_R = nullptr;  // num_rendered read-back
-// side stream of this thread for the depth sort (created on first use, lives with the thread)
-thread_local cudaStream_t g_side = nullptr;
-thread_local cudaEvent_t g_fork = nullptr, g_join = nullptr;
-thread_local int g_side_dev = -1;
+// Helper resources of one (host thread, device) pair, created on first use and kept for the life of the thread:
+// pinned memory + event for the num_rendered read-back, the side stream of the depth sort with its fork / join events.
+// Events and streams belong to the device that was current when they were created, so they are keyed by it.
+struct DevCtx {
+  bool ready = false;
+  int* pinned = nullptr;
+  cudaEvent_t ev_R = nullptr, fork = nullptr, join = nullptr;
+  cudaStream_t side = nullptr;
+};
+constexpr int MAX_DEVICES = 64;
+thread_local DevCtx g_dev[MAX_DEVICES];
 const bool g_no_side_sort = getenv("GSR_NO_SIDE_SORT") != nullptr;  // diagnostics: everything on the caller's stream
-thread_local cudaEvent_t g_blend_done = nullptr;  // gsr_set_blend_done_event
-thread_local std::vector<StageSpan> g_spans;
-thread_local std::vector<cudaEvent_t> g_free_events;
-thread_local float g_gaps[GSR_NUM_STAGES] = {0, 0, 0, 0, 0, 0};  // idle time on the stream before each stage
-cudaEvent_t take_event() {
-  cudaEvent_t e;
-  if (!g_free_events.empty()) { e = g_free_events.back(); g_free_events.pop_back(); return e; }
-  cudaEventCreate(&e);
-  return e;
+const bool g_nvtx = getenv("GSR_NVTX") != nullptr;                  // NVTX range per stage (timeline tools)
+cudaError_t dev_ctx(DevCtx** out) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= MAX_DEVICES) return cudaErrorInvalidDevice;
+  DevCtx& c = g_dev[dev];
+  if (!c.ready) {
+    if ((e = cudaHostAlloc(&c.pinned, 8 * sizeof(int), cudaHostAllocPortable)) != cudaSuccess) return e;
+    if ((e = cudaEventCreateWithFlags(&c.ev_R, cudaEventDisableTiming)) != cudaSuccess) return e;
+    if ((e = cudaEventCreateWithFlags(&c.fork, cudaEventDisableTiming)) != cudaSuccess) return e;
+    if ((e = cudaEventCreateWithFlags(&c.join, cudaEventDisableTiming)) != cudaSuccess) return e;
+    if ((e = cudaStreamCreateWithFlags(&c.side, cudaStreamNonBlocking)) != cudaSuccess) return e;
+    c.ready = true;
+  }
+  *out = &c;
+  return cudaSuccess;
 }
+}  // namespace
+
+// ---- optional per-stage event timing (gsr_ext::timer) ----
+struct gsr_timer {
+  struct Span { int stage; cudaEvent_t a, b; };
+  std::vector<Span> spans;
+  std::vector<cudaEvent_t> free_events;
+  cudaEvent_t take() {
+    cudaEvent_t e;
+    if (!free_events.empty()) { e = free_events.back(); free_events.pop_back(); return e; }
+    cudaEventCreate(&e);
+    return e;
+  }
+};
+
+namespace {
+const char* const STAGE_NAMES[GSR_NUM_STAGES] = {"gsr:preprocess", "gsr:depth_sort_offsets", "gsr:binning", "gsr:render_fwd",
+                                                 "gsr:render_bwd", "gsr:preprocess_bwd"};
 struct StageTimer {
-  bool on; int stage; cudaStream_t s; cudaEvent_t a;
-  StageTimer(int stage_, cudaStream_t s_) : on(g_timing), stage(stage_), s(s_), a(nullptr) {
-    if (on) { a = take_event(); cudaEventRecord(a, s); }
+  gsr_timer* t; int stage; cudaStream_t s; cudaEvent_t a; bool nvtx;
+  StageTimer(const gsr_params* p, int stage_, cudaStream_t s_)
+      : t(p->ext ? p->ext->timer : nullptr), stage(stage_), s(s_), a(nullptr), nvtx(g_nvtx || p->debug) {
+    if (nvtx) nvtxRangePushA(STAGE_NAMES[stage]);
+    if (t) { a = t->take(); cudaEventRecord(a, s); }
   }
   ~StageTimer() {
-    if (on) { cudaEvent_t b = take_event(); cudaEventRecord(b, s); g_spans.push_back({stage, a, b}); }
+    if (t) { cudaEvent_t b = t->take(); cudaEventRecord(b, s); t->spans.push_back({stage, a, b}); }
+    if (nvtx) nvtxRangePop();
   }
 };
 
@@ -197,7 +233,7 @@ int gsr_forward(const gsr_params* p, gsr_alloc_fn geom_alloc, void* geom_ctx, gs
   CUDA_TRY(cudaMemsetAsync(img.sat, 0, gsr::sat_ints(cam.gx, cam.gy) * sizeof(int), stream));
   const gsr::FwdInputs in = make_inputs(p, means3D, shs, colors_precomp, opacities, scales, rotations, cov3D_precomp);
   {
-    StageTimer tm(0, stream);
+    StageTimer tm(p, 0, stream);
     gsr::launch_preprocess(in, cam, g, img, radii, is_used, stream);
   }
   g_launches += 1;
@@ -205,41 +241,34 @@ int gsr_forward(const gsr_params* p, gsr_alloc_fn geom_alloc, void* geom_ctx, gs
   // The one data-dependent host sync of the path (reference: rasterizer_impl.cu:289-290). num_rendered comes out of the
   // coverage grids, not out of the sort: offsets first, their read-back queued, then the depth sort -- the host waits
   // for the read-back event only and sizes / allocates / enqueues the next stages while the sort is still running.
-  if (!g_pinned) CUDA_TRY(cudaHostAlloc(&g_pinned, 8 * sizeof(int), cudaHostAllocDefault));
-  if (!g_ev_R) CUDA_TRY(cudaEventCreateWithFlags(&g_ev_R, cudaEventDisableTiming));
+  DevCtx* dc = nullptr;  // helper resources of this (host thread, device)
+  CUDA_TRY(dev_ctx(&dc));
   unsigned long long t_enq;
   {
-    StageTimer tm(1, stream);
+    StageTimer tm(p, 1, stream);
     // The depth sort (twelve small latency-bound launches) and the coverage / offsets kernels only share their input
     // (the preprocess outputs): the sort runs on this thread's side stream beside them and joins before binning.
-    cudaStream_t sort_stream = stream;
-    if (!g_no_side_sort) {
-      int dev = 0;
-      CUDA_TRY(cudaGetDevice(&dev));
-      if (!g_side || g_side_dev != dev) {  // one side stream per (thread, device)
-        g_side_dev = dev;
-        CUDA_TRY(cudaStreamCreateWithFlags(&g_side, cudaStreamNonBlocking));
-        CUDA_TRY(cudaEventCreateWithFlags(&g_fork, cudaEventDisableTiming));
-        CUDA_TRY(cudaEventCreateWithFlags(&g_join, cudaEventDisableTiming));
-      }
-      CUDA_TRY(cudaEventRecord(g_fork, stream));
-      CUDA_TRY(cudaStreamWaitEvent(g_side, g_fork, 0));
-      sort_stream = g_side;
+    cudaStream_t sort_stream = g_no_side_sort ? stream : dc->side;
+    if (sort_stream != stream) {
+      CUDA_TRY(cudaEventRecord(dc->fork, stream));
+      CUDA_TRY(cudaStreamWaitEvent(dc->side, dc->fork, 0));
     }
     gsr::launch_depth_sort(P, g, sort_stream, g_launches);
-    if (sort_stream != stream) CUDA_TRY(cudaEventRecord(g_join, g_side));
+    if (sort_stream != stream) CUDA_TRY(cudaEventRecord(dc->join, dc->side));
     gsr::launch_offsets(P, cam, g, img, stream, g_launches);
     t_enq = now_us();
-    CUDA_TRY(cudaMemcpyAsync(g_pinned, g.flags, 4 * sizeof(int), cudaMemcpyDeviceToHost, stream));
-    CUDA_TRY(cudaEventRecord(g_ev_R, stream));
-    if (sort_stream != stream) CUDA_TRY(cudaStreamWaitEvent(stream, g_join, 0));
+    CUDA_TRY(cudaMemcpyAsync(dc->pinned, g.flags, 4 * sizeof(int), cudaMemcpyDeviceToHost, stream));
+    CUDA_TRY(cudaEventRecord(dc->ev_R, stream));
+    if (sort_stream != stream) CUDA_TRY(cudaStreamWaitEvent(stream, dc->join, 0));
   }
   STAGE_CHECK("depth_sort");
-  CUDA_TRY(cudaEventSynchronize(g_ev_R));
+  CUDA_TRY(cudaEventSynchronize(dc->ev_R));
   const unsigned long long t_sync = now_us();
-  const int64_t R = (int64_t)(uint32_t)g_pinned[0];
-  const uint64_t l1_total = (uint64_t)(uint32_t)g_pinned[2] | ((uint64_t)(uint32_t)g_pinned[3] << 32);
-  if (g_pinned[1]) return fail(GSR_ERR_INVALID_ARGUMENT, "Point is filtered although prefiltered is set");
+  const int* const rb = dc->pinned;
+  // the offsets kernel stores -1 when the sum of the tile-list lengths passes int32 (reference: :289 reads into an int)
+  const int64_t R = rb[0] < 0 ? (int64_t)0x80000000LL : (int64_t)rb[0];
+  const uint64_t l1_total = (uint64_t)(uint32_t)rb[2] | ((uint64_t)(uint32_t)rb[3] << 32);
+  if (rb[1]) return fail(GSR_ERR_INVALID_ARGUMENT, "Point is filtered although prefiltered is set");
   if (R > 0x7fffffffLL) return fail(GSR_ERR_UNSUPPORTED, "num_rendered exceeds int32");
   if (l1_total > 0xffffffffull) return fail(GSR_ERR_UNSUPPORTED, "supertile list length exceeds uint32");
   if (num_rendered) *num_rendered = (int)R;
@@ -253,12 +282,12 @@ int gsr_forward(const gsr_params* p, gsr_alloc_fn geom_alloc, void* geom_ctx, gs
   gsr::bin_from_chunk(bin_chunk, (size_t)R, (size_t)l1_total, nw_ns, b);
   const unsigned long long t_alloc = now_us();
   {
-    StageTimer tm(2, stream);
+    StageTimer tm(p, 2, stream);
     gsr::launch_binning(P, R, cam, g, b, img, stream, g_launches);
   }
   STAGE_CHECK("binning");
   {
-    StageTimer tm(3, stream);
+    StageTimer tm(p, 3, stream);
     gsr::launch_render_forward(p->F, cam, g, b, img, sh_objs, out_depth, out_color, out_objects, stream);
   }
   g_launches += 1;
@@ -266,6 +295,11 @@ int gsr_forward(const gsr_params* p, gsr_alloc_fn geom_alloc, void* geom_ctx, gs
   g_last_stats[2] = t_sync - t_enq;           // host us blocked in the num_rendered synchronisation
   g_last_stats[3] = t_alloc - t_sync;         // host us in the binning allocator callback
   g_last_stats[4] = now_us() - t_alloc;       // host us launching binning + forward blend
+  if (p->ext && p->ext->stats) {
+    gsr_stats* st = p->ext->stats;
+    st->num_rendered = g_last_stats[0]; st->l1_total = g_last_stats[1]; st->sync_us = g_last_stats[2];
+    st->alloc_us = g_last_stats[3]; st->launch_us = g_last_stats[4]; st->launches = g_launches;
+  }
   return GSR_OK;
 }
 
@@ -285,12 +319,29 @@ static int backward_impl(const gsr_params* p, int num_rendered, const float* bac
   if (p->P == 0) return GSR_OK;
   if (!geom_buffer || !binning_buffer || !image_buffer) return fail(GSR_ERR_INVALID_ARGUMENT, "scratch buffer is NULL");
   if (!dL_dpix_depth || !dL_dpix || !dL_dpix_obj) return fail(GSR_ERR_INVALID_ARGUMENT, "upstream gradient is NULL");
-  if (!dL_dmean2D || !dL_dconic || !dL_dopacity || !dL_ddepths || !dL_dcolor || !dL_dobjects || !dL_dmean3D ||
-      !dL_dcov3D)
-    return fail(GSR_ERR_INVALID_ARGUMENT, "gradient output is NULL");
-  if (shs && !dL_dsh) return fail(GSR_ERR_INVALID_ARGUMENT, "dL_dsh is NULL although shs given");
-  if (((uintptr_t)dL_dobjects & 15) || (dL_drot && ((uintptr_t)dL_drot & 15)))
-    return fail(GSR_ERR_INVALID_ARGUMENT, "dL_dobjects / dL_drot must be 16-byte aligned");
+  const gsr_ext* x = p->ext;
+  const bool tracking = x && x->tracking;
+  if (tracking && !dL_dviewmatrix)
+    return fail(GSR_ERR_INVALID_ARGUMENT, "tracking mode computes only the camera gradients: call gsr_backward_pose");
+  if (!tracking) {
+    if (!dL_dmean2D || !dL_dconic || !dL_dopacity || !dL_ddepths || !dL_dcolor || !dL_dobjects || !dL_dmean3D ||
+        !dL_dcov3D)
+      return fail(GSR_ERR_INVALID_ARGUMENT, "gradient output is NULL");
+    if (shs && !dL_dsh) return fail(GSR_ERR_INVALID_ARGUMENT, "dL_dsh is NULL although shs given");
+    if (((uintptr_t)dL_dobjects & 15) || (dL_drot && ((uintptr_t)dL_drot & 15)))
+      return fail(GSR_ERR_INVALID_ARGUMENT, "dL_dobjects / dL_drot must be 16-byte aligned");
+  }
+  if (x && x->touched_mask && x->touched_len != p->P)
+    return fail(GSR_ERR_INVALID_ARGUMENT, "touched_mask holds %d flags but P = %d (stale mask of another map size?)",
+                x->touched_len, p->P);
+  if (x && x->sparse_rows && !tracking && !x->touched_mask)
+    return fail(GSR_ERR_INVALID_ARGUMENT, "sparse_rows needs touched_mask: it is what tells the consumer which rows are valid");
+  if (x && x->accumulate && !(x->sparse_rows && x->touched_mask))
+    return fail(GSR_ERR_INVALID_ARGUMENT, "accumulate is defined for sparse_rows with a touched_mask only");
+  if (x && (x->touched_idx != nullptr) != (x->touched_count != nullptr))
+    return fail(GSR_ERR_INVALID_ARGUMENT, "touched_idx and touched_count go together");
+  if (x && x->row_workspace && ((uintptr_t)x->row_workspace & 15))
+    return fail(GSR_ERR_INVALID_ARGUMENT, "row_workspace must be 16-byte aligned");
   cudaStream_t stream = (cudaStream_t)p->stream;
   const int P = p->P;
   const gsr::Cam cam = make_cam(p, viewmatrix, projmatrix, cam_pos, background);
@@ -303,26 +354,43 @@ static int backward_impl(const gsr_params* p, int num_rendered, const float* bac
   gsr::bin_from_chunk(binning_buffer, (size_t)(num_rendered > 0 ? num_rendered : 0), 0, 0, b);
   if (!radii) radii = g.radii_internal;
 
+  gsr::BwdOpts opt{};
+  opt.rows = g.grad_rows;
+  opt.touched = g.touched;
+  if (x && x->row_workspace) {  // caller-owned persistent workspace, clean on entry and on exit: no memset
+    opt.rows = reinterpret_cast<float*>(x->row_workspace);
+    opt.touched = reinterpret_cast<uint8_t*>(opt.rows + (size_t)P * gsr::grad_row_floats(p->F));
+    opt.clean_rows = true;
+  }
+  opt.touched_ext = x ? x->touched_mask : nullptr;
+  opt.tracking = tracking;
+  opt.sparse_rows = x && x->sparse_rows && !tracking;
+  opt.accumulate = x && x->accumulate;
+  opt.touched_idx = x ? x->touched_idx : nullptr;
+  opt.touched_count = x ? x->touched_count : nullptr;
   {
-    StageTimer tm(4, stream);
-    CUDA_TRY(cudaMemsetAsync(g.grad_rows, 0, (size_t)P * gsr::grad_row_floats(p->F) * sizeof(float) + (size_t)P, stream));  // rows + touched flags
+    StageTimer tm(p, 4, stream);
+    if (!opt.clean_rows)  // rows + internal touched flags
+      CUDA_TRY(cudaMemsetAsync(opt.rows, 0, (size_t)P * gsr::grad_row_floats(p->F) * sizeof(float) + (size_t)P, stream));
     if (num_rendered > 0) {
-      gsr::launch_render_backward(p->F, cam, g, b, img, sh_objs, dL_dpix_depth, dL_dpix, dL_dpix_obj, g_touched, stream);
+      gsr::launch_render_backward(p->F, cam, g, b, img, sh_objs, dL_dpix_depth, dL_dpix, dL_dpix_obj, opt, stream);
       g_launches += 1;
     }
   }
-  if (g_blend_done) CUDA_TRY(cudaEventRecord(g_blend_done, stream));  // the touched flags are final from here on
+  if (x && x->blend_done_event)  // the touched flags and the gradient rows of the blend are final from here on
+    CUDA_TRY(cudaEventRecord((cudaEvent_t)x->blend_done_event, stream));
   STAGE_CHECK("render_backward");
   const gsr::FwdInputs in = make_inputs(p, means3D, shs, colors_precomp, nullptr, scales, rotations, cov3D_precomp);
   gsr::BwdOutputs out{dL_dmean2D, dL_dconic, dL_dopacity, dL_ddepths, dL_dcolor, dL_dobjects,
                       dL_dmean3D, dL_dcov3D, dL_dsh,      dL_dscale,  dL_drot,
                       dL_dviewmatrix, dL_dprojmatrix, dL_dcampos};
   {
-    StageTimer tm(5, stream);
-    gsr::launch_preprocess_backward(in, cam, g, radii, out, stream);
+    StageTimer tm(p, 5, stream);
+    gsr::launch_preprocess_backward(in, cam, g, radii, out, opt, stream);
   }
   g_launches += dL_dviewmatrix ? 2 : 1;
   STAGE_CHECK("preprocess_backward");
+  if (x && x->stats) x->stats->launches = g_launches;
   return GSR_OK;
 }
 
@@ -363,37 +431,31 @@ int gsr_last_forward_stats(unsigned long long* out) {
   for (int i = 0; i < 6; i++) out[i] = g_last_stats[i];
   return GSR_OK;
 }
-int gsr_set_stage_timing(int enable) {
-  g_timing = enable != 0;
-  return GSR_OK;
+gsr_timer* gsr_timer_create(void) { return new (std::nothrow) gsr_timer(); }
+void gsr_timer_destroy(gsr_timer* t) {
+  if (!t) return;
+  for (const gsr_timer::Span& sp : t->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
+  for (cudaEvent_t e : t->free_events) cudaEventDestroy(e);
+  delete t;
 }
-int gsr_get_stage_times(float* ms) {
-  if (!ms) return fail(GSR_ERR_INVALID_ARGUMENT, "ms is NULL");
-  const StageSpan* prev = nullptr;
-  for (const StageSpan& sp : g_spans) {
+int gsr_timer_read(gsr_timer* t, float* stage_ms, float* gap_ms) {
+  if (!t) return fail(GSR_ERR_INVALID_ARGUMENT, "timer is NULL");
+  const gsr_timer::Span* prev = nullptr;
+  for (const gsr_timer::Span& sp : t->spans) {
     CUDA_TRY(cudaEventSynchronize(sp.b));
-    float t = 0.f;
-    CUDA_TRY(cudaEventElapsedTime(&t, sp.a, sp.b));
-    if (sp.stage >= 0 && sp.stage < GSR_NUM_STAGES) ms[sp.stage] += t;
-    if (prev && sp.stage >= 0 && sp.stage < GSR_NUM_STAGES && cudaEventElapsedTime(&t, prev->b, sp.a) == cudaSuccess)
-      g_gaps[sp.stage] += t;
+    float ms = 0.f;
+    CUDA_TRY(cudaEventElapsedTime(&ms, sp.a, sp.b));
+    const bool ok = sp.stage >= 0 && sp.stage < GSR_NUM_STAGES;
+    if (ok && stage_ms) stage_ms[sp.stage] += ms;
+    if (prev && ok && gap_ms && cudaEventElapsedTime(&ms, prev->b, sp.a) == cudaSuccess) gap_ms[sp.stage] += ms;
     prev = &sp;
-    g_free_events.push_back(sp.a);
-    g_free_events.push_back(sp.b);
   }
-  g_spans.clear();
+  for (const gsr_timer::Span& sp : t->spans) { t->free_events.push_back(sp.a); t->free_events.push_back(sp.b); }
+  t->spans.clear();
   return GSR_OK;
 }
 
-int gsr_set_touched_mask(uint8_t* mask) {
-  g_touched = mask;
-  return GSR_OK;
-}
-
-int gsr_set_blend_done_event(void* event) {
-  g_blend_done = (cudaEvent_t)event;
-  return GSR_OK;
-}
+size_t gsr_row_workspace_bytes(int P, int F) { return gsr::row_workspace_bytes((size_t)(P > 0 ? P : 1), F); }
 
 size_t gsr_exchange_scratch_bytes(int P) { return gsr::exchange_scratch_bytes(P > 0 ? P : 1); }
 
@@ -437,13 +499,25 @@ int gsr_exchange_compact_peers(const uint8_t* const* flags, int nranks, int P, i
   return GSR_OK;
 }
 
-int gsr_exchange_sum_rows_peers(const float* const* buckets, int nranks, int ntensors, const long long* tensor_offset,
-                                float* const* compact, const int* floats_per_row, const int* idx, const int* count, int cap,
-                                void* stream_) {
+int gsr_exchange_signal_wait(void* const* pads, int nranks, int rank, unsigned int seq, int timeout_ms, int* status,
+                             void* stream_) {
+  if (!pads || nranks <= 0 || nranks > 16 || rank < 0 || rank >= nranks || !status || timeout_ms <= 0)
+    return fail(GSR_ERR_INVALID_ARGUMENT, "exchange_signal_wait: bad argument");
+  for (int r = 0; r < nranks; r++)
+    if (!pads[r] || ((uintptr_t)pads[r] & 3)) return fail(GSR_ERR_INVALID_ARGUMENT, "exchange_signal_wait: bad pad pointer");
+  gsr::launch_signal_wait(pads, nranks, rank, seq, (unsigned long long)timeout_ms * 1000000ull, status, (cudaStream_t)stream_);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "exchange_signal_wait: %s", cudaGetErrorString(e));
+  return GSR_OK;
+}
+
+int gsr_exchange_sum_rows_peers(const float* const* buckets, const uint8_t* const* flags, int nranks, int ntensors,
+                                const long long* tensor_offset, float* const* compact, const int* floats_per_row,
+                                const int* idx, const int* count, int cap, void* stream_) {
   if (!buckets || nranks <= 0 || nranks > 16 || ntensors <= 0 || ntensors > 8 || !tensor_offset || !compact ||
       !floats_per_row || !idx || !count || cap < 0)
     return fail(GSR_ERR_INVALID_ARGUMENT, "exchange_sum_rows_peers: bad argument");
-  gsr::launch_sum_rows_peers(buckets, nranks, ntensors, tensor_offset, compact, floats_per_row, idx, count, cap,
+  gsr::launch_sum_rows_peers(buckets, flags, nranks, ntensors, tensor_offset, compact, floats_per_row, idx, count, cap,
                              (cudaStream_t)stream_);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "exchange_sum_rows_peers: %s", cudaGetErrorString(e));
@@ -516,21 +590,22 @@ int gsr_activate(const gsr_adam_tensors* t, int P, int M, void* stream_) {
 
 int gsr_adam_step(const gsr_adam_tensors* t, int P, int M, int F, const float* lr, float beta1, float beta2, float eps,
                   int step, const int* idx, const int* count, int cap, void* stream_) {
+  return gsr_adam_step_ex(t, P, M, F, lr, beta1, beta2, eps, step, idx, count, cap, 0, stream_);
+}
+
+int gsr_adam_step_ex(const gsr_adam_tensors* t, int P, int M, int F, const float* lr, float beta1, float beta2, float eps,
+                     int step, const int* idx, const int* count, int cap, int flags, void* stream_) {
+  if ((flags & GSR_ADAM_DENSE_GRAD_ROWS) && !idx)
+    return fail(GSR_ERR_INVALID_ARGUMENT, "adam_step: GSR_ADAM_DENSE_GRAD_ROWS is a sparse-mode flag (idx is NULL)");
   if (!t || !lr || P < 0 || M < 1 || M > 16 || F < 1 || step < 1 || (idx && (!count || cap < 0)))
     return fail(GSR_ERR_INVALID_ARGUMENT, "adam_step: bad argument");
   const float* const* q = reinterpret_cast<const float* const*>(t);
   for (int i = 0; i < (int)(sizeof(gsr_adam_tensors) / sizeof(float*)); i++)
     if (!q[i] && !(M == 1 && (i == 2 || i == 9 || i == 16)))  // f_rest and its moments are empty at SH degree 0
       return fail(GSR_ERR_INVALID_ARGUMENT, "adam_step: NULL tensor (field %d)", i);
-  gsr::launch_adam(*t, P, M, F, lr, beta1, beta2, eps, step, idx, count, cap, (cudaStream_t)stream_);
+  gsr::launch_adam(*t, P, M, F, lr, beta1, beta2, eps, step, idx, count, cap, flags, (cudaStream_t)stream_);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "adam_step: %s", cudaGetErrorString(e));
-  return GSR_OK;
-}
-
-int gsr_get_stage_gaps(float* ms) {
-  if (!ms) return fail(GSR_ERR_INVALID_ARGUMENT, "ms is NULL");
-  for (int i = 0; i < GSR_NUM_STAGES; i++) { ms[i] = g_gaps[i]; g_gaps[i] = 0.f; }
   return GSR_OK;
 }
 

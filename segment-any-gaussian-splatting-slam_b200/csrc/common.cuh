@@ -1,10 +1,24 @@
 // Shared definitions for the sm_100a rasterizer kernels (internal; the public surface is
 // include/gsraster_b200.h).
 #pragma once
+#include <atomic>
 #include <cstdint>
 #include <cuda_runtime.h>
 
 namespace gsr {
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is a PER-DEVICE setting: `done` (one static per call site) is a
+// bitmap over device ordinals, so every device a process uses opts in exactly once, from whichever host thread gets
+// there first (setting it twice is harmless).
+template <typename K>
+inline void ensure_dyn_smem(K kernel, int bytes, std::atomic<unsigned long long>& done) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const unsigned long long bit = dev >= 0 && dev < 64 ? 1ull << dev : 0ull;
+  if (bit && (done.load(std::memory_order_acquire) & bit)) return;
+  cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (bit) done.fetch_or(bit, std::memory_order_release);
+}
 
 constexpr int TILE_X = 16, TILE_Y = 16;  // fixed by parity: reference config.h:17-18
 
@@ -85,13 +99,15 @@ __host__ __device__ inline SuperGrid super_grid(int gx, int gy) {
 // is point (x, y) (packed x | y<<8 | x<<16 | y<<24) inside the packed rect? bytes 0,1: lo <= p ; bytes 2,3: !(hi <= p)
 __device__ __forceinline__ bool rect_has(uint32_t rc, uint32_t pxy) { return __vcmpleu4(rc, pxy) == 0x0000FFFFu; }
 
+inline int grad_row_floats(int F) { return F <= 16 ? 32 : 64; }
 template <typename T>
 inline void carve(char*& p, T*& out, size_t count) {
   p = reinterpret_cast<char*>(align_up(reinterpret_cast<size_t>(p), 256));
   out = reinterpret_cast<T*>(p);
   p += count * sizeof(T);
 }
-inline int grad_row_floats(int F) { return F <= 16 ? 32 : 64; }
+// persistent backward workspace (gsr_ext::row_workspace): rows + internal touched flags
+inline size_t row_workspace_bytes(size_t P, int F) { return P * (size_t)grad_row_floats(F) * sizeof(float) + align_up(P, 256); }
 
 inline size_t geom_from_chunk(char* chunk, size_t P, GeomState& g, int F = 32) {
   char* p = chunk;
@@ -188,9 +204,21 @@ void launch_tile_pull(const Cam& cam, const BinState& b, const ImageState& img, 
 void launch_render_forward(int F, const Cam& cam, const GeomState& g, const BinState& b,
                            ImageState& img, const float* sh_objs, float* out_depth, float* out_color,
                            float* out_objects, cudaStream_t s);
+// Per-call options of the backward pass (gsr_ext, include/gsraster_b200.h) as the kernels see them.
+struct BwdOpts {
+  float* rows;           // gradient-row accumulation area: the geometry buffer's, or the caller's persistent workspace
+  uint8_t* touched;      // internal per-call flags, P bytes directly behind the rows
+  uint8_t* touched_ext;  // gsr_ext::touched_mask (NULL = none)
+  bool clean_rows;       // persistent workspace: K7 re-zeroes the rows and flags it consumed
+  bool tracking;         // K5 skips the feature-channel reductions, K7 writes no per-Gaussian tensor
+  bool sparse_rows;      // K7 writes only the rows the blend reached
+  bool accumulate;       // sparse rows: rows whose touched_ext flag is already set are added to
+  int* touched_idx;      // sparse rows: list of the Gaussians written (first touch), may be NULL
+  int* touched_count;
+};
 void launch_render_backward(int F, const Cam& cam, const GeomState& g, const BinState& b,
                             const ImageState& img, const float* sh_objs, const float* dL_dpix_depth,
-                            const float* dL_dpix, const float* dL_dpix_obj, uint8_t* touched, cudaStream_t s);
+                            const float* dL_dpix, const float* dL_dpix_obj, const BwdOpts& opt, cudaStream_t s);
 void launch_count_pairs(const Cam& cam, const GeomState& g, const BinState& b, const ImageState& img,
                         unsigned long long* counts, cudaStream_t s);
 struct BwdOutputs {
@@ -200,7 +228,7 @@ struct BwdOutputs {
   float* dL_dviewmatrix; float* dL_dprojmatrix; float* dL_dcampos;
 };
 void launch_preprocess_backward(const FwdInputs& in, const Cam& cam, const GeomState& g, const int* radii,
-                                const BwdOutputs& out, cudaStream_t s);
+                                const BwdOutputs& out, const BwdOpts& opt, cudaStream_t s);
 void launch_export(int P, int64_t R, const Cam& cam, const GeomState& g, const BinState& b, uint32_t* tiles_touched,
                    float* depths, float* means2D, float* conic_opacity, float* rgb, uint8_t* clamped,
                    uint64_t* sorted_keys, cudaStream_t s);

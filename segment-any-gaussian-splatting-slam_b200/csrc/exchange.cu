@@ -19,7 +19,7 @@ struct XcPeers {
 __device__ __forceinline__ uint32_t union4(const XcPeers& f, size_t g) {
   // 4 consecutive flag bytes, OR over ranks (P % 4 == 0 is not required: callers bound-check per byte)
   uint32_t u = 0;
-  for (int r = 0; r < f.n; r++) u |= *reinterpret_cast<const uint32_t*>(static_cast<const uint8_t*>(f.p[r]) + g);
+  for (int r = 0; r < f.n; r++) u |= __ldcg(reinterpret_cast<const uint32_t*>(static_cast<const uint8_t*>(f.p[r]) + g));
   return u;
 }
 
@@ -133,22 +133,62 @@ struct XcPeerTensors {
   int n[8];
   int count;
 };
+// MASKED: rank q's row g is valid only where q's own flag g is set (sparse-row backward, gsr_ext::sparse_rows: the
+// other rows of its bucket are stale, not zero). Peer memory is read with ld.global.cg (L2 of the owning GPU, never
+// a stale line of this SM's L1).
+template <bool MASKED>
 __global__ void __launch_bounds__(256)
-xc_gather_sum_kernel(XcPeerTensors t, XcPeers buckets, const int* __restrict__ idx, const int* __restrict__ count, int cap) {
+xc_gather_sum_kernel(XcPeerTensors t, XcPeers buckets, XcPeers flags, const int* __restrict__ idx,
+                     const int* __restrict__ count, int cap) {
   const int lane = threadIdx.x & 31;
   const int nrows = min(*count, cap);  // rows beyond are left untouched: consumers read idx / compact only below *count
   for (int row = blockIdx.x * 8 + (threadIdx.x >> 5); row < nrows; row += gridDim.x * 8) {
     const size_t g = (size_t)idx[row];
+    uint32_t live = 0xffffffffu;  // bit r: rank r contributes to this row
+    if (MASKED) {
+      live = 0;
+      for (int r = 0; r < buckets.n; r++) live |= (__ldcg(static_cast<const uint8_t*>(flags.p[r]) + g) ? 1u : 0u) << r;
+    }
     for (int k = 0; k < t.count; k++) {
       const int n = t.n[k];
       float* d = t.dst[k] + (size_t)row * n;
       const long long base = t.off[k] + (long long)(g * n);
       for (int i = lane; i < n; i += 32) {
         float s = 0.f;
-        for (int r = 0; r < buckets.n; r++) s += static_cast<const float*>(buckets.p[r])[base + i];
+        for (int r = 0; r < buckets.n; r++)
+          if ((live >> r) & 1u) s += __ldcg(static_cast<const float*>(buckets.p[r]) + base + i);
         d[i] = s;
       }
     }
+  }
+}
+
+// Cross-rank "ready" handshake over peer memory, one launch: thread q publishes this rank's sequence number in slot
+// [rank] of rank q's signal pad (release at system scope: everything this stream wrote before is visible to a peer
+// that observes it), then waits until slot [q] of its OWN pad has reached `seq` (acquire). Sequence numbers only grow,
+// so there is nothing to reset and no second barrier. A peer that never arrives (crashed rank) ends the wait after
+// `timeout_ns` and sets *status instead of hanging the GPU; the host checks status when it next synchronises.
+__global__ void xc_signal_wait_kernel(XcPeers pads, int rank, uint32_t seq, unsigned long long timeout_ns,
+                                      int* __restrict__ status) {
+  const int q = threadIdx.x;
+  if (q >= pads.n) return;
+  __threadfence_system();
+  uint32_t* theirs = static_cast<uint32_t*>(const_cast<void*>(pads.p[q])) + rank;
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(theirs), "r"(seq) : "memory");
+  const uint32_t* mine = static_cast<const uint32_t*>(pads.p[rank]) + q;
+  unsigned long long t0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  for (;;) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
+    if ((int32_t)(v - seq) >= 0) break;
+    unsigned long long t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    if (t1 - t0 > timeout_ns) {
+      atomicExch(status, 1 + q);
+      break;
+    }
+    __nanosleep(200);
   }
 }
 // The same gather with a thread per OUTPUT element (blockIdx.y = tensor): rows of 1-45 floats leave most lanes of a
@@ -228,17 +268,26 @@ void launch_union_compact_peers(const uint8_t* const* flags, int nranks, int P, 
   for (int r = 0; r < nranks; r++) f.p[r] = flags[r];
   union_compact(f, P, cap, idx, count, scratch, s);
 }
-void launch_sum_rows_peers(const float* const* buckets, int nranks, int ntensors, const long long* off, float* const* dst,
-                           const int* n, const int* idx, const int* count, int cap, cudaStream_t s) {
+void launch_signal_wait(void* const* pads, int nranks, int rank, uint32_t seq, unsigned long long timeout_ns, int* status,
+                        cudaStream_t s) {
+  XcPeers p;
+  p.n = nranks;
+  for (int r = 0; r < nranks; r++) p.p[r] = pads[r];
+  xc_signal_wait_kernel<<<1, 32, 0, s>>>(p, rank, seq, timeout_ns, status);
+}
+void launch_sum_rows_peers(const float* const* buckets, const uint8_t* const* flags, int nranks, int ntensors,
+                           const long long* off, float* const* dst, const int* n, const int* idx, const int* count, int cap,
+                           cudaStream_t s) {
   if (cap <= 0) return;
-  XcPeers b;
-  b.n = nranks;
-  for (int r = 0; r < nranks; r++) b.p[r] = buckets[r];
+  XcPeers b, f;
+  b.n = f.n = nranks;
+  for (int r = 0; r < nranks; r++) { b.p[r] = buckets[r]; f.p[r] = flags ? flags[r] : nullptr; }
   XcPeerTensors t;
   t.count = ntensors;
   for (int k = 0; k < ntensors; k++) { t.off[k] = off[k]; t.dst[k] = dst[k]; t.n[k] = n[k]; }
   const int nb = (cap + 7) / 8;
-  xc_gather_sum_kernel<<<nb < 148 * 8 ? nb : 148 * 8, 256, 0, s>>>(t, b, idx, count, cap);
+  if (flags) xc_gather_sum_kernel<true><<<nb < 148 * 8 ? nb : 148 * 8, 256, 0, s>>>(t, b, f, idx, count, cap);
+  else xc_gather_sum_kernel<false><<<nb < 148 * 8 ? nb : 148 * 8, 256, 0, s>>>(t, b, f, idx, count, cap);
 }
 void launch_rows(int scatter, int ntensors, const float* const* src, float* const* dst, const int* n, const int* idx,
                  const int* count, int cap, cudaStream_t s) {

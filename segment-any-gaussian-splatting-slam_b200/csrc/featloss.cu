@@ -260,11 +260,8 @@ template <int F, int NT>
 void launch_fl(const float* obj, const long long* gt, int HW, int C, const float* weight, const float* bias, float gscale,
                float* dobj, int* pred, float* partial, int grid, cudaStream_t s) {
   auto k = feature_loss_kernel<F, NT>;
-  static bool once = false;
-  if (!once) {
-    cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FlCfg<F, NT>::SMEM);
-    once = true;
-  }
+  static std::atomic<unsigned long long> attr_done{0};  // per template instance, per-device bitmap (common.cuh)
+  ensure_dyn_smem(k, (int)FlCfg<F, NT>::SMEM, attr_done);
   k<<<grid, FL_THREADS, FlCfg<F, NT>::SMEM, s>>>(obj, gt, HW, C, weight, bias, gscale, dobj, pred, partial);
 }
 

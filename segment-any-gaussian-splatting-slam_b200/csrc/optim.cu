@@ -24,6 +24,7 @@ struct AdamArgs {
   const int* idx;    // sparse mode: rows to step (NULL = dense)
   const int* count;  // sparse mode: number of valid rows (device scalar)
   int cap;           // sparse mode: rows in the compact gradient tensors
+  int dense_grad_rows;  // sparse mode: the gradient tensors are addressed by Gaussian index (sparse-row backward output)
 };
 
 // torch/optim/adam.py (_single_tensor_adam): exp_avg.lerp_(grad, 1 - beta1); exp_avg_sq = beta2 v + (1 - beta2) g g;
@@ -46,7 +47,7 @@ adam_step_kernel(const AdamArgs a) {
   if (a.idx) {
     if (row >= a.cap || row >= *a.count) return;
     g = (size_t)a.idx[row];
-    gr = (size_t)row;
+    gr = a.dense_grad_rows ? g : (size_t)row;
   } else {
     if (row >= a.P) return;
     g = gr = (size_t)row;
@@ -221,7 +222,7 @@ activate_kernel(const gsr_adam_tensors t, int P, int M) {
 }
 
 void launch_adam(const gsr_adam_tensors& t, int P, int M, int F, const float* lr, float beta1, float beta2, float eps,
-                 int step, const int* idx, const int* count, int cap, cudaStream_t s) {
+                 int step, const int* idx, const int* count, int cap, int flags, cudaStream_t s) {
   AdamArgs a;
   a.t = t;
   for (int i = 0; i < 7; i++) a.lr[i] = lr[i];
@@ -229,6 +230,7 @@ void launch_adam(const gsr_adam_tensors& t, int P, int M, int F, const float* lr
   a.bc1 = (float)(1.0 - pow((double)beta1, (double)step));
   a.bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, (double)step));
   a.P = P; a.M = M; a.F = F; a.idx = idx; a.count = count; a.cap = cap;
+  a.dense_grad_rows = (flags & GSR_ADAM_DENSE_GRAD_ROWS) ? 1 : 0;
   if (idx) {  // sparse: a warp per listed row
     if (cap > 0) adam_step_kernel<<<(cap + 7) / 8, 256, 0, s>>>(a);
     return;

@@ -28,13 +28,18 @@ __device__ __forceinline__ void stage_out(float* tile, float* __restrict__ gbase
   __syncthreads();
 }
 
-template <int F, bool POSE>
+// MODE 0: the reference's dense outputs (every row of the eleven tensors written, zeros for Gaussians without a
+//         gradient); MODE 1: sparse rows (gsr_ext::sparse_rows): only the rows of Gaussians the backward blend reached
+//         are written -- or, with opt.accumulate, added to when the step-level flag of the row was already set (several
+//         views of one mapping step accumulating into one bucket); MODE 2: tracking (gsr_ext::tracking): no per-Gaussian
+//         output at all, only the camera sums.
+template <int F, bool POSE, int MODE>
 __global__ void __launch_bounds__(PB_THREADS)
 preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restrict__ tiles_touched,
                       const uint8_t* __restrict__ clampedb, const int* __restrict__ radii,
-                      const float* __restrict__ grad_rows, const uint8_t* __restrict__ touched,
+                      float* __restrict__ grad_rows, uint8_t* __restrict__ touched,
                       const float4* __restrict__ rec, double* __restrict__ pose_acc,
-                      const BwdOutputs out) {
+                      const BwdOutputs out, const BwdOpts opt) {
   constexpr int ROW = (F == 16) ? 32 : 64;
   __shared__ CamS cs;
   __shared__ float4 tile4[PB_THREADS * 13];  // M == 16: SH rows of 12 float4 at a 13-float4 stride
@@ -46,12 +51,14 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
   const bool valid = idx < in.P;
   const int M = in.M, D = in.D;
   // Gaussians the backward blend never reached have all-zero rows, hence all-zero gradients: only zeros are written
-  const bool visible = valid && radii[idx] > 0 && touched[idx] != 0;
+  // (a touched Gaussian was rendered, so radii > 0 is implied: the sparse modes do not read radii)
+  const bool visible = valid && touched[idx] != 0 && (MODE != 0 || radii[idx] > 0);
   const bool any_visible = __syncthreads_or(visible);
+  if (MODE != 0 && !any_visible) return;  // sparse / tracking: nothing to write for this block
   const int SS = (3 * M) | 1;  // odd row stride -> conflict-free per-thread rows
   // SH coefficients of the block's Gaussians: coalesced load into the tile
-  const bool sh16 = in.shs != nullptr && M == 16 && (((uintptr_t)in.shs | (uintptr_t)out.dL_dsh) & 15) == 0;
-  if (!any_visible) {
+  const bool sh16 = MODE == 0 && in.shs != nullptr && M == 16 && (((uintptr_t)in.shs | (uintptr_t)out.dL_dsh) & 15) == 0;
+  if (!any_visible || MODE != 0) {  // (the sparse modes read the few SH rows they need straight from global memory)
     // nothing to read for this block
   } else if (sh16) {
     const int n = min(PB_THREADS, in.P - first) * 12;
@@ -68,11 +75,16 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
 #pragma unroll
   for (int k = 0; k < 12 + F; k++) g[k] = 0.f;
   if (visible) {
-    const float4* row = reinterpret_cast<const float4*>(grad_rows + (size_t)idx * ROW);
+    float4* row = reinterpret_cast<float4*>(grad_rows + (size_t)idx * ROW);
 #pragma unroll
     for (int q = 0; q < (12 + F) / 4; q++) {
       float4 t = row[q];
       g[4 * q] = t.x; g[4 * q + 1] = t.y; g[4 * q + 2] = t.z; g[4 * q + 3] = t.w;
+    }
+    if (opt.clean_rows) {  // persistent workspace (gsr_ext::row_workspace): consumed rows and flags go back to zero
+#pragma unroll
+      for (int q = 0; q < (12 + F) / 4; q++) row[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+      touched[idx] = 0;
     }
   }
   if (visible) {
@@ -91,7 +103,7 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
     g[6] = -cb2 * Wx;            // d/dcov_yz (sic, backward.cu:629)
   }
   // scalar / float4 outputs of K5 are written directly (coalesced as they are)
-  if (valid) {
+  if (MODE == 0 && valid) {
     out.dL_dopacity[idx] = g[7];
     out.dL_ddepths[idx] = g[8];
     float4* o = reinterpret_cast<float4*>(out.dL_dobjects + (size_t)idx * F);
@@ -239,7 +251,7 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
       const float3 dir_orig = {m.x - cs.campos[0], m.y - cs.campos[1], m.z - cs.campos[2]};
       const float len = sqrtf(dir_orig.x * dir_orig.x + dir_orig.y * dir_orig.y + dir_orig.z * dir_orig.z);
       const float x = dir_orig.x / len, y = dir_orig.y / len, z = dir_orig.z / len;
-      const float* sh = tile + threadIdx.x * SS;
+      const float* sh = MODE == 0 ? tile + threadIdx.x * SS : in.shs + (size_t)idx * 3 * M;
       const uint8_t cb = clampedb[idx];
       dRGB[0] = g[9] * ((cb & 1) ? 0.f : 1.f);
       dRGB[1] = g[10] * ((cb & 2) ? 0.f : 1.f);
@@ -339,7 +351,46 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
     }
   }
 
-  // ---- coalesced stores through the tile ----
+  if (MODE == 1 && visible) {
+    // ---- sparse rows: this thread's rows only; first touch of the step writes, later views of the step add ----
+    const bool acc = opt.accumulate && opt.touched_ext[idx] != 0;
+    auto put = [acc](float* p, float v) { *p = acc ? *p + v : v; };
+    put(out.dL_dopacity + idx, g[7]);
+    put(out.dL_ddepths + idx, g[8]);
+#pragma unroll
+    for (int k = 0; k < F; k++) put(out.dL_dobjects + (size_t)idx * F + k, g[12 + k]);
+    put(out.dL_dmean2D + 3 * (size_t)idx, g[0]);
+    put(out.dL_dmean2D + 3 * (size_t)idx + 1, g[1]);
+    put(out.dL_dmean2D + 3 * (size_t)idx + 2, 0.f);
+    const float v6[6] = {g[2], g[3], 0.f, g[4], g[5], g[6]};
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+      put(out.dL_dconic + 6 * (size_t)idx + k, v6[k]);
+      put(out.dL_dcov3D + 6 * (size_t)idx + k, dcov[k]);
+    }
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      put(out.dL_dcolor + 3 * (size_t)idx + k, g[9 + k]);
+      put(out.dL_dmean3D + 3 * (size_t)idx + k, dmean[k]);
+      if (out.dL_dscale) put(out.dL_dscale + 3 * (size_t)idx + k, dscale[k]);
+    }
+    if (out.dL_drot) {
+#pragma unroll
+      for (int k = 0; k < 4; k++) put(out.dL_drot + 4 * (size_t)idx + k, drot[k]);
+    }
+    if (out.dL_dsh != nullptr) {
+#pragma unroll
+      for (int k = 0; k < 16; k++)
+        if (k < M) {
+#pragma unroll
+          for (int c = 0; c < 3; c++) put(out.dL_dsh + ((size_t)idx * M + k) * 3 + c, basis[k] * dRGB[c]);
+        }
+    }
+    if (opt.accumulate) opt.touched_ext[idx] = 1;  // (without accumulate the backward blend has set it already)
+    if (opt.touched_idx && !acc) opt.touched_idx[atomicAdd(opt.touched_count, 1)] = idx;
+  }
+  // ---- dense outputs: coalesced stores through the tile ----
+  if (MODE == 0) {
   __syncthreads();  // every thread is done reading its SH row
   if (sh16) {
     float d48[48];
@@ -377,7 +428,9 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
     if (out.dL_dscale) stage_out<3>(tile, out.dL_dscale, dscale, in.P);
   }
   if (out.dL_drot && valid) reinterpret_cast<float4*>(out.dL_drot)[idx] = make_float4(drot[0], drot[1], drot[2], drot[3]);
+  }  // MODE == 0
   if (want_pose) {  // block-uniform: warp shuffle -> shared -> one double atomic per value per block
+    __syncthreads();
     if (threadIdx.x < 27) tile[threadIdx.x] = 0.f;
     __syncthreads();
 #pragma unroll
@@ -406,15 +459,22 @@ __global__ void pose_finalize_kernel(const double* __restrict__ acc, float* __re
 }
 
 void launch_preprocess_backward(const FwdInputs& in, const Cam& cam, const GeomState& g, const int* radii,
-                                const BwdOutputs& out, cudaStream_t s) {
+                                const BwdOutputs& out, const BwdOpts& opt, cudaStream_t s) {
   const int nb = (in.P + PB_THREADS - 1) / PB_THREADS;
   if (out.dL_dviewmatrix) cudaMemsetAsync(g.pose_acc, 0, 32 * sizeof(double), s);
-#define GSR_LAUNCH_PB(FF, PP)                                                                                      \
-  preprocess_bwd_kernel<FF, PP><<<nb, PB_THREADS, 0, s>>>(in, cam, g.tiles_touched, g.clamped, radii, g.grad_rows, g.touched, \
-                                                          g.rec, g.pose_acc, out)
+#define GSR_LAUNCH_PB(FF, PP, MM)                                                                                        \
+  preprocess_bwd_kernel<FF, PP, MM><<<nb, PB_THREADS, 0, s>>>(in, cam, g.tiles_touched, g.clamped, radii, opt.rows, opt.touched, \
+                                                              g.rec, g.pose_acc, out, opt)
   const bool pose = out.dL_dviewmatrix != nullptr;
-  if (in.F == 16) { if (pose) GSR_LAUNCH_PB(16, true); else GSR_LAUNCH_PB(16, false); }
-  else            { if (pose) GSR_LAUNCH_PB(32, true); else GSR_LAUNCH_PB(32, false); }
+  const int mode = opt.tracking ? 2 : (opt.sparse_rows ? 1 : 0);
+#define GSR_LAUNCH_PB_F(FF)                                                          \
+  do {                                                                               \
+    if (mode == 2) { GSR_LAUNCH_PB(FF, true, 2); }                                   \
+    else if (mode == 1) { if (pose) GSR_LAUNCH_PB(FF, true, 1); else GSR_LAUNCH_PB(FF, false, 1); } \
+    else { if (pose) GSR_LAUNCH_PB(FF, true, 0); else GSR_LAUNCH_PB(FF, false, 0); } \
+  } while (0)
+  if (in.F == 16) GSR_LAUNCH_PB_F(16); else GSR_LAUNCH_PB_F(32);
+#undef GSR_LAUNCH_PB_F
 #undef GSR_LAUNCH_PB
   if (out.dL_dviewmatrix)
     pose_finalize_kernel<<<1, 32, 0, s>>>(g.pose_acc, out.dL_dviewmatrix, out.dL_dprojmatrix, out.dL_dcampos);

@@ -400,22 +400,22 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
 
 void launch_render_backward(int F, const Cam& cam, const GeomState& g, const BinState& b, const ImageState& img,
                             const float* sh_objs, const float* dL_dpix_depth, const float* dL_dpix,
-                            const float* dL_dpix_obj, uint8_t* touched, cudaStream_t s) {
+                            const float* dL_dpix_obj, const BwdOpts& opt, cudaStream_t s) {
   dim3 grid(cam.gx, cam.gy), block(256);
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(render_bwd_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmem<16>));
-    cudaFuncSetAttribute(render_bwd_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmem<32>));
-    attr_set = true;
-  }
-  if (F == 16)
+  // with opt.accumulate the per-Gaussian backward maintains the external flags (it has to see their previous value)
+  uint8_t* const ext = opt.accumulate ? nullptr : opt.touched_ext;
+  static std::atomic<unsigned long long> done16{0}, done32{0};  // per-device opt-in bitmaps (common.cuh)
+  if (F == 16) {
+    ensure_dyn_smem(render_bwd_kernel<16>, (int)sizeof(BwdSmem<16>), done16);
     render_bwd_kernel<16><<<grid, block, sizeof(BwdSmem<16>), s>>>(
         img.ranges, b.point_list, b.hitw, g.rec, sh_objs, cam.W, cam.H, cam.bg, img.final_T, img.n_contrib,
-        dL_dpix_depth, dL_dpix, dL_dpix_obj, g.grad_rows, g.touched, touched);
-  else
+        dL_dpix_depth, dL_dpix, dL_dpix_obj, opt.rows, opt.touched, ext);
+  } else {
+    ensure_dyn_smem(render_bwd_kernel<32>, (int)sizeof(BwdSmem<32>), done32);
     render_bwd_kernel<32><<<grid, block, sizeof(BwdSmem<32>), s>>>(
         img.ranges, b.point_list, b.hitw, g.rec, sh_objs, cam.W, cam.H, cam.bg, img.final_T, img.n_contrib,
-        dL_dpix_depth, dL_dpix, dL_dpix_obj, g.grad_rows, g.touched, touched);
+        dL_dpix_depth, dL_dpix, dL_dpix_obj, opt.rows, opt.touched, ext);
+  }
 }
 
 }  // namespace gsr

@@ -17,11 +17,117 @@ LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libgsraster_b200.so")
 ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_size_t)
 
 
+class Stats(C.Structure):
+    """gsr_stats: OUT record of one call."""
+    _fields_ = [("num_rendered", C.c_ulonglong), ("l1_total", C.c_ulonglong), ("sync_us", C.c_ulonglong),
+                ("alloc_us", C.c_ulonglong), ("launch_us", C.c_ulonglong), ("launches", C.c_int)]
+
+
+class _ExtStruct(C.Structure):
+    """gsr_ext (include/gsraster_b200.h): the per-call extensions. There are no mode switches in the library: what a
+    call does differently from the reference is passed to that call."""
+    _fields_ = [("touched_mask", C.c_void_p), ("touched_len", C.c_int), ("blend_done_event", C.c_void_p),
+                ("tracking", C.c_int), ("sparse_rows", C.c_int), ("accumulate", C.c_int), ("touched_idx", C.c_void_p),
+                ("touched_count", C.c_void_p), ("row_workspace", C.c_void_p), ("timer", C.c_void_p),
+                ("stats", C.POINTER(Stats))]
+
+
 class Params(C.Structure):
     _fields_ = [("P", C.c_int), ("D", C.c_int), ("M", C.c_int), ("F", C.c_int), ("width", C.c_int),
                 ("height", C.c_int), ("tan_fovx", C.c_float), ("tan_fovy", C.c_float),
                 ("scale_modifier", C.c_float), ("prefiltered", C.c_int), ("debug", C.c_int),
-                ("stream", C.c_void_p)]
+                ("stream", C.c_void_p), ("ext", C.POINTER(_ExtStruct))]
+
+
+class Timer:
+    """gsr_timer: per-stage CUDA-event spans of the calls it is handed to (Ext(timer=...))."""
+
+    def __init__(self):
+        L = lib()
+        L.gsr_timer_create.restype = C.c_void_p
+        L.gsr_timer_destroy.argtypes = [C.c_void_p]
+        L.gsr_timer_read.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+        self.h = L.gsr_timer_create()
+        if not self.h:
+            raise RuntimeError("gsr_timer_create failed")
+
+    def read(self):
+        """-> (stage_ms, gap_ms): milliseconds per stage, and idle stream time before each stage, accumulated since the
+        previous read (synchronises the recorded events)."""
+        ms, gap = (C.c_float * len(STAGES))(), (C.c_float * len(STAGES))()
+        _check(lib().gsr_timer_read(self.h, ms, gap))
+        return dict(zip(STAGES, [float(v) for v in ms])), dict(zip(STAGES, [float(v) for v in gap]))
+
+    def __del__(self):
+        try:
+            if self.h:
+                lib().gsr_timer_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+
+class Ext:
+    """Per-call extensions of rasterize_gaussians / rasterize_gaussians_backward (gsr_ext). Keeps the tensors it
+    points to alive. Fields (all optional):
+      touched_mask   CUDA uint8 (P,) zeroed by the caller: flags of the Gaussians the backward blend reached
+      blend_done     torch.cuda.Event (recorded once before): recorded right after the backward blend
+      tracking       camera-tracking backward: only the camera gradients (camera_grads=True), no per-Gaussian outputs
+      sparse_rows    backward writes only the rows of touched Gaussians (needs touched_mask), nothing else is written
+      accumulate     sparse rows of Gaussians already flagged are added to (views of one step into one bucket)
+      touched_idx / touched_count   CUDA int32 (P,) / (1,): list of the Gaussians written
+      row_workspace  persistent CUDA uint8 buffer of row_workspace_bytes(P, F), all zero (kept zero by the library)
+      timer          capi.Timer: per-stage events of this call
+    After the call `ext.stats` holds the gsr_stats record of it."""
+
+    def __init__(self, touched_mask=None, blend_done=None, tracking=False, sparse_rows=False, accumulate=False,
+                 touched_idx=None, touched_count=None, row_workspace=None, timer=None):
+        self.stats = Stats()
+        self._keep = (touched_mask, blend_done, touched_idx, touched_count, row_workspace, timer)
+        s = _ExtStruct()
+        if touched_mask is not None:
+            if touched_mask.dtype != torch.uint8 or not touched_mask.is_cuda or not touched_mask.is_contiguous():
+                raise RuntimeError("touched mask must be a contiguous CUDA uint8 tensor")
+            s.touched_mask, s.touched_len = touched_mask.data_ptr(), touched_mask.numel()
+        if blend_done is not None:
+            h = blend_done.cuda_event
+            h = getattr(h, "value", h)
+            if not h:
+                raise RuntimeError("blend-done event has no CUDA handle yet: record it once before passing it")
+            s.blend_done_event = h
+        s.tracking, s.sparse_rows, s.accumulate = int(bool(tracking)), int(bool(sparse_rows)), int(bool(accumulate))
+        for name, t in (("touched_idx", touched_idx), ("touched_count", touched_count)):
+            if t is not None:
+                if t.dtype != torch.int32 or not t.is_cuda or not t.is_contiguous():
+                    raise RuntimeError(name + " must be a contiguous CUDA int32 tensor")
+                setattr(s, name, t.data_ptr())
+        if row_workspace is not None:
+            if row_workspace.dtype != torch.uint8 or not row_workspace.is_cuda or not row_workspace.is_contiguous():
+                raise RuntimeError("row_workspace must be a contiguous CUDA uint8 tensor")
+            s.row_workspace = row_workspace.data_ptr()
+        self.workspace_bytes = 0 if row_workspace is None else row_workspace.numel()
+        if timer is not None:
+            s.timer = timer.h
+        s.stats = C.pointer(self.stats)
+        self.struct = s
+
+    def ptr(self, P=None, F=None):
+        if P is not None and self.workspace_bytes and self.workspace_bytes < row_workspace_bytes(P, F):
+            raise RuntimeError("row_workspace is smaller than row_workspace_bytes(P, F)")
+        return C.pointer(self.struct)
+
+
+def row_workspace_bytes(P, F):
+    L = lib()
+    L.gsr_row_workspace_bytes.restype = C.c_size_t
+    L.gsr_row_workspace_bytes.argtypes = [C.c_int, C.c_int]
+    return int(L.gsr_row_workspace_bytes(int(P), int(F)))
+
+
+def new_row_workspace(P, F, device):
+    """Zeroed persistent accumulation workspace for Ext(row_workspace=...)."""
+    return torch.zeros(row_workspace_bytes(P, F) + 256, dtype=torch.uint8, device=device)
+
 
 
 _lib = None
@@ -47,16 +153,12 @@ def lib():
         L.gsr_knn.argtypes = [C.c_int] + [C.c_void_p] * 4
         L.gsr_export_state.argtypes = [C.POINTER(Params), C.c_int] + [C.c_void_p] * 14
         L.gsr_count_pairs.argtypes = [C.POINTER(Params), C.c_int] + [C.c_void_p] * 3 + [C.POINTER(C.c_ulonglong)]
-        L.gsr_get_stage_times.argtypes = [C.POINTER(C.c_float)]
-        L.gsr_get_stage_gaps.argtypes = [C.POINTER(C.c_float)]
-        L.gsr_set_touched_mask.argtypes = [C.c_void_p]
         L.gsr_exchange_scratch_bytes.argtypes = [C.c_int]
         L.gsr_exchange_compact.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                            C.c_void_p, C.c_void_p]
         L.gsr_exchange_rows.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
                                         C.POINTER(C.c_int), C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.gsr_last_forward_stats.argtypes = [C.POINTER(C.c_ulonglong)]
-        L.gsr_set_stage_timing.argtypes = [C.c_int]
         _lib = L
     return _lib
 
@@ -135,8 +237,9 @@ def _stream_ptr():
 
 def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
                         viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, sh_objs, degree,
-                        campos, prefiltered, debug):
-    """-> (num_rendered, depth, color, objects, radii, is_used, geomBuffer, binningBuffer, imgBuffer)."""
+                        campos, prefiltered, debug, ext=None):
+    """-> (num_rendered, depth, color, objects, radii, is_used, geomBuffer, binningBuffer, imgBuffer).
+    `ext` (extension): a capi.Ext with the per-call options / timer / statistics of this call."""
     if means3D.dim() != 2 or means3D.size(1) != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
     if not means3D.is_cuda:
@@ -159,7 +262,7 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         return 0, out_depth, out_color, out_objects, radii, is_used, geo.take(), binb.take(), img.take()
     M = sh.size(1) if (sh is not None and sh.numel() != 0) else 0
     prm = Params(P, int(degree), int(M), int(F), W, H, float(tan_fovx), float(tan_fovy), float(scale_modifier),
-                 int(bool(prefiltered)), int(bool(debug)), _stream_ptr())
+                 int(bool(prefiltered)), int(bool(debug)), _stream_ptr(), ext.ptr(P, F) if ext is not None else None)
     keep = [_f32c(t) for t in (background, means3D, sh, sh_objs, colors, opacity, scales, rotations, cov3D_precomp,
                                viewmatrix, projmatrix, campos)]
     with torch.cuda.device(dev):
@@ -171,11 +274,21 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
     return (rendered.value, out_depth, out_color, out_objects, radii, is_used) + bufs
 
 
+def _alloc_grads(P, M, F, o):
+    return dict(means3D=torch.empty((P, 3), **o), means2D=torch.empty((P, 3), **o), depths=torch.empty((P, 1), **o),
+                colors=torch.empty((P, 3), **o), objects=torch.empty((P, F), **o), conic=torch.empty((P, 6), **o),
+                opacity=torch.empty((P, 1), **o), cov3D=torch.empty((P, 6), **o), sh=torch.empty((P, M, 3), **o),
+                scales=torch.empty((P, 3), **o), rotations=torch.empty((P, 4), **o))
+
+
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier,
                                  cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_depth,
                                  dL_dout_color, sh, dL_dout_objects, sh_objs, degree, campos, geomBuffer, R,
-                                 binningBuffer, imageBuffer, debug, out=None, camera_grads=False):
-    """`camera_grads` (extension, gsr_backward_pose): also compute dL/dviewmatrix (4,4), dL/dprojmatrix (4,4),
+                                 binningBuffer, imageBuffer, debug, out=None, camera_grads=False, ext=None):
+    """`ext` (extension): a capi.Ext with the per-call options of this call (touched flags, sparse rows, tracking, ...).
+    With Ext(tracking=True) no per-Gaussian gradient is computed: the returned 9-tuple holds empty tensors and only
+    `last_camera_grads` is meaningful (camera_grads must be True).
+    `camera_grads` (extension, gsr_backward_pose): also compute dL/dviewmatrix (4,4), dL/dprojmatrix (4,4),
     dL/dcampos (3,) -- same flat layout as the inputs -- left in `rasterize_gaussians_backward.last_camera_grads`.
     `out` (extension): dict of preallocated contiguous fp32 tensors keyed like the local `g` below
     (e.g. views into one flat all-reduce bucket, see mapping.GradBucket) that the kernels write
@@ -188,18 +301,22 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     M = sh.size(1) if (sh is not None and sh.numel() != 0) else 0
     F = sh_objs.numel() // max(P, 1)
     o = dict(device=dev, dtype=torch.float32)
-    g = dict(means3D=torch.empty((P, 3), **o), means2D=torch.empty((P, 3), **o), depths=torch.empty((P, 1), **o),
-             colors=torch.empty((P, 3), **o), objects=torch.empty((P, F), **o), conic=torch.empty((P, 6), **o),
-             opacity=torch.empty((P, 1), **o), cov3D=torch.empty((P, 6), **o), sh=torch.empty((P, M, 3), **o),
-             scales=torch.empty((P, 3), **o), rotations=torch.empty((P, 4), **o))
-    if out:
+    tracking = ext is not None and bool(ext.struct.tracking)
+    if tracking:
+        if not camera_grads:
+            raise RuntimeError("Ext(tracking=True) computes only the camera gradients: pass camera_grads=True")
+        P_alloc = 0
+    else:
+        P_alloc = P
+    g = _alloc_grads(P_alloc, M, F, o)
+    if out and not tracking:
         for k, t in out.items():
             if t.numel() != g[k].numel() or t.dtype != torch.float32 or not t.is_contiguous() or not t.is_cuda:
                 raise RuntimeError(f"out[{k!r}] must be a contiguous CUDA float32 tensor of {g[k].numel()} elements")
             g[k] = t.view(g[k].shape)
     if P != 0:
         prm = Params(P, int(degree), int(M), int(F), W, H, float(tan_fovx), float(tan_fovy), float(scale_modifier),
-                     0, int(bool(debug)), _stream_ptr())
+                     0, int(bool(debug)), _stream_ptr(), ext.ptr(P, F) if ext is not None else None)
         keep = [_f32c(t) for t in (background, means3D, sh, sh_objs, colors, scales, rotations, cov3D_precomp,
                                    viewmatrix, projmatrix, campos)]
         ups = [_f32c(t) for t in (dL_dout_depth, dL_dout_color, dL_dout_objects)]
@@ -212,10 +329,12 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
                 cg = (torch.empty((4, 4), **o), torch.empty((4, 4), **o), torch.empty((3,), **o))
                 rc = lib().gsr_backward_pose(*args, *[_ptr(t) for t in cg])
                 rasterize_gaussians_backward.last_camera_grads = cg
+                if ext is not None:
+                    ext.camera_grads = cg
             else:
                 rc = lib().gsr_backward(*args)
         _check(rc)
-        if scales is None or scales.numel() == 0:
+        if (scales is None or scales.numel() == 0) and not tracking:
             g["scales"].zero_()
             g["rotations"].zero_()
     rasterize_gaussians_backward.last_internal = (g["conic"], g["depths"])
@@ -278,37 +397,6 @@ def last_forward_stats():
     return dict(R=int(c[0]), l1_total=int(c[1]), sync_us=int(c[2]), alloc_us=int(c[3]), launch_us=int(c[4]))
 
 
-def set_stage_timing(enable):
-    _check(lib().gsr_set_stage_timing(int(bool(enable))))
-
-
-def get_stage_times():
-    """Milliseconds per stage accumulated since the previous call (synchronises)."""
-    ms = (C.c_float * len(STAGES))()
-    _check(lib().gsr_get_stage_times(ms))
-    return dict(zip(STAGES, [float(v) for v in ms]))
-
-
-def set_touched_mask(mask):
-    """mask: CUDA uint8 tensor of P elements (zeroed by the caller) or None; see gsr_set_touched_mask."""
-    if mask is not None and (mask.dtype != torch.uint8 or not mask.is_cuda or not mask.is_contiguous()):
-        raise RuntimeError("touched mask must be a contiguous CUDA uint8 tensor")
-    _check(lib().gsr_set_touched_mask(None if mask is None else mask.data_ptr()))
-
-
-def set_blend_done_event(event):
-    """event: a torch.cuda.Event that has been recorded at least once (so its handle exists) or None; see
-    gsr_set_blend_done_event."""
-    h = None
-    if event is not None:
-        h = event.cuda_event
-        h = getattr(h, "value", h)
-        if not h:
-            raise RuntimeError("blend-done event has no CUDA handle yet: record it once before passing it")
-    lib().gsr_set_blend_done_event.argtypes = [C.c_void_p]
-    _check(lib().gsr_set_blend_done_event(h))
-
-
 def exchange_scratch_bytes(P):
     return int(lib().gsr_exchange_scratch_bytes(int(P)))
 
@@ -356,13 +444,6 @@ def exchange_sum_rows_peers(bucket_ptrs, tensor_offsets, compact, floats_per_row
     with torch.cuda.device(idx.device):
         _check(L.gsr_exchange_sum_rows_peers(bp, n, k, off, cp, fp, idx.data_ptr(), count.data_ptr(), int(cap),
                                              _stream_ptr()))
-
-
-def get_stage_gaps():
-    """Idle milliseconds on the stream before each stage (see gsr_get_stage_gaps); call after get_stage_times()."""
-    ms = (C.c_float * len(STAGES))()
-    _check(lib().gsr_get_stage_gaps(ms))
-    return dict(zip(STAGES, [float(v) for v in ms]))
 
 
 def count_pairs(P, D, M, F, W, H, R, geomBuffer, binningBuffer, imageBuffer):

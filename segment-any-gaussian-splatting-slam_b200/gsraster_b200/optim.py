@@ -31,6 +31,7 @@ def _bind():
         L.gsr_activate.argtypes = [C.POINTER(AdamTensors), C.c_int, C.c_int, C.c_void_p]
         L.gsr_adam_step.argtypes = [C.POINTER(AdamTensors), C.c_int, C.c_int, C.c_int, C.POINTER(C.c_float), C.c_float,
                                     C.c_float, C.c_float, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.gsr_adam_step_ex.argtypes = L.gsr_adam_step.argtypes[:-1] + [C.c_int, C.c_void_p]
         L._optim_bound = True
     return L
 
@@ -96,11 +97,12 @@ class FusedGaussianAdam:
                     opacities=self.opacities, scales=self.scales, rotations=self.rotations)
 
     def step(self, grads: Dict[str, torch.Tensor], idx: Optional[torch.Tensor] = None,
-             count: Optional[torch.Tensor] = None):
+             count: Optional[torch.Tensor] = None, dense_rows: bool = False):
         """One Adam step. grads: means3D, sh, objects, opacity, scales, rotations (the rasterizer's gradients w.r.t.
         the activated values; mapping.GradBucket.views or the compact views of a SparseGradExchange).
         idx/count None: dense (= torch.optim.Adam on all P rows). idx (int32, sorted) + count (int32 device scalar, or
-        None = all of idx): sparse, only those Gaussians are stepped."""
+        None = all of idx): sparse, only those Gaussians are stepped. dense_rows (sparse only): grads are the P-row
+        outputs of a sparse-row backward (capi.Ext(sparse_rows=True)): Gaussian idx[r] takes its own row idx[r]."""
         self.step_count += 1
         t = self._tensors(grads)
         lr = (C.c_float * 7)(*[self.lr[k] for k in GROUPS])
@@ -112,6 +114,7 @@ class FusedGaussianAdam:
             if count is None:
                 count = torch.full((1,), cap, dtype=torch.int32, device=idx.device)
         with torch.cuda.device(self.shs.device):
-            capi._check(_bind().gsr_adam_step(C.byref(t), self.P, self.M, self.F, lr, self.betas[0], self.betas[1],
-                                              self.eps, self.step_count, None if idx is None else idx.data_ptr(),
-                                              None if idx is None else count.data_ptr(), cap, capi._stream_ptr()))
+            capi._check(_bind().gsr_adam_step_ex(C.byref(t), self.P, self.M, self.F, lr, self.betas[0], self.betas[1],
+                                                 self.eps, self.step_count, None if idx is None else idx.data_ptr(),
+                                                 None if idx is None else count.data_ptr(), cap,
+                                                 1 if (dense_rows and idx is not None) else 0, capi._stream_ptr()))
