@@ -1,18 +1,21 @@
 #!/usr/bin/env python
 """bench.py -- headline benchmark of the rasterizer hot path (BASELINE.json metric).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl mine|reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl mine|reference] [--config headline|c2|c3|c4]
 
-A "step" is one mapping iteration of the hot path on one keyframe view: rasterizer forward +
-backward (rasterize_gaussians + rasterize_gaussians_backward through the C ABI) on the headline
-workload: 1M Gaussians, 1280x1024, SH degree 3 (M=16), 16-d feature. With N GPUs every rank
-rasterizes its own view per step against replicated Gaussians and the parameter gradients are
-summed with one NCCL all-reduce (weak scaling); value = view-iterations/s over all ranks.
+A "step" is one mapping step of the hot path: every rank runs rasterizer forward + backward (through the C ABI) for its
+`--views-per-rank` keyframe views of the step's batch, accumulating the Gaussian-parameter gradients of its views; with
+N > 1 the ranks then sum their gradients (sparse exchange over peer memory). The batch of a step is the next N x V
+keyframes of a fixed trajectory of `--pool` DISTINCT poses (5 degrees of yaw + 0.25 m per keyframe) over a map
+sampled on the union of their frusta -- the reference, too, steps on a different keyframe every iteration
+(scripts/gaussian_splatting.py:792-833, 887-935). Views are assigned to ranks longest-processing-time-first on their
+measured cost. value = view-iterations (one view forward + backward) per second over all ranks; N = 1 renders the same
+keyframes one after the other, so per-GPU work is the same at every N (weak scaling).
 
---impl reference times the UNMODIFIED reference CUDA rasterizer (oracle/_ref, built by
-oracle/build_ref.sh for sm_100a) on the same workload on GPU 0 (the reference has no CPU path and
-no multi-GPU path); if oracle/_ref is absent it falls back to timing the CPU oracle port.
-Prints ONE JSON line on rank 0.
+Headline workload: 1M Gaussians, 1280x1024, SH degree 3 (M=16), 16-d feature (BASELINE.json metric).
+--impl reference times the UNMODIFIED reference CUDA rasterizer (oracle/_ref, built by oracle/build_ref.sh for
+sm_100a) on the same keyframes on GPU 0 (the reference has no CPU path and no multi-GPU path); if oracle/_ref is
+absent it falls back to timing the CPU oracle port. Prints ONE JSON line on rank 0.
 """
 import argparse
 import json
@@ -31,37 +34,77 @@ for _p in (ROOT, PKG):
 METRIC = "mapping_iters_per_sec_fwd_bwd"
 UNIT = "iters/s"
 
+CONFIGS = {   # BASELINE.json configs (config 1 is the CPU-runnable parity case, config 5 = the tracking / kNN legs)
+    "headline": dict(P=1_000_000, width=1280, height=1024, F=16, views_per_rank=2, pool=16),
+    "c2": dict(P=500_000, width=1280, height=1024, F=16, views_per_rank=1, pool=1),
+    "c3": dict(P=2_000_000, width=1280, height=1024, F=16, views_per_rank=1, pool=8),
+    "c4": dict(P=6_000_000, width=1920, height=1080, F=32, views_per_rank=1, pool=8),
+}
+
 
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=40)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="mine", choices=["mine", "reference"])
-    ap.add_argument("--P", type=int, default=1_000_000)
-    ap.add_argument("--width", type=int, default=1280)
-    ap.add_argument("--height", type=int, default=1024)
-    ap.add_argument("--F", type=int, default=16)
+    ap.add_argument("--config", default="headline", choices=sorted(CONFIGS))
+    ap.add_argument("--P", type=int, default=None)
+    ap.add_argument("--width", type=int, default=None)
+    ap.add_argument("--height", type=int, default=None)
+    ap.add_argument("--F", type=int, default=None)
     ap.add_argument("--deg", type=int, default=3)
+    ap.add_argument("--views-per-rank", type=int, default=None, help="keyframe views per rank per step")
+    ap.add_argument("--pool", type=int, default=None, help="distinct keyframe poses of the trajectory")
+    ap.add_argument("--same-pose", action="store_true",
+                    help="secondary figure (scaling_same_pose): every rank renders keyframe 0 of the single-frustum "
+                         "SURVEY 8d scene, as the round-1 scaling run did")
+    ap.add_argument("--no-lpt", action="store_true", help="contiguous view blocks instead of the LPT assignment")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-legs", action="store_true", help="skip the secondary legs (workloads, render FPS, kNN, ...)")
     ap.add_argument("--nccl-exchange", action="store_true",
-                    help="N > 1, sparse exchange: NCCL all-gather + all-reduce instead of the peer-memory kernels")
-    ap.add_argument("--no-exchange-overlap", action="store_true",
-                    help="N > 1, sparse exchange: run the flag all-gather + compaction after the per-Gaussian backward "
-                         "instead of beside it")
+                    help="N > 1: NCCL all-gather + all-reduce instead of the peer-memory kernels")
     ap.add_argument("--dense-allreduce", action="store_true",
-                    help="N > 1: sum the full 4(11+3M+F) B/Gaussian bucket instead of the sparse (touched-rows) exchange")
-    ap.add_argument("--distinct-views", action="store_true", help="rank r renders keyframe pose r (unequal work)")
-    return ap.parse_args()
+                    help="N > 1, one view per rank: NCCL all-reduce of the full 4(11+3M+F) B/Gaussian bucket")
+    a = ap.parse_args()
+    cfg = CONFIGS[a.config]
+    for k, v in cfg.items():
+        if getattr(a, k) is None:
+            setattr(a, k, v)
+    if a.same_pose:
+        a.pool = 1
+    if a.dense_allreduce:
+        a.views_per_rank = 1
+    return a
+
+
+def workload_string(a):
+    """Identical in both arms (the driver compares config.workload of the two lines)."""
+    if a.pool == 1:
+        traj = "keyframe 0 of the single-frustum SURVEY 8d scene"
+    else:
+        traj = "keyframes cycling through a %d-pose trajectory (5 deg yaw + 0.25 m per keyframe) over a map sampled on the " \
+               "union of their frusta" % a.pool
+    return "%s: 1 view fwd+bwd per iteration, %d Gaussians, %dx%d, SH deg %d (M=%d), F=%d feature channels, %s" % (
+        a.config, a.P, a.width, a.height, a.deg, (a.deg + 1) ** 2, a.F, traj)
 
 
 def peaks():
+    d, src = {}, "fallback"
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
-        d = json.load(open(path))
-        return dict(hbm_gbs=float(d["hbm_gbs"]), sm_max_mhz=float(d.get("sm_max_mhz", 1965.0)), source="measured")
-    return dict(hbm_gbs=6650.0, sm_max_mhz=1965.0, source="fallback")
+        d, src = json.load(open(path)), "measured"
+    out = dict(hbm_gbs=float(d.get("hbm_gbs", 6650.0)), sm_max_mhz=float(d.get("sm_max_mhz", 1965.0)), source=src)
+    # FP32 FMA pipes: measured by tests/gpu_fma_peak.py on this pool's B200 (dependent-free FFMA chains on all SMs)
+    fp = os.path.join(ROOT, "profiles", "r02_fp32_peak.json")
+    if os.path.exists(fp):
+        out["fp32_tflops"] = float(json.load(open(fp))["fp32_tflops"])
+        out["fp32_source"] = "profiles/r02_fp32_peak.json (measured FFMA microbenchmark, tests/gpu_fma_peak.py)"
+    else:
+        out["fp32_tflops"] = 148 * 128 * 2 * out["sm_max_mhz"] * 1e6 / 1e12
+        out["fp32_source"] = "nominal 148 SM x 128 lanes x 2 x clocks.max.sm (no measured figure found)"
+    return out
 
 
 class ClockSampler:
@@ -119,44 +162,91 @@ class ClockSampler:
                     reasons=sorted(reasons), samples=len(sm))
 
 
-def make_workload(args, view, device, grad_seed=99):
-    """Seeded synthetic scene of the headline shape, tensors resident on `device`."""
-    import numpy as np
-    import torch
-    from gsraster_b200 import scenes
-    sc = scenes.make_scene(args.P, sh_degree=args.deg, F=args.F, seed=1234, W=args.width, H=args.height)
-    cam = scenes.make_camera(args.width, args.height, view)
-    grads = scenes.make_upstream_grads(args.width, args.height, args.F, seed=grad_seed)
-    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(device)
-    d = dict(bg=t(sc.bg), means3D=t(sc.means3D), scales=t(sc.scales), rotations=t(sc.rotations),
-             opacities=t(sc.opacities), shs=t(sc.shs), sh_objs=t(sc.sh_objs), viewmatrix=t(cam.viewmatrix),
-             projmatrix=t(cam.projmatrix), campos=t(cam.campos))
-    g = [t(x) for x in grads]
-    return sc, cam, d, g
+
+
+class Workload:
+    """Seeded synthetic scene + keyframe trajectory, resident on `device`, with the forward / backward
+    calls of the product path (ctypes binding of the C ABI)."""
+
+    def __init__(self, args, device, scene=None, num_poses=None, grad_seed=99):
+        import numpy as np
+        import torch
+        from gsraster_b200 import scenes
+        self.args, self.dev = args, device
+        K = args.pool if num_poses is None else num_poses
+        W, H, F, deg = args.width, args.height, args.F, args.deg
+        if scene is None:
+            scene = (scenes.make_scene(args.P, sh_degree=deg, F=F, seed=1234, W=W, H=H) if K == 1 else
+                     scenes.make_trajectory_scene(args.P, K, sh_degree=deg, F=F, seed=1234, W=W, H=H))
+        self.scene, self.P, self.K = scene, scene.P, K
+        t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(device)
+        self.d = dict(bg=t(scene.bg), means3D=t(scene.means3D), scales=t(scene.scales), rotations=t(scene.rotations),
+                      opacities=t(scene.opacities), shs=t(scene.shs), sh_objs=t(scene.sh_objs))
+        self.cams = [scenes.make_camera(W, H, k) for k in range(K)]
+        self.cam_t = [dict(viewmatrix=t(c.viewmatrix), projmatrix=t(c.projmatrix), campos=t(c.campos)) for c in self.cams]
+        self.g = [t(x) for x in scenes.make_upstream_grads(W, H, F, seed=grad_seed)]
+        self.e = torch.empty(0, device=device)
+        self.M = (deg + 1) ** 2
+
+    def fwd(self, pose, cam_t=None, ext=None):
+        from gsraster_b200 import capi
+        a, d, c, ct = self.args, self.d, self.cams[pose], (cam_t or self.cam_t[pose])
+        return capi.rasterize_gaussians(d["bg"], d["means3D"], self.e, d["opacities"], d["scales"], d["rotations"], 1.0,
+                                        self.e, ct["viewmatrix"], ct["projmatrix"], c.tanfovx, c.tanfovy, a.height, a.width,
+                                        d["shs"], d["sh_objs"], a.deg, ct["campos"], False, False, ext=ext)
+
+    def bwd(self, pose, res, out=None, ext=None, cam_t=None, grads=None, camera_grads=False):
+        from gsraster_b200 import capi
+        a, d, c, ct = self.args, self.d, self.cams[pose], (cam_t or self.cam_t[pose])
+        gd, gc, go = grads or self.g
+        R, depth, color, objects, radii, is_used, gb, bb, ib = res
+        return capi.rasterize_gaussians_backward(d["bg"], d["means3D"], radii, self.e, d["scales"], d["rotations"], 1.0,
+                                                 self.e, ct["viewmatrix"], ct["projmatrix"], c.tanfovx, c.tanfovy, gd, gc,
+                                                 d["shs"], go, d["sh_objs"], a.deg, ct["campos"], gb, R, bb, ib, False,
+                                                 out=out, ext=ext, camera_grads=camera_grads)
+
+    def view_stats(self, pose):
+        """Work counters of one keyframe for the roofline model (outside every timed region)."""
+        import torch
+        from gsraster_b200 import capi
+        a = self.args
+        ext = capi.Ext()
+        res = self.fwd(pose, ext=ext)
+        R = res[0]
+        st = capi.export_state(self.P, a.deg, self.M, a.F, a.width, a.height, R, res[6], res[7], res[8])
+        cp = capi.count_pairs(self.P, a.deg, self.M, a.F, a.width, a.height, R, res[6], res[7], res[8])
+        mask = torch.zeros(self.P, dtype=torch.uint8, device=self.dev)
+        self.bwd(pose, res, ext=capi.Ext(touched_mask=mask))
+        return dict(P=self.P, Pvis=int((res[4] > 0).sum()), R=int(R), Npix=a.width * a.height,
+                    n_eval_fwd=cp["evaluated"], n_blend=cp["blended"], warp_blended=cp["warp_blended"],
+                    n_eval_bwd=int(st["n_contrib"].to(torch.int64).sum()), l1_total=int(ext.stats.l1_total),
+                    touched_rows=int(mask.sum()))
 
 
 def stage_model(args, stats):
-    """ALGORITHMIC bytes / flops per launch of each stage (restated in DESIGN.md).
-    stats: P, Pvis, R, Npix, n_eval_fwd, n_blend, n_eval_bwd."""
-    P, Pv, R, N = stats["P"], stats["Pvis"], stats["R"], stats["Npix"]
+    """ALGORITHMIC bytes / flops per view of each stage (restated in DESIGN.md).
+    stats: P, Pvis, R, Npix, n_eval_fwd, n_blend, n_eval_bwd, l1_total, touched_rows (floats: averages over views)."""
+    P, Pv = stats["P"], stats["Pvis"]
     M, F = (args.deg + 1) ** 2, args.F
-    L1 = stats["l1_total"]
+    L1, U = stats["l1_total"], stats["touched_rows"]
     return {
         "preprocess": ("hbm", Pv * (44 + 12 * M + 84) + (P - Pv) * 20),
         # 4 depth passes over P 8-byte items (histogram read + scatter read + write) + coverage grids (8 B/Gaussian)
         "depth_sort_offsets": ("hbm", P * (4 * 24 + 8)),
-        # supertile lists: 2 sweeps over (depth key 8 + tiles_touched 4 + rect 4) B/Gaussian, 8 B/entry written;
-        # (the per-tile pull, 4 B/instance, now lives in the forward blend and covers only the consumed prefix)
+        # supertile lists: 2 sweeps over (depth key 8 + tiles_touched 4 + rect 4) B/Gaussian, 8 B/entry written
         "binning": ("hbm", P * 32 + L1 * 16),
         "render_fwd": ("fp32", 13 * stats["n_eval_fwd"] + (15 + 2 * (3 + F)) * stats["n_blend"]),
         "render_bwd": ("fp32", 13 * stats["n_eval_bwd"] + (100 + 7 * (3 + F)) * stats["n_blend"]),
-        "preprocess_bwd": ("hbm", Pv * ((95 + 12 * M) + (64 + 12 * M)) + (P - Pv) * 4),
+        # sparse rows: one flag byte per Gaussian + per reached Gaussian the SURVEY 8d row (95 + 12M read, 64 + 12M
+        # written) and its 4(12+F)-byte accumulation row read and re-zeroed
+        "preprocess_bwd": ("hbm", P * 1 + U * ((95 + 12 * M) + (64 + 12 * M) + 8 * (12 + F))),
     }
 
 
-def load_traffic():
-    path = os.path.join(ROOT, "profiles", "traffic.json")
-    return json.load(open(path)) if os.path.exists(path) else {}
+def mean_stats(per_pose, weights):
+    tot = float(sum(weights.values())) or 1.0
+    keys = next(iter(per_pose.values())).keys()
+    return {k: sum(per_pose[p][k] * w for p, w in weights.items()) / tot for k in keys}
 
 
 def run_mine(args, rank, world, local_rank):
@@ -164,134 +254,154 @@ def run_mine(args, rank, world, local_rank):
     import torch.distributed as dist
     from gsraster_b200 import capi, mapping
     dev = torch.device("cuda", local_rank)
-    # Weak scaling needs equal work per rank. The SURVEY 8d scene sampler is centred on view 0, so other poses see a
-    # different visible set (measured: 2.72 ms of kernels for view 0, 3.75 ms for view 1) and the all-reduce would
-    # then time the synthetic scene's load imbalance. Default: every rank renders the view-0 pose with its own
-    # upstream gradients; --distinct-views gives rank r the pose of view r.
-    sc, cam, d, g = make_workload(args, view=rank if args.distinct_views else 0, device=dev, grad_seed=99 + rank)
-    P, W, H, F, deg = args.P, args.width, args.height, args.F, args.deg
-    M = (deg + 1) ** 2
-    e = torch.empty(0, device=dev)
-    sparse = world > 1 and not args.dense_allreduce
-    peer = sparse and not args.nccl_exchange
-    bucket = mapping.GradBucket(P, M, F, dev, symmetric=peer)
+    wl = Workload(args, dev, grad_seed=99 + rank)
+    P, F, M, K, V = wl.P, args.F, wl.M, wl.K, args.views_per_rank
+    dense = world > 1 and args.dense_allreduce
+    peer = world > 1 and not dense and not args.nccl_exchange
+    bucket = mapping.GradBucket(P, M, F, dev, symmetric=peer, copies=2 if peer else 1)
+    ex = None if dense else mapping.SparseGradExchange(bucket, peer_memory=peer, world=world, rank=rank)
     launches = [0]
-    ex = mapping.SparseGradExchange(bucket, peer_memory=peer) if sparse else None
-    if sparse:
-        ex.arm(overlap=not args.no_exchange_overlap)   # touched flags + blend-done event registered with the library
+    timer = [None]
+    rendered = {}           # pose -> how often this rank rendered it while the stage timer was on
+    batch_views = world * V
 
-    def fwd(dd):
-        return capi.rasterize_gaussians(dd["bg"], dd["means3D"], e, dd["opacities"], dd["scales"], dd["rotations"],
-                                        1.0, e, dd["viewmatrix"], dd["projmatrix"], cam.tanfovx, cam.tanfovy, H, W,
-                                        dd["shs"], dd["sh_objs"], deg, dd["campos"], False, False)
-
-    def bwd(dd, res, gd, gc, go):
-        R, depth, color, objects, radii, is_used, gb, bb, ib = res
-        return capi.rasterize_gaussians_backward(dd["bg"], dd["means3D"], radii, e, dd["scales"], dd["rotations"], 1.0,
-                                                 e, dd["viewmatrix"], dd["projmatrix"], cam.tanfovx, cam.tanfovy, gd,
-                                                 gc, dd["shs"], go, dd["sh_objs"], deg, dd["campos"], gb, R, bb, ib,
-                                                 False, out=bucket.views)
-
-    def step():
-        res = fwd(d)
+    # ---- view costs (device time of one forward + backward per pose, measured on rank 0, identical everywhere) and
+    #      the LPT assignment of every distinct batch ----
+    def one_view(pose, ext_b=None):
+        res = wl.fwd(pose, ext=capi.Ext(timer=timer[0]) if timer[0] else None)
         launches[0] += capi.last_launch_count()
-        if sparse:
-            ex.begin_step()
-        bwd(d, res, g[0], g[1], g[2])
+        wl.bwd(pose, res, out=bucket.views, ext=ext_b)
         launches[0] += capi.last_launch_count()
-        if world > 1:
-            if ar_events is not None:
-                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                a.record()
-            if peer:
-                ex.exchange()      # barrier, union of the peers' flags, rank-ordered row sums out of the peers' buckets,
-                                   # barrier: all queued, nothing to read back (capacity = P; consumers take device count)
-            elif sparse:
-                ex.exchange()      # flags all-gather, union scan, row gather, SUM-reduce of the touched rows: all queued
-                ex.finish()        # count read-back (dense fallback if the capacity guess was too small)
-            else:
-                dist.all_reduce(bucket.flat)
-            if ar_events is not None:
-                b.record()
-                ar_events.append((a, b))
+        if timer[0]:
+            rendered[pose] = rendered.get(pose, 0) + 1
         return res
 
-    ar_events = None
+    for p in range(K):  # settle allocators / lazy initialisation on every pose
+        if ex:
+            ex.begin_step()
+        one_view(p, ex.ext(accumulate=False) if ex else None)
+    torch.cuda.synchronize()
+    cost = torch.zeros(K, dtype=torch.float64, device=dev)
+    for p in range(K):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if ex:
+            ex.begin_step()
+        e0.record()
+        one_view(p, ex.ext(accumulate=False) if ex else None)
+        e1.record()
+        e1.synchronize()
+        cost[p] = e0.elapsed_time(e1)
+    if world > 1:
+        dist.broadcast(cost, 0)
+    cost = [float(c) for c in cost.cpu()]
+    assign_cache = {}
+
+    def my_views(step):
+        first = (step * batch_views) % K
+        if first not in assign_cache:
+            batch = [(first + j) % K for j in range(batch_views)]
+            if args.no_lpt or world == 1:
+                a = [batch[r * V:(r + 1) * V] for r in range(world)]
+            else:
+                a = [[batch[i] for i in grp] for grp in mapping.assign_views_lpt([cost[p] for p in batch], world)]
+            assign_cache[first] = a
+        return assign_cache[first][rank]
+
+    ar_events = [None]
+
+    def step(s):
+        views = my_views(s)
+        if ex:
+            ex.begin_step()
+            ext_b = ex.ext(accumulate=len(views) > 1, overlap=True, timer=timer[0])
+        else:
+            ext_b = capi.Ext(timer=timer[0]) if timer[0] else None
+        res = None
+        for p in views:
+            res = one_view(p, ext_b)
+        if world > 1:
+            if ar_events[0] is not None:
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record()
+            if dense:
+                dist.all_reduce(bucket.flat)
+            else:
+                ex.exchange()      # everything queued; peer transport: nothing to read back (consumers take the device count)
+                if not peer:
+                    ex.finish()    # NCCL transport: count read-back (redo at full capacity if the guess was too small)
+            if ar_events[0] is not None:
+                b.record()
+                ar_events[0].append((a, b))
+        return res
 
     def sync_all():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(max(args.warmup, 3)):
-        res = step()
+    step_no = [0]
+
+    def run_steps(n):
+        for _ in range(n):
+            step(step_no[0])
+            step_no[0] += 1
+
+    run_steps(max(args.warmup, 3))
     sync_all()
-    # workload statistics for the roofline model (outside the timed region)
-    R = res[0]
-    l1_total = capi.last_forward_stats()["l1_total"]
-    st = capi.export_state(P, deg, M, F, W, H, R, res[6], res[7], res[8])
-    cp = capi.count_pairs(P, deg, M, F, W, H, R, res[6], res[7], res[8])
-    stats = dict(P=P, Pvis=int((res[4] > 0).sum()), R=int(R), Npix=W * H, n_eval_fwd=cp["evaluated"],
-                 n_blend=cp["blended"], n_eval_bwd=int(st["n_contrib"].to(torch.int64).sum()),
-                 warp_blended=cp["warp_blended"], l1_total=l1_total)
-    del st
-    tm = torch.zeros(P, dtype=torch.uint8, device=dev)
-    capi.set_touched_mask(tm)
-    bwd(d, res, g[0], g[1], g[2])
-    capi.set_touched_mask(ex.touched if sparse else None)
-    touched_rows = int(tm.sum())
-    del tm
     clocks = ClockSampler(local_rank, enabled=(rank == 0))  # rank 0 prints the line; 8 concurrent nvidia-smi slow each other
     clocks.start()  # waits (untimed) for nvidia-smi's first sample, so the sampler is live during the timed region
-    sync_all()      # the other ranks wait here, not inside a device-side barrier
-    for _ in range(3):  # settle the caching allocator again after the statistics pass (untimed, in addition to W)
-        step()
     sync_all()
 
     # ---- timed region 1: inputs resident in HBM, EXACTLY K steps, nothing but the step on the stream ----
+    step_no[0] = 0
     launches[0] = 0
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sync_all()
     clocks.mark()
     ev0.record()
-    for _ in range(args.steps):
-        step()
+    run_steps(args.steps)
     ev1.record()
     sync_all()
     ms = ev0.elapsed_time(ev1)
     n_launch = launches[0]
+    views_rendered = sum(len(my_views(s)) for s in range(args.steps))
 
-    # ---- region 1b: the same K steps again with every stage bracketed by CUDA events (roofline figures). The 12
-    # event records per step serialise the stream and lengthen the num_rendered bubble (measured: +0.4 ms/step),
-    # so this pass is reported separately (ms_per_step_instrumented) and never used for `value`. ----
+    # ---- region 1b: the same K steps again with every stage bracketed by CUDA events (roofline figures). The event
+    # records serialise the stream and lengthen the num_rendered bubble, so this pass is reported separately
+    # (ms_per_step_instrumented) and never used for `value`. ----
     instrument = not os.environ.get("GSR_BENCH_NO_STAGE_TIMING")
-    capi.set_stage_timing(instrument)
-    capi.get_stage_times()
-    capi.get_stage_gaps()
-    ar_events = [] if (world > 1 and instrument) else None
+    step_no[0] = 0
+    if instrument:
+        timer[0] = capi.Timer()
+        ar_events[0] = [] if world > 1 else None
     ev2, ev3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sync_all()
     ev2.record()
-    for _ in range(args.steps if instrument else 0):
-        step()
+    run_steps(args.steps if instrument else 0)
     ev3.record()
     sync_all()
     ms_instr = ev2.elapsed_time(ev3)
-    stage_ms = capi.get_stage_times()
-    gap_ms = capi.get_stage_gaps()
-    capi.set_stage_timing(False)
-    allreduce_ms = sum(a.elapsed_time(b) for a, b in ar_events) / len(ar_events) if ar_events else 1e-9
-    ar_events = None
-    if peer and ex._pending is not None:
-        ex.finish()   # outside every timed region: the union size of the last step, for the report
+    stage_ms, gap_ms = timer[0].read() if instrument else ({k: 0.0 for k in capi.STAGES}, {k: 0.0 for k in capi.STAGES})
+    timer[0] = None
+    allreduce_ms = (sum(a.elapsed_time(b) for a, b in ar_events[0]) / len(ar_events[0])) if ar_events[0] else 1e-9
+    ar_events[0] = None
+    exchange_rows = P
+    if ex is not None and world > 1:
+        if ex._pending is not None:
+            ex.finish()   # outside every timed region: the union size of the last step, for the report
+        exchange_rows = ex.last_rows
 
     # ---- timed region 2: end to end with host buffers ----
     e2e = None
     if not args.no_e2e:
-        e2e = run_e2e(args, cam, d, g, fwd, bwd, bucket, world, dev, sync_all, ex)
+        e2e = run_e2e(args, wl, bucket, ex, world, peer, dense, my_views, sync_all)
     clk = clocks.stop()
+    # workload statistics of the views this rank rendered in the instrumented pass (outside the timed regions)
+    per_pose = {p: wl.view_stats(p) for p in sorted(rendered)} if rendered else {0: wl.view_stats(0)}
+    stats = mean_stats(per_pose, rendered or {0: 1})
     rank_ms = [sum(stage_ms.values())]
-    if world > 1:  # per-rank kernel time (sum of the six stages): shows the skew the all-reduce has to absorb
+    nviews_instr = sum(rendered.values()) or 1
+    if world > 1:  # per-rank kernel time (sum of the six stages): shows the skew the exchange has to absorb
         allr = [torch.zeros(1, device=dev, dtype=torch.float64) for _ in range(world)]
         dist.all_gather(allr, torch.tensor([rank_ms[0]], device=dev, dtype=torch.float64))
         rank_ms = [round(float(x), 3) for x in allr]
@@ -300,80 +410,89 @@ def run_mine(args, rank, world, local_rank):
         ms = float(t[0])
         if e2e:
             e2e["ms"] = float(t[1])
-    return dict(ms=ms, ms_instr=ms_instr, gap_ms=gap_ms, stage_ms=stage_ms, stats=stats, launches=n_launch, e2e=e2e, clocks=clk,
-                bucket_bytes=bucket.nbytes, allreduce_ms=allreduce_ms, rank_ms=rank_ms,
-                exchange_rows=(ex.last_rows if sparse else P), touched_rows=touched_rows)
+    return dict(ms=ms, ms_instr=ms_instr, gap_ms=gap_ms, stage_ms=stage_ms, stats=stats, launches=n_launch, e2e=e2e,
+                clocks=clk, bucket_bytes=bucket.nbytes, allreduce_ms=allreduce_ms, rank_ms=rank_ms,
+                exchange_rows=exchange_rows, nviews_instr=nviews_instr, view_cost_ms=cost,
+                views_per_step=batch_views, assignment={k: v for k, v in assign_cache.items()}, wl=wl, ex=ex, bucket=bucket,
+                views_rendered=views_rendered, per_pose=per_pose)
 
 
-def run_e2e(args, cam, d, g, fwd, bwd, bucket, world, dev, sync_all, ex=None):
-    """Same step through the public API with HOST buffers: per step the keyframe (view matrix,
-    projection matrix, camera centre, ground-truth RGB image) is copied from pinned host memory, an
-    the reference's masked L1 photometric loss (gsr_photometric_loss, lambda_dssim = 0) on the rendered colour produces dL/dcolour on the device, and the loss
-    scalar is read back. Gaussian parameters stay resident (they are the optimiser's state)."""
+def run_e2e(args, wl, bucket, ex, world, peer, dense, my_views, sync_all):
+    """The same step through the public API with HOST buffers: per view the keyframe (view matrix, projection matrix,
+    camera centre, ground-truth RGB image) is copied from pinned host memory, the reference's masked L1 photometric
+    loss (gsr_photometric_loss, lambda_dssim = 0) on the rendered colour produces dL/dcolour on the device, and the
+    step's loss values are read back. Gaussian parameters stay resident (they are the optimiser's state)."""
     import torch
     import torch.distributed as dist
-    W, H = args.width, args.height
+    from gsraster_b200 import capi, losses
+    W, H, dev = args.width, args.height, wl.dev
     pin = lambda t: t.detach().cpu().pin_memory()
-    h_view, h_proj, h_campos = pin(d["viewmatrix"]), pin(d["projmatrix"]), pin(d["campos"])
+    h_cam = [{k: pin(v) for k, v in ct.items()} for ct in wl.cam_t]
     torch.manual_seed(7)
     h_gt = torch.rand(3, H, W).pin_memory()
-    dd = dict(d)
-    dd["viewmatrix"], dd["projmatrix"], dd["campos"] = (torch.empty_like(d["viewmatrix"]),
-                                                         torch.empty_like(d["projmatrix"]),
-                                                         torch.empty_like(d["campos"]))
-    gt = [torch.empty(3, H, W, device=dev) for _ in range(2)]  # double-buffered: the copy of step i overlaps step i's forward
-    h_loss = [torch.zeros(1).pin_memory() for _ in range(2)]
-    h2d = sum(t.numel() * 4 for t in (h_view, h_proj, h_campos, h_gt))
-    from gsraster_b200 import losses
+    NB = 4   # ring of device-side keyframe slots: the copies of view i+1 overlap the work of view i
+    cam_d = [{k: torch.empty_like(v) for k, v in wl.cam_t[0].items()} for _ in range(NB)]
+    gt = [torch.empty(3, H, W, device=dev) for _ in range(NB)]
+    h2d_view = sum(t.numel() * 4 for t in h_cam[0].values()) + h_gt.numel() * 4
     ploss = losses.PhotometricLoss(H, W, 0.0, device=dev)  # lambda_dssim = 0: masked L1 (the SSIM kernels are measured in loss_n2)
-    loss3 = [torch.empty(3, device=dev) for _ in range(2)]
-    grad_buf = torch.empty(3, H, W, device=dev)
+    loss3 = [torch.empty(3, device=dev) for _ in range(NB)]
+    grad_buf = [torch.empty(3, H, W, device=dev) for _ in range(2)]
     copy_stream = torch.cuda.Stream(device=dev)
-    ev_gt = [torch.cuda.Event() for _ in range(2)]
-    ev_free = [torch.cuda.Event() for _ in range(2)]
-    ev_loss = [torch.cuda.Event() for _ in range(2)]
+    ev_in = [torch.cuda.Event() for _ in range(NB)]
+    ev_free = [torch.cuda.Event() for _ in range(NB)]
     main = torch.cuda.current_stream()
     for e_ in ev_free:
         e_.record(main)
-    state = dict(i=0, last=0.0)
+    V = args.views_per_rank
+    h_loss = [torch.zeros(8 * max(V, 1) + 8).pin_memory() for _ in range(2)]
+    d_loss = [torch.zeros(8 * max(V, 1) + 8, device=dev) for _ in range(2)]
+    ev_loss = [torch.cuda.Event() for _ in range(2)]
+    state = dict(i=0, slot=0, last=0.0)
 
     def step():
         i = state["i"]
-        k = i & 1
-        # ground-truth image: pinned host -> device on the copy stream, concurrent with this step's forward
-        copy_stream.wait_event(ev_free[k])
-        with torch.cuda.stream(copy_stream):
-            gt[k].copy_(h_gt, non_blocking=True)
-            ev_gt[k].record(copy_stream)
-        dd["viewmatrix"].copy_(h_view, non_blocking=True)
-        dd["projmatrix"].copy_(h_proj, non_blocking=True)
-        dd["campos"].copy_(h_campos, non_blocking=True)
-        res = fwd(dd)
-        main.wait_event(ev_gt[k])
-        # masked L1 photometric loss (loss_utils.py:17-20), value and dL/dcolour in one fused pass
-        out3, grad_c = ploss(res[2], gt[k], out=loss3[k], grad_out=grad_buf)
-        loss = out3[0:1]
-        ev_free[k].record(main)
-        if ex is not None:
+        k2 = i & 1
+        views = my_views(i)
+        if ex:
             ex.begin_step()
-        bwd(dd, res, g[0], grad_c, g[2])
+            ext_b = ex.ext(accumulate=len(views) > 1, overlap=True)
+        else:
+            ext_b = None
+        for j, p in enumerate(views):
+            k = state["slot"] % NB
+            state["slot"] += 1
+            # keyframe: pinned host -> device on the copy stream, concurrent with the previous view's kernels
+            copy_stream.wait_event(ev_free[k])
+            with torch.cuda.stream(copy_stream):
+                gt[k].copy_(h_gt, non_blocking=True)
+                for name in cam_d[k]:
+                    cam_d[k][name].copy_(h_cam[p][name], non_blocking=True)
+                ev_in[k].record(copy_stream)
+            main.wait_event(ev_in[k])
+            res = wl.fwd(p, cam_t=cam_d[k])
+            # masked L1 photometric loss (loss_utils.py:17-20), value and dL/dcolour in one fused pass
+            out3, grad_c = ploss(res[2], gt[k], out=loss3[k], grad_out=grad_buf[j & 1])
+            d_loss[k2][j:j + 1].copy_(out3[0:1])
+            wl.bwd(p, res, out=bucket.views, ext=ext_b, cam_t=cam_d[k], grads=(wl.g[0], grad_c, wl.g[2]))
+            ev_free[k].record(main)
         if world > 1:
-            if ex is not None:
-                ex.exchange()
-                if not ex.peer:
-                    ex.finish()
-            else:
+            if dense:
                 dist.all_reduce(bucket.flat)
-        h_loss[k].copy_(loss.reshape(1), non_blocking=True)  # 4-byte D2H of the step's result
-        ev_loss[k].record(main)
-        if i > 0:  # read the previous step's loss: keeps one step in flight instead of draining the GPU
-            ev_loss[k ^ 1].synchronize()
-            state["last"] = float(h_loss[k ^ 1][0])
+            else:
+                ex.exchange()
+                if not peer:
+                    ex.finish()
+        h_loss[k2].copy_(d_loss[k2], non_blocking=True)   # D2H of the step's results
+        ev_loss[k2].record(main)
+        if i > 0:  # read the previous step's losses: keeps one step in flight instead of draining the GPU
+            ev_loss[k2 ^ 1].synchronize()
+            state["last"] = float(h_loss[k2 ^ 1][0])
         state["i"] = i + 1
         return state["last"]
 
     for _ in range(3):
         step()
+    state["i"] = 0
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sync_all()
     ev0.record()
@@ -383,7 +502,154 @@ def run_e2e(args, cam, d, g, fwd, bwd, bucket, world, dev, sync_all, ex=None):
     loss = float(h_loss[(state["i"] - 1) & 1][0])
     ev1.record()
     sync_all()
-    return dict(ms=ev0.elapsed_time(ev1), h2d=h2d, d2h=4, loss=loss)
+    if ex is not None and world > 1 and ex._pending is not None:
+        ex.finish()
+    return dict(ms=ev0.elapsed_time(ev1), h2d=h2d_view * V, d2h=int(h_loss[0].numel() * 4), loss=loss)
+
+
+def timed(fn, n, warm=3):
+    import torch
+    for _ in range(warm):
+        fn()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(n):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / n
+
+
+def single_view_measure(args, wl, pose, hbm_gbs, fp32_tflops, steps=20, sparse=True):
+    """One keyframe, forward + backward, the way `value` runs it (sparse rows + row workspace), with the stage table."""
+    import torch
+    from gsraster_b200 import capi, mapping
+    bucket = mapping.GradBucket(wl.P, wl.M, args.F, wl.dev)
+    mask = torch.zeros(wl.P, dtype=torch.uint8, device=wl.dev)
+    ws = capi.new_row_workspace(wl.P, args.F, wl.dev)
+    tm = [None]
+
+    def it():
+        res = wl.fwd(pose, ext=capi.Ext(timer=tm[0]) if tm[0] else None)
+        if sparse:
+            mask.zero_()
+            wl.bwd(pose, res, out=bucket.views, ext=capi.Ext(touched_mask=mask, sparse_rows=True, row_workspace=ws, timer=tm[0]))
+        else:
+            wl.bwd(pose, res, out=bucket.views, ext=capi.Ext(timer=tm[0]) if tm[0] else None)
+
+    ms = timed(it, steps)
+    tm[0] = capi.Timer()
+    for _ in range(steps):
+        it()
+    torch.cuda.synchronize()
+    stage_ms, _ = tm[0].read()
+    tm[0] = None
+    st = wl.view_stats(pose)
+    model = stage_model(args, st)
+    stages = {}
+    for name, (bound, work) in model.items():
+        t = max(stage_ms[name] / steps * 1e-3, 1e-12)
+        ach, peak = (work / t / 1e9, hbm_gbs) if bound == "hbm" else (work / t / 1e12, fp32_tflops)
+        stages[name] = dict(ms=round(t * 1e3, 4), frac=round(ach / peak, 4))
+    return dict(ms_per_iter=round(ms, 4), iters_per_s=round(1e3 / ms, 2), R=st["R"], Pvis=st["Pvis"],
+                touched_rows=st["touched_rows"], touched_frac_of_visible=round(st["touched_rows"] / max(st["Pvis"], 1), 4),
+                n_eval_over_R=round(st["n_eval_fwd"] / max(st["R"], 1) / 256.0, 4), n_eval=st["n_eval_fwd"],
+                n_blend=st["n_blend"], stages=stages)
+
+
+def workloads_leg(args, dev, pk):
+    """Single-view workloads beside the headline (the headline scene is front-loaded): the round-1 SURVEY 8d
+    scene, BASELINE config 2, the 'trained-like' x3 scene and a scene whose pixels do not saturate. `--impl reference`
+    prints the reference's time on the same scenes under the same names."""
+    import copy
+    from gsraster_b200 import scenes
+    out = {}
+    for name in scenes.WORKLOADS:
+        a = copy.copy(args)
+        a.P, a.pool = scenes.WORKLOADS[name]["P"], 1
+        try:
+            wl = Workload(a, dev, scene=scenes.make_workload_scene(name, args.deg, args.F, args.width, args.height), num_poses=1)
+            out[name] = single_view_measure(a, wl, 0, pk["hbm_gbs"], pk["fp32_tflops"], steps=10)
+            out[name]["note"] = scenes.WORKLOADS[name]["note"]
+            del wl
+        except Exception as ex:
+            out[name] = dict(error=repr(ex)[:200])
+    return out
+
+
+def render_fps_leg(wl, steps=32):
+    """BASELINE metric (ii), render FPS: forward only (the reference's render path, scripts/gaussian_splatting.py:331-377
+    -> render_4), cycling through the trajectory's keyframes."""
+    k = [0]
+
+    def it():
+        wl.fwd(k[0] % wl.K)
+        k[0] += 1
+
+    ms = timed(it, steps)
+    return dict(ms_per_frame=round(ms, 4), fps=round(1e3 / ms, 1),
+                note="forward only (gsr_forward) over the trajectory's keyframes, inputs resident")
+
+
+def dropin_dense_leg(args, wl, steps=32):
+    """The reference's output contract (all eleven gradient tensors fully written, zeros for Gaussians without a
+    gradient; no persistent workspace): what a caller of the drop-in diff_gaussian_rasterization module gets."""
+    from gsraster_b200 import mapping
+    bucket = mapping.GradBucket(wl.P, wl.M, args.F, wl.dev)
+    k = [0]
+
+    def it():
+        p = k[0] % wl.K
+        k[0] += 1
+        wl.bwd(p, wl.fwd(p), out=bucket.views)
+
+    ms = timed(it, steps)
+    return dict(ms_per_iter=round(ms, 4), iters_per_s=round(1e3 / ms, 2),
+                note="forward + backward with the reference's dense output contract (gsr_ext = NULL) over the same keyframes")
+
+
+def pose_backward_leg(args, wl, steps=32):
+    """BASELINE config 5: per-frame camera-pose gradient backward (extension; gsr_backward_pose) on the map."""
+    from gsraster_b200 import capi
+    res = [wl.fwd(p) for p in range(min(wl.K, 4))]
+    k = [0]
+
+    def full():
+        p = k[0] % len(res)
+        k[0] += 1
+        wl.bwd(p, res[p], camera_grads=True)
+
+    def track():
+        p = k[0] % len(res)
+        k[0] += 1
+        wl.bwd(p, res[p], camera_grads=True, ext=capi.Ext(tracking=True))
+
+    ms_full, ms_track = timed(full, steps), timed(track, steps)
+    return dict(tracking_mode_ms=round(ms_track, 4), full_backward_plus_pose_ms=round(ms_full, 4),
+                note="gsr_backward_pose on %d Gaussians: tracking mode (gsr_ext::tracking: no feature reductions, no "
+                     "per-Gaussian outputs) vs the full mapping backward + the 27 camera sums" % wl.P)
+
+
+def knn_leg(hbm_gbs, P=5_000_000):
+    """BASELINE config 5 / metric (iv): simple-knn distCUDA2 over 5M LiDAR points; the reference build
+    (oracle/_ref/libref_knn.so: KNN/simple_knn.cu:185-221) timed beside it when it was shipped."""
+    import ctypes as C
+    import numpy as np
+    import torch
+    from gsraster_b200 import capi, scenes
+    pts = torch.from_numpy(scenes.make_points(P, seed=55)).cuda()
+    ms = timed(lambda: capi.distCUDA2(pts), 5, warm=2)
+    out = dict(points=P, ms=round(ms, 3), mpoints_per_s=round(P / ms / 1e3, 1),
+               frac_of_hbm_at_108B_per_point=round(108.0 * P / ms / 1e6 / hbm_gbs, 4))
+    ref = os.path.join(ROOT, "oracle", "_ref", "libref_knn.so")
+    if os.path.exists(ref):
+        L = C.CDLL(ref)
+        L.ref_knn.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
+        o = torch.zeros(P, device="cuda")
+        rms = timed(lambda: L.ref_knn(P, pts.data_ptr(), o.data_ptr()), 3, warm=1)
+        out.update(reference_ms=round(rms, 3), speedup=round(rms / ms, 2))
+    return out
 
 
 def optimizer_leg(args, touched_rows, hbm_gbs):
@@ -611,15 +877,16 @@ def store_leg(args):
 
 
 def cpu_baseline(args, threads=None):
-    """CPU oracle port (oracle/oracle.cpp, OpenMP) timed on the host cores on a bounded sample."""
-    import numpy as np
+    """CPU oracle port (oracle/oracle.cpp, OpenMP) timed on the host cores on a bounded sample of the headline."""
     from gsraster_b200 import scenes
     from oracle import pyoracle as po
     po.build()
     cores = po.num_threads()
     # bounded sample: the full camera/resolution with P scaled so the sample stays in the 10-30 s range
     Ps = args.P if cores >= 32 else min(args.P, 250_000)
-    sc = scenes.make_scene(Ps, sh_degree=args.deg, F=args.F, seed=1234, W=args.width, H=args.height)
+    K = args.pool
+    sc = (scenes.make_scene(Ps, sh_degree=args.deg, F=args.F, seed=1234, W=args.width, H=args.height) if K == 1 else
+          scenes.make_trajectory_scene(Ps, K, sh_degree=args.deg, F=args.F, seed=1234, W=args.width, H=args.height))
     cam = scenes.make_camera(args.width, args.height, 0)
     grads = scenes.make_upstream_grads(args.width, args.height, args.F)
     pr = po.Problem(sc, cam)
@@ -627,58 +894,91 @@ def cpu_baseline(args, threads=None):
     st = po.forward(pr)
     po.backward(pr, st, *grads)
     dt = time.time() - t0
-    sample = "1 fwd+bwd iteration, %d Gaussians (of %d), %dx%d, deg %d, F=%d, R=%d" % (
+    sample = "1 fwd+bwd iteration on keyframe 0, %d Gaussians (of %d), %dx%d, deg %d, F=%d, R=%d" % (
         Ps, args.P, args.width, args.height, args.deg, args.F, st["R"])
-    return dict(value=1.0 / dt, unit=UNIT, cores=cores, kind="port", sample=sample, seconds=dt)
+    return dict(value=1.0 / dt, unit=UNIT, cores=cores, kind="port", sample=sample, seconds=dt,
+                sample_scale=round(Ps / float(args.P), 4))
 
 
 def run_reference(args):
-    """Reference arm: unmodified reference CUDA rasterizer (oracle/_ref) on GPU 0, same workload."""
+    """Reference arm: unmodified reference CUDA rasterizer (oracle/_ref) on GPU 0, same keyframes, same scenes."""
+    import copy
     import torch
+    from gsraster_b200 import scenes
     from oracle import refcuda
-    cfg = dict(workload="headline: 1 view fwd+bwd, %d Gaussians, %dx%d, SH deg %d, F=%d" % (
-        args.P, args.width, args.height, args.deg, args.F), l2="inputs (>=300 MB) larger than the 126 MB L2")
+    cfg = dict(workload=workload_string(args), l2="inputs (>=300 MB of Gaussian parameters) larger than the 126 MB L2; no flush needed")
     if not (torch.cuda.is_available() and refcuda.available(args.F)):
         cb = cpu_baseline(args)
         ms = 1e3 * cb["seconds"]
         return dict(metric=METRIC, value=cb["value"], unit=UNIT, n_gpus=0, steps=1, warmup=0, ms_per_step=ms,
                     higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
-                    config=cfg, impl="reference", cpu_baseline={k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+                    config=cfg, impl="reference",
+                    cpu_baseline={k: cb[k] for k in ("value", "unit", "cores", "kind", "sample", "sample_scale")},
                     e2e=dict(value=cb["value"], unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0),
                     note="oracle/_ref (reference CUDA build) not available: CPU oracle port timed instead")
     dev = torch.device("cuda", 0)
     torch.cuda.set_device(dev)
-    sc, cam, d, g = make_workload(args, view=0, device=dev)
     ref = refcuda.RefRasterizer(args.F)
     W, H = args.width, args.height
 
-    def step():
-        R, depth, color, objects, radii, is_used, bufs = ref.forward(d, W, H, cam.tanfovx, cam.tanfovy, args.deg)
-        ref.backward(d, W, H, cam.tanfovx, cam.tanfovy, args.deg, R, radii, bufs, g[0], g[1], g[2])
-        return R
+    def measure(wl, iters, warm):
+        Rs = []
+        k = [0]
 
-    for _ in range(max(args.warmup, 3)):
-        R = step()
-    torch.cuda.synchronize()
+        def it():
+            p = k[0] % wl.K
+            k[0] += 1
+            d = dict(wl.d, **wl.cam_t[p])
+            c = wl.cams[p]
+            R, depth, color, objects, radii, is_used, bufs = ref.forward(d, W, H, c.tanfovx, c.tanfovy, args.deg)
+            ref.backward(d, W, H, c.tanfovx, c.tanfovy, args.deg, R, radii, bufs, wl.g[0], wl.g[1], wl.g[2])
+            Rs.append(int(R))
+
+        for _ in range(warm):
+            it()
+        k[0] = 0
+        del Rs[:]
+        torch.cuda.synchronize()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        for _ in range(iters):
+            it()
+        ev1.record()
+        torch.cuda.synchronize()
+        return ev0.elapsed_time(ev1) / max(iters, 1), Rs
+
+    wl = Workload(args, dev)
+    V = args.views_per_rank
     clocks = ClockSampler(0)
+    measure(wl, 0, max(args.warmup, 3) * V)
     clocks.start()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     clocks.mark()
-    ev0.record()
-    for _ in range(args.steps):
-        step()
-    ev1.record()
-    torch.cuda.synchronize()
-    ms = ev0.elapsed_time(ev1)
+    ms_view, Rs = measure(wl, args.steps * V, 0)     # the same keyframes, in the same order, as `--impl mine` at N = 1
     clk = clocks.stop()
-    value = args.steps / (ms * 1e-3)
-    return dict(metric=METRIC, value=value, unit=UNIT, n_gpus=1, steps=args.steps, warmup=max(args.warmup, 3),
-                ms_per_step=ms / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32",
-                data="synthetic", config=dict(cfg, R=int(R)), impl="reference", clocks=clk,
-                cpu_baseline=dict(value=value, unit=UNIT, cores=0, kind="reference",
-                                  sample="unmodified reference CUDA rasterizer built for sm_100a (oracle/_ref), "
-                                         "run on GPU 0: the reference has no CPU implementation of this path"),
-                e2e=dict(value=value, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0))
+    value = 1e3 / ms_view
+    out = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=1, steps=args.steps, warmup=max(args.warmup, 3),
+               ms_per_step=ms_view * V, higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32",
+               data="synthetic", config=dict(cfg, views_per_step=V, R_mean=int(sum(Rs) / max(len(Rs), 1))), impl="reference",
+               clocks=clk,
+               cpu_baseline=dict(value=value, unit=UNIT, cores=0, kind="reference",
+                                 sample="unmodified reference CUDA rasterizer built for sm_100a (oracle/_ref), "
+                                        "run on GPU 0: the reference has no CPU implementation of this path"),
+               e2e=dict(value=value, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0))
+    del wl
+    if not args.no_legs and args.config == "headline":
+        wls = {}
+        for name in scenes.WORKLOADS:
+            a = copy.copy(args)
+            a.P, a.pool = scenes.WORKLOADS[name]["P"], 1
+            try:
+                w1 = Workload(a, dev, scene=scenes.make_workload_scene(name, args.deg, args.F, W, H), num_poses=1)
+                ms1, R1 = measure(w1, 5, 2)
+                wls[name] = dict(ms_per_iter=round(ms1, 3), iters_per_s=round(1e3 / ms1, 3), R=R1[0])
+                del w1
+            except Exception as ex:
+                wls[name] = dict(error=repr(ex)[:200])
+        out["workloads"] = wls
+    return out
 
 
 def main():
@@ -711,82 +1011,98 @@ def main():
     pk = peaks()
     K = args.steps
     ms = r["ms"]
-    value = world * K / (ms * 1e-3)
-    # per-stage roofline (CUDA events around every stage in the instrumented pass, per launch = per step)
+    nv = r["views_per_step"]
+    value = nv * K / (ms * 1e-3)
+    # per-stage roofline (CUDA events around every stage in the instrumented pass, per view)
     model = stage_model(args, r["stats"])
-    fp32_peak = 148 * 128 * 2 * pk["sm_max_mhz"] * 1e6 / 1e12  # TFLOP/s at clocks.max.sm, non-tensor FMA pipes
-    traffic = load_traffic()
     stages = {}
     for name, (bound, work) in model.items():
-        t = max(r["stage_ms"][name] / K * 1e-3, 1e-12)
+        t = max(r["stage_ms"][name] / r["nviews_instr"] * 1e-3, 1e-12)
         if bound == "hbm":
             ach, peak, unit = work / t / 1e9, pk["hbm_gbs"], "GB/s"
         else:
-            ach, peak, unit = work / t / 1e12, fp32_peak, "TFLOP/s"
+            ach, peak, unit = work / t / 1e12, pk["fp32_tflops"], "TFLOP/s"
         stages[name] = dict(ms=round(t * 1e3, 4), bound=bound, achieved=round(ach, 3), peak=round(peak, 1), unit=unit,
-                            frac=round(ach / peak, 4), work=int(work), traffic=traffic.get(name))
+                            frac=round(ach / peak, 4), work=int(work))
     top = max(stages, key=lambda k: stages[k]["ms"])
-    roof = dict(kernel=top, **{k: stages[top][k] for k in ("bound", "achieved", "peak", "unit", "frac", "traffic")},
-                peak_source=("MEASURED_PEAKS.json hbm_gbs" if stages[top]["bound"] == "hbm" else
-                             "148 SM x 128 FMA lanes x 2 x clocks.max.sm (no fp32 figure in MEASURED_PEAKS.json)") +
-                            " (%s)" % pk["source"])
+    traffic = {}
+    tpath = os.path.join(ROOT, "profiles", "r02_traffic.json")
+    if os.path.exists(tpath):
+        traffic = json.load(open(tpath))
+    roof = dict(kernel=top, **{k: stages[top][k] for k in ("bound", "achieved", "peak", "unit", "frac")},
+                traffic=traffic.get(top, {}).get("dram_bytes"), work_executed=traffic.get(top, {}).get("work_executed"),
+                frac_executed=(round(traffic[top]["work_executed"] / (stages[top]["ms"] * 1e-3) / 1e12 / stages[top]["peak"], 4)
+                               if traffic.get(top, {}).get("work_executed") and stages[top]["bound"] == "fp32" else None),
+                per="one view (forward + backward) of the instrumented pass, mean over the keyframes rank 0 rendered",
+                peak_source=("MEASURED_PEAKS.json hbm_gbs (%s)" % pk["source"]) if stages[top]["bound"] == "hbm" else pk["fp32_source"])
+    if world == 1:
+        par = "single GPU, %d views per step" % nv
+    else:
+        xb = r["exchange_rows"] * (r["bucket_bytes"] // args.P)
+        mode = ("1 NCCL all-reduce of the dense %d MB bucket per step" % (r["bucket_bytes"] // 1000000) if args.dense_allreduce else
+                ("sparse gradient exchange, NCCL transport (flags all-gather + SUM-reduce of the union's rows)" if args.nccl_exchange
+                 else "sparse gradient exchange over peer memory (no collective library call: one signal/wait handshake "
+                      "kernel, union of the peers' touched flags read in place, rank-ordered sum of the union's rows out of "
+                      "the peers' double-buffered buckets over NVLink)") + ": %d touched rows (of %d) = %.1f MB per step" % (
+                     r["exchange_rows"], args.P, xb / 1e6))
+        par = "view-data-parallel x%d, %s, %d views per rank per step, %s, replicated Gaussians, %s" % (
+            world, "same pose on every rank" if args.same_pose else "distinct keyframe poses on every rank (pose of view r on rank r)",
+            args.views_per_rank, "contiguous view blocks" if args.no_lpt else "views assigned longest-processing-time-first", mode)
     out = dict(metric=METRIC, value=round(value, 4), unit=UNIT, n_gpus=world, steps=K, warmup=max(args.warmup, 3),
                ms_per_step=round(ms / K, 4), higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32",
                data="synthetic",
-               config=dict(workload="headline: 1 view fwd+bwd per GPU per step, %d Gaussians, %dx%d, SH deg %d (M=%d), "
-                                    "F=%d feature channels" % (args.P, args.width, args.height, args.deg,
-                                                               (args.deg + 1) ** 2, args.F),
-                           parallelism="view-data-parallel x%d (%s), replicated Gaussians, %s" % (
-                               world, "pose of view r on rank r" if args.distinct_views else
-                               "same pose, per-rank upstream gradients: equal work per rank",
-                               "1 NCCL all-reduce of the dense %d MB bucket/step" % (r["bucket_bytes"] // 1000000)
-                               if args.dense_allreduce else
-                               ("sparse gradient exchange: NCCL all-gather of the touched flags + SUM-reduce of the " if args.nccl_exchange else
-                                "sparse gradient exchange over peer memory (no collective library call: barrier, union of the "
-                                "peers' touched flags read in place, rank-ordered sum of the union's rows out of the peers' "
-                                "buckets over NVLink): ") +
-                               "%d touched rows (of %d) = %d MB/step" % (
-                                   r["exchange_rows"], args.P,
-                                   r["exchange_rows"] * (r["bucket_bytes"] // args.P) // 1000000)) if world > 1 else "single GPU",
+               config=dict(workload=workload_string(args), parallelism=par, views_per_step=nv,
                            l2="inputs (>=300 MB of Gaussian parameters) larger than the 126 MB L2; no flush needed",
-                           **{k: r["stats"][k] for k in ("Pvis", "R", "l1_total", "n_eval_fwd", "n_blend", "warp_blended", "n_eval_bwd")}),
+                           gradient_outputs="sparse rows (gsr_ext::sparse_rows + persistent row workspace): rows of the "
+                                            "Gaussians the views reached + their flags; the dense reference contract is "
+                                            "timed in dropin_dense",
+                           view_cost_ms=[round(c, 3) for c in r["view_cost_ms"]],
+                           **{k: int(r["stats"][k]) for k in ("Pvis", "R", "l1_total", "n_eval_fwd", "n_blend", "warp_blended",
+                                                              "n_eval_bwd", "touched_rows")}),
                gpu_launches=r["launches"], clocks=r["clocks"], roofline=roof, stages=stages,
                ms_per_step_instrumented=round(r["ms_instr"] / K, 4),
-               idle_before_stage_ms={k: round(v / K, 4) for k, v in r["gap_ms"].items()})
+               idle_before_stage_ms={k: round(v / r["nviews_instr"], 4) for k, v in r["gap_ms"].items()})
     if world > 1:
         xbytes = r["exchange_rows"] * (r["bucket_bytes"] // args.P)
         out["allreduce"] = dict(ms=round(r["allreduce_ms"], 4), bytes=xbytes, dense_bytes=r["bucket_bytes"],
                                 rows=r["exchange_rows"], mode="dense" if args.dense_allreduce else "sparse",
                                 busbw_gbs=round(2 * (world - 1) / world * xbytes / r["allreduce_ms"] / 1e6, 1),
-                                rank_kernel_ms_per_step=[round(x / K, 4) for x in r["rank_ms"]])
+                                rank_kernel_ms_per_step=[round(x / K, 4) for x in r["rank_ms"]],
+                                assignment={str(k): v for k, v in r["assignment"].items()})
     if r["e2e"]:
         e = r["e2e"]
-        out["e2e"] = dict(value=round(world * K / (e["ms"] * 1e-3), 4), unit=UNIT, h2d_bytes_per_step=e["h2d"],
+        out["e2e"] = dict(value=round(nv * K / (e["ms"] * 1e-3), 4), unit=UNIT, h2d_bytes_per_step=e["h2d"],
                           d2h_bytes_per_step=e["d2h"], ms_per_step=round(e["ms"] / K, 4))
-    if world == 1:
-        try:
-            out["optimizer_n1"] = optimizer_leg(args, r["touched_rows"], pk["hbm_gbs"])
-        except Exception as ex:  # the leg is informative only; the headline line must still be printed
-            out["optimizer_n1"] = dict(error=repr(ex)[:200])
-        try:
-            out["loss_n2"] = loss_leg(args, pk["hbm_gbs"])
-        except Exception as ex:
-            out["loss_n2"] = dict(error=repr(ex)[:200])
-        try:
-            out["feature_loss_n2"] = feature_loss_leg(args, pk["hbm_gbs"])
-        except Exception as ex:
-            out["feature_loss_n2"] = dict(error=repr(ex)[:200])
-        try:
-            out["cls3d_n4"] = cls3d_leg(args)
-        except Exception as ex:
-            out["cls3d_n4"] = dict(error=repr(ex)[:200])
-        try:
-            out["store_n3"] = store_leg(args)
-        except Exception as ex:
-            out["store_n3"] = dict(error=repr(ex)[:200])
+    if world == 1 and not args.no_legs:
+        wl = r["wl"]
+        dev = wl.dev
+
+        def leg(name, fn):
+            try:
+                out[name] = fn()
+            except Exception as ex:  # the legs are informative only; the headline line must still be printed
+                out[name] = dict(error=repr(ex)[:200])
+
+        leg("render_fps", lambda: render_fps_leg(wl))
+        leg("dropin_dense", lambda: dropin_dense_leg(args, wl))
+        leg("pose_backward", lambda: pose_backward_leg(args, wl))
+        out["pose_backward_ms"] = out["pose_backward"].get("tracking_mode_ms")
+        leg("optimizer_n1", lambda: optimizer_leg(args, int(r["stats"]["touched_rows"]), pk["hbm_gbs"]))
+        leg("loss_n2", lambda: loss_leg(args, pk["hbm_gbs"]))
+        leg("feature_loss_n2", lambda: feature_loss_leg(args, pk["hbm_gbs"]))
+        leg("cls3d_n4", lambda: cls3d_leg(args))
+        leg("store_n3", lambda: store_leg(args))
+        del wl
+        r["wl"] = r["ex"] = r["bucket"] = None
+        torch.cuda.empty_cache()
+        leg("knn", lambda: knn_leg(pk["hbm_gbs"]))
+        if args.config == "headline":
+            torch.cuda.empty_cache()
+            leg("workloads", lambda: workloads_leg(args, dev, pk))
     if world == 1 and not args.no_cpu_baseline:
         cb = cpu_baseline(args)
-        out["cpu_baseline"] = {k: (round(cb[k], 5) if k == "value" else cb[k]) for k in ("value", "unit", "cores", "kind", "sample")}
+        out["cpu_baseline"] = {k: (round(cb[k], 5) if k == "value" else cb[k])
+                               for k in ("value", "unit", "cores", "kind", "sample", "sample_scale")}
     print(json.dumps(out), flush=True)
     if world > 1:
         torch.distributed.destroy_process_group()

@@ -211,9 +211,12 @@ int gsr_exchange_compact(const uint8_t* flags, int nranks, int P, int Ppad, int 
 /* Row gather (scatter = 0): compact[t][r][:] = dense[t][idx[r]][:] for r < min(*count, cap), zeros up to cap (scatter = 2:
  * the same without the zero fill, rows >= *count are left untouched: stream compaction); or row
  * scatter (scatter = 1): dense[t][idx[r]][:] = compact[t][r][:]. t < ntensors <= 8 tensors of floats_per_row[t] floats per
- * Gaussian; the pointer arrays are HOST arrays of device pointers. */
+ * Gaussian; the pointer arrays are HOST arrays of device pointers. row_mask (gather modes, may be NULL): dense row g is
+ * read only where row_mask[g] != 0 and gathered as zeros elsewhere (the dense tensors of a sparse-row backward,
+ * gsr_ext::sparse_rows, hold stale data in the rows their touched flag does not cover). */
 int gsr_exchange_rows(int scatter, int ntensors, const float* const* dense, float* const* compact,
-                      const int* floats_per_row, const int* idx, const int* count, int cap, void* stream);
+                      const int* floats_per_row, const int* idx, const int* count, int cap, const uint8_t* row_mask,
+                      void* stream);
 /* Peer-memory version of the exchange (one process per GPU, buffers mapped into every rank, e.g. CUDA VMM / symmetric
  * memory over NVLink): no collective library call on the data path.
  * gsr_exchange_compact_peers: as gsr_exchange_compact, but flags[r] (HOST array of nranks <= 16 device pointers, 4-byte

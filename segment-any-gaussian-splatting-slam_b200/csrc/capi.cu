@@ -43,7 +43,7 @@ void launch_signal_wait(void* const* pads, int nranks, int rank, uint32_t seq, u
 void launch_prune_flags(const float* opacity, const float* scaling, int P, float min_opacity, float max_scale,
                         uint8_t* keep, cudaStream_t s);
 void launch_rows(int scatter, int ntensors, const float* const* src, float* const* dst, const int* n, const int* idx,
-                 const int* count, int cap, cudaStream_t s);
+                 const int* count, int cap, const uint8_t* row_mask, cudaStream_t s);
 void launch_export_keys(int T, const uint2* ranges, const uint32_t* point_list, const float4* rec, uint64_t* keys,
                         cudaStream_t s);
 }
@@ -471,16 +471,16 @@ int gsr_exchange_compact(const uint8_t* flags, int nranks, int P, int Ppad, int 
 }
 
 int gsr_exchange_rows(int scatter, int ntensors, const float* const* dense, float* const* compact, const int* floats_per_row,
-                      const int* idx, const int* count, int cap, void* stream_) {
+                      const int* idx, const int* count, int cap, const uint8_t* row_mask, void* stream_) {
   if (ntensors <= 0 || ntensors > 8 || !dense || !compact || !floats_per_row || !idx || !count || cap < 0)
     return fail(GSR_ERR_INVALID_ARGUMENT, "exchange_rows: bad argument");
   if (scatter < 0 || scatter > 2) return fail(GSR_ERR_INVALID_ARGUMENT, "exchange_rows: mode must be 0, 1 or 2");
   if (scatter == 1) {  // compact -> dense
     const float* src[8]; float* dst[8];
     for (int k = 0; k < ntensors; k++) { src[k] = compact[k]; dst[k] = const_cast<float*>(dense[k]); }
-    gsr::launch_rows(1, ntensors, src, dst, floats_per_row, idx, count, cap, (cudaStream_t)stream_);
+    gsr::launch_rows(1, ntensors, src, dst, floats_per_row, idx, count, cap, nullptr, (cudaStream_t)stream_);
   } else {
-    gsr::launch_rows(scatter, ntensors, dense, compact, floats_per_row, idx, count, cap, (cudaStream_t)stream_);
+    gsr::launch_rows(scatter, ntensors, dense, compact, floats_per_row, idx, count, cap, row_mask, (cudaStream_t)stream_);
   }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "exchange_rows: %s", cudaGetErrorString(e));

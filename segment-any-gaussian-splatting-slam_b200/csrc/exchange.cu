@@ -110,13 +110,15 @@ struct XcTensors {
   float* dst[8];
   int n[8];
   int count;
+  const uint8_t* row_mask;  // gather: dense row g is valid only if row_mask[g] != 0 (NULL: every row is), else zeros
 };
 __global__ void __launch_bounds__(256)
 xc_gather_kernel(XcTensors t, const int* __restrict__ idx, const int* __restrict__ count, int cap) {
   const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (row >= cap) return;
-  const bool live = row < *count;
+  bool live = row < *count;
   const size_t g = live ? (size_t)idx[row] : 0;
+  if (live && t.row_mask) live = t.row_mask[g] != 0;
   for (int k = 0; k < t.count; k++) {
     const int n = t.n[k];
     const float* s = t.src[k] + g * n;
@@ -206,7 +208,8 @@ xc_gather_flat_kernel(XcTensors t, const int* __restrict__ idx, const int* __res
     float v = 0.f;
     if (e < live) {
       const unsigned r = (unsigned)(e / n), i = (unsigned)(e - (size_t)r * n);
-      v = src[(size_t)idx[r] * n + i];
+      const size_t g = (size_t)idx[r];
+      if (!t.row_mask || t.row_mask[g]) v = src[g * n + i];
     }
     dst[e] = v;
   }
@@ -290,9 +293,10 @@ void launch_sum_rows_peers(const float* const* buckets, const uint8_t* const* fl
   else xc_gather_sum_kernel<false><<<nb < 148 * 8 ? nb : 148 * 8, 256, 0, s>>>(t, b, f, idx, count, cap);
 }
 void launch_rows(int scatter, int ntensors, const float* const* src, float* const* dst, const int* n, const int* idx,
-                 const int* count, int cap, cudaStream_t s) {
+                 const int* count, int cap, const uint8_t* row_mask, cudaStream_t s) {
   XcTensors t;
   t.count = ntensors;
+  t.row_mask = scatter == 1 ? nullptr : row_mask;
   for (int k = 0; k < ntensors; k++) { t.src[k] = src[k]; t.dst[k] = dst[k]; t.n[k] = n[k]; }
   if (cap <= 0) return;
   const int nb = (cap + 7) / 8;

@@ -34,7 +34,7 @@ const float* fptr(const torch::Tensor& t) {  // 0-element tensor == "not provide
 void check(int rc) { TORCH_CHECK(rc == GSR_OK, "gsraster_b200 error ", rc, ": ", gsr_last_error()); }
 gsr_params make_params(int P, int D, int M, int F, int W, int H, float tx, float ty, float mod, bool prefiltered,
                        bool debug) {
-  gsr_params p;
+  gsr_params p{};  // ext = NULL: the reference's behaviour
   p.P = P; p.D = D; p.M = M; p.F = F; p.width = W; p.height = H;
   p.tan_fovx = tx; p.tan_fovy = ty; p.scale_modifier = mod;
   p.prefiltered = prefiltered; p.debug = debug;

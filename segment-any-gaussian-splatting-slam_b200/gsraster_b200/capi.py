@@ -157,7 +157,7 @@ def lib():
         L.gsr_exchange_compact.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                            C.c_void_p, C.c_void_p]
         L.gsr_exchange_rows.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
-                                        C.POINTER(C.c_int), C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+                                        C.POINTER(C.c_int), C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         L.gsr_last_forward_stats.argtypes = [C.POINTER(C.c_ulonglong)]
         _lib = L
     return _lib
@@ -408,15 +408,16 @@ def exchange_compact(flags, nranks, P, Ppad, cap, idx, count, scratch):
                                           count.data_ptr(), scratch.data_ptr(), _stream_ptr()))
 
 
-def exchange_rows(scatter, dense, compact, floats_per_row, idx, count, cap):
-    """Row gather (dense -> compact) or scatter (compact -> dense) of the bucket tensors (gsr_exchange_rows)."""
+def exchange_rows(scatter, dense, compact, floats_per_row, idx, count, cap, own_flags=None):
+    """Row gather (dense -> compact) or scatter (compact -> dense) of the bucket tensors (gsr_exchange_rows).
+    own_flags (gather): uint8 (P,) -- dense rows whose flag is 0 are gathered as zeros (sparse-row buckets)."""
     n = len(dense)
     dp = (C.c_void_p * n)(*[t.data_ptr() for t in dense])
     cp = (C.c_void_p * n)(*[t.data_ptr() for t in compact])
     fp = (C.c_int * n)(*[int(v) for v in floats_per_row])
     with torch.cuda.device(idx.device):
         _check(lib().gsr_exchange_rows(int(scatter), n, dp, cp, fp, idx.data_ptr(), count.data_ptr(), int(cap),
-                                       _stream_ptr()))
+                                       None if own_flags is None else own_flags.data_ptr(), _stream_ptr()))
 
 
 def exchange_compact_peers(flag_ptrs, P, cap, idx, count, scratch):
@@ -431,18 +432,30 @@ def exchange_compact_peers(flag_ptrs, P, cap, idx, count, scratch):
                                             _stream_ptr()))
 
 
-def exchange_sum_rows_peers(bucket_ptrs, tensor_offsets, compact, floats_per_row, idx, count, cap):
-    """gsr_exchange_sum_rows_peers: compact rows = sum over ranks of the union's rows, read from the peers' buckets."""
+def exchange_signal_wait(pad_ptrs, rank, seq, timeout_ms, status):
+    """gsr_exchange_signal_wait: publish `seq` to every peer's signal pad and wait for theirs (one launch)."""
+    n = len(pad_ptrs)
+    pp = (C.c_void_p * n)(*[int(p) for p in pad_ptrs])
+    L = lib()
+    L.gsr_exchange_signal_wait.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_uint, C.c_int, C.c_void_p, C.c_void_p]
+    with torch.cuda.device(status.device):
+        _check(L.gsr_exchange_signal_wait(pp, n, int(rank), int(seq), int(timeout_ms), status.data_ptr(), _stream_ptr()))
+
+
+def exchange_sum_rows_peers(bucket_ptrs, tensor_offsets, compact, floats_per_row, idx, count, cap, flags=None):
+    """gsr_exchange_sum_rows_peers: compact rows = sum over ranks of the union's rows, read from the peers' buckets
+    (flags: the ranks' flag buffers; a rank contributes to a row only where its flag is set)."""
     n, k = len(bucket_ptrs), len(compact)
     bp = (C.c_void_p * n)(*[int(p) for p in bucket_ptrs])
+    fl = None if flags is None else (C.c_void_p * n)(*[int(p) for p in flags])
     off = (C.c_longlong * k)(*[int(o) for o in tensor_offsets])
     cp = (C.c_void_p * k)(*[t.data_ptr() for t in compact])
     fp = (C.c_int * k)(*[int(v) for v in floats_per_row])
     L = lib()
-    L.gsr_exchange_sum_rows_peers.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
-                                              C.c_void_p, C.c_int, C.c_void_p]
+    L.gsr_exchange_sum_rows_peers.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                              C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
     with torch.cuda.device(idx.device):
-        _check(L.gsr_exchange_sum_rows_peers(bp, n, k, off, cp, fp, idx.data_ptr(), count.data_ptr(), int(cap),
+        _check(L.gsr_exchange_sum_rows_peers(bp, fl, n, k, off, cp, fp, idx.data_ptr(), count.data_ptr(), int(cap),
                                              _stream_ptr()))
 
 

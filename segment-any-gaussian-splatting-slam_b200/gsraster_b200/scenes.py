@@ -98,6 +98,64 @@ def make_scene(P, sh_degree=3, F=16, seed=1234, W=1280, H=1024, scale_mul=1.0, b
     return Scene(means, scales, q.astype(np.float32), opac, shs, objs, sh_degree)
 
 
+def make_trajectory_scene(P, num_views, sh_degree=3, F=16, seed=1234, W=1280, H=1024, scale_mul=1.0, behind_frac=0.05,
+                          opacity_mean=-1.0):
+    """'lidar-init' Gaussians over the UNION of the frusta of a keyframe trajectory (views 0 .. num_views-1 of
+    make_camera: 5 degrees of yaw and 0.25 m of lateral motion per keyframe): every Gaussian is drawn with the
+    SURVEY 8d sampler in the camera frame of a uniformly chosen keyframe and moved to the world frame, so every
+    keyframe looks at the same kind of population (a SLAM map covers what the sensor has swept, not one frustum).
+    num_views = 1 is make_scene. Same attribute distributions as make_scene."""
+    rng = np.random.default_rng(seed)
+    cam0 = make_camera(W, H, 0)
+    u = rng.uniform(-1.3, 1.3, P) * cam0.tanfovx
+    v = rng.uniform(-1.3, 1.3, P) * cam0.tanfovy
+    z = np.exp(rng.uniform(math.log(0.5), math.log(40.0), P))
+    behind = rng.uniform(size=P) < behind_frac
+    z = np.where(behind, -z, z)
+    local = np.stack([u * np.abs(z), v * np.abs(z), z], 1)
+    owner = rng.integers(0, num_views, P)
+    means = np.empty((P, 3), np.float64)
+    for k in range(num_views):
+        sel = owner == k
+        if not sel.any():
+            continue
+        Vk = make_camera(W, H, k).viewmatrix.T.astype(np.float64)       # world -> camera k
+        Rk, tk = Vk[:3, :3], Vk[:3, 3]
+        means[sel] = (local[sel] - tk) @ Rk                              # p_world = R^T (p_cam - t)
+    scales = (np.exp(rng.normal(math.log(0.02), 0.5, (P, 3))) * scale_mul).astype(np.float32)
+    q = rng.normal(size=(P, 4))
+    q /= np.linalg.norm(q, axis=1, keepdims=True)
+    opac = (1.0 / (1.0 + np.exp(-rng.normal(opacity_mean, 1.5, (P, 1))))).astype(np.float32)
+    M = (sh_degree + 1) ** 2
+    shs = np.zeros((P, M, 3), np.float32)
+    shs[:, 0, :] = (rng.uniform(size=(P, 3)) - 0.5) / 0.28209
+    if M > 1:
+        shs[:, 1:, :] = rng.normal(0, 0.05, (P, M - 1, 3))
+    objs = ((rng.uniform(size=(P, 1, F)) - 0.5) / 0.28209).astype(np.float32)
+    return Scene(means.astype(np.float32), scales, q.astype(np.float32), opac, shs, objs, sh_degree)
+
+
+# Named single-view workloads of bench.py's `workloads` block (both arms build them from here, so the scenes are
+# identical): the SURVEY 8d scene of round 1, BASELINE config 2, the "trained-like" x3 scene, and a scene whose pixels
+# do NOT saturate early (small, faint splats: most visible Gaussians receive a gradient).
+WORKLOADS = {
+    "survey8d_view0": dict(P=1_000_000, scale_mul=1.0, opacity_cap=None,
+                           note="SURVEY 8d lidar-init scene in the frustum of view 0 (the round-1 headline)"),
+    "c2_500k": dict(P=500_000, scale_mul=1.0, opacity_cap=None, note="BASELINE config 2: 500k Gaussians"),
+    "trained_like_x3": dict(P=1_000_000, scale_mul=3.0, opacity_cap=None, note="SURVEY 8d 'trained-like': scales x3"),
+    "non_saturating": dict(P=1_000_000, scale_mul=0.3, opacity_cap=0.1,
+                           note="scales x0.3 and opacity <= 0.1: pixels do not saturate, most visible Gaussians are touched"),
+}
+
+
+def make_workload_scene(name, sh_degree=3, F=16, W=1280, H=1024, seed=1234):
+    w = WORKLOADS[name]
+    sc = make_scene(w["P"], sh_degree=sh_degree, F=F, seed=seed, W=W, H=H, scale_mul=w["scale_mul"])
+    if w["opacity_cap"] is not None:
+        sc.opacities = np.minimum(sc.opacities, np.float32(w["opacity_cap"])).astype(np.float32)
+    return sc
+
+
 def make_upstream_grads(W, H, F, seed=99):
     rng = np.random.default_rng(seed)
     n = float(H * W)

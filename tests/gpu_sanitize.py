@@ -11,9 +11,7 @@ for (P, W, H, F, deg) in ((3000, 200, 136, 16, 3), (1500, 131, 77, 32, 1), (5, 6
     cam = scenes.make_camera(W, H, 1)
     grads = scenes.make_upstream_grads(W, H, F)
     mask = torch.zeros(P, dtype=torch.uint8, device="cuda")
-    capi.set_touched_mask(mask)
-    out = h.run_mine(sc, cam, grads)          # forward, export (full pull), backward
-    capi.set_touched_mask(None)
+    out = h.run_mine(sc, cam, grads, ext=capi.Ext(touched_mask=mask))   # forward, export (full pull), backward
     print("scene", P, W, H, F, "R", out["R"], "touched", int(mask.sum()))
     Ppad = (P + 3) // 4 * 4
     flags = torch.zeros(2, Ppad, dtype=torch.uint8, device="cuda")

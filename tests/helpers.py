@@ -27,15 +27,16 @@ def to_torch(scene, cam, device="cuda"):
                 viewmatrix=t(cam.viewmatrix), projmatrix=t(cam.projmatrix), campos=t(cam.campos))
 
 
-def run_mine(scene, cam, grads=None, colors_precomp=None, cov3D_precomp=None, debug=False):
-    """Product path through the C ABI. Returns dict of torch tensors (+ exported state)."""
+def run_mine(scene, cam, grads=None, colors_precomp=None, cov3D_precomp=None, debug=False, ext=None, device="cuda"):
+    """Product path through the C ABI. Returns dict of torch tensors (+ exported state).
+    ext: capi.Ext handed to the backward call (touched flags, sparse rows, ...)."""
     import torch
     from gsraster_b200 import capi
-    d = to_torch(scene, cam)
-    e = torch.empty(0, device="cuda")
+    d = to_torch(scene, cam, device=device)
+    e = torch.empty(0, device=device)
     sh = d["shs"] if colors_precomp is None else e
-    col = e if colors_precomp is None else torch.from_numpy(colors_precomp).cuda()
-    sc, rot, cov = (d["scales"], d["rotations"], e) if cov3D_precomp is None else (e, e, torch.from_numpy(cov3D_precomp).cuda())
+    col = e if colors_precomp is None else torch.from_numpy(colors_precomp).to(device)
+    sc, rot, cov = (d["scales"], d["rotations"], e) if cov3D_precomp is None else (e, e, torch.from_numpy(cov3D_precomp).to(device))
     F = scene.sh_objs.shape[-1]
     R, depth, color, objects, radii, is_used, gb, bb, ib = capi.rasterize_gaussians(
         d["bg"], d["means3D"], col, d["opacities"], sc, rot, scene.scale_modifier, cov, d["viewmatrix"],
@@ -46,16 +47,17 @@ def run_mine(scene, cam, grads=None, colors_precomp=None, cov3D_precomp=None, de
                launches_fwd=capi.last_launch_count())
     out.update(capi.export_state(scene.P, scene.sh_degree, M, F, cam.W, cam.H, R, gb, bb, ib))
     if grads is not None:
-        gd, gc, go = [torch.from_numpy(g).cuda() for g in grads]
+        gd, gc, go = [torch.from_numpy(g).to(device) for g in grads]
         res = capi.rasterize_gaussians_backward(
             d["bg"], d["means3D"], radii, col, sc, rot, scene.scale_modifier, cov, d["viewmatrix"], d["projmatrix"],
-            cam.tanfovx, cam.tanfovy, gd, gc, sh, go, d["sh_objs"], scene.sh_degree, d["campos"], gb, R, bb, ib, debug)
+            cam.tanfovx, cam.tanfovy, gd, gc, sh, go, d["sh_objs"], scene.sh_degree, d["campos"], gb, R, bb, ib, debug,
+            ext=ext)
         names = ("dL_dmeans2D", "dL_dcolors", "dL_dobjects", "dL_dopacity", "dL_dmeans3D", "dL_dcov3D", "dL_dsh",
                  "dL_dscales", "dL_drotations")
         out.update(dict(zip(names, res)))
         out["dL_dconic"], out["dL_ddepths"] = capi.rasterize_gaussians_backward.last_internal
         out["launches_bwd"] = capi.last_launch_count()
-    torch.cuda.synchronize()
+    torch.cuda.synchronize(device)
     return out
 
 

@@ -93,6 +93,20 @@ def test_shard_views_partitions():
         mapping.shard_views(4, 2, 2)
 
 
+def test_assign_views_lpt_balances_and_is_deterministic():
+    from gsraster_b200 import mapping
+    costs = [1.7, 2.6, 1.9, 2.2, 2.7, 1.8, 2.0, 2.4, 1.75, 2.65, 1.95, 2.25, 2.75, 1.85, 2.05, 2.45]
+    a = mapping.assign_views_lpt(costs, 8)
+    assert a == mapping.assign_views_lpt(list(costs), 8)
+    assert sorted(v for r in a for v in r) == list(range(16))
+    loads = [sum(costs[v] for v in r) for r in a]
+    assert max(loads) <= 1.06 * (sum(costs) / 8)          # contiguous pairs would be at 1.25x the mean
+    assert mapping.assign_views_lpt([3.0, 1.0, 1.0, 1.0], 2) == [[0], [1, 2, 3]]
+    assert mapping.assign_views_lpt([], 3) == [[], [], []]
+    with pytest.raises(ValueError):
+        mapping.assign_views_lpt([1.0], 0)
+
+
 def test_grad_bucket_layout():
     from gsraster_b200 import mapping
     P, M, F = 1001, 16, 16
@@ -105,6 +119,13 @@ def test_grad_bucket_layout():
         v.fill_(1.0)
     # views do not overlap and cover everything but the alignment padding
     assert int(b.flat.sum()) == P * 75
+    b2 = mapping.GradBucket(P, M, F, "cpu", copies=2)   # double-buffered: flip() switches flat / views to the other copy
+    p0 = b2.views["sh"].data_ptr()
+    b2.views["sh"].fill_(2.0)
+    b2.flip()
+    assert b2.views["sh"].data_ptr() != p0 and float(b2.flat.sum()) == 0.0
+    b2.flip()
+    assert b2.views["sh"].data_ptr() == p0 and float(b2.flat.sum()) == 2.0 * P * 48
 
 
 def _worker(rank, world, port, q):
@@ -154,17 +175,27 @@ def _sparse_worker(rank, world, port, q):
     out = []
     for step, nrows in enumerate((150, 150, 2000)):   # step 0: cap = P; step 1: guessed cap; step 2: overflow -> dense fallback
         ex.begin_step()
-        bucket.flat.zero_()
+        # sparse-row bucket: rows are valid only where this rank's step flags are set, everything else is STALE data
+        # (here: garbage on purpose) that the exchange must not pick up
+        bucket.flat.fill_(777.0)
         rows = torch.randperm(P, generator=g)[:nrows + 50 * rank]  # each rank touches its own subset
-        for k, n in ex.sizes:
-            bucket.views[k].view(P, n)[rows] = torch.randn(len(rows), n, generator=g)
-        ex.touched[rows] = 1
-        dense = bucket.flat.clone()
-        dist.all_reduce(dense)                       # the dense exchange is the oracle
+        dense = torch.zeros_like(bucket.flat)
+        dviews = {k: dense[bucket.offsets[k]:bucket.offsets[k] + P * n].view(P, n) for k, n in ex.sizes}
+        for v in range(2):                               # two views per rank accumulate into the same rows
+            sub = rows if v == 0 else rows[::2]
+            for k, n in ex.sizes:
+                val = torch.randn(len(sub), n, generator=g)
+                tgt = bucket.views[k].view(P, n)
+                first = ex.touched[sub] == 0             # first touch of the step writes, later views add
+                tgt[sub] = torch.where(first.unsqueeze(1), val, tgt[sub] + val)
+                dviews[k][sub] += val
+            ex.touched[sub] = 1
+        dist.all_reduce(dense)                       # the dense exchange of the true per-rank sums is the oracle
         ex.exchange()
         idx, views = ex.finish()
-        ex.scatter_dense(idx, views)
-        out.append((int(idx.numel()), float((bucket.flat - dense).abs().max()), float(dense.abs().max()),
+        got = mapping.GradBucket(P, M, F, "cpu")
+        ex.scatter_dense(idx, views, out=got)
+        out.append((int(idx.numel()), float((got.flat - dense).abs().max()), float(dense.abs().max()),
                     bool((idx[1:] > idx[:-1]).all()), ex.fallbacks, ex.cap))
     q.put((rank, out))
     dist.destroy_process_group()

@@ -451,7 +451,7 @@ def test_knn_config5_5M_points():
 
 @pytest.mark.gpu
 def test_touched_mask_marks_exactly_the_nonzero_gradient_rows():
-    """gsr_set_touched_mask: Gaussians the backward blend did not reach have exactly-zero parameter gradients
+    """gsr_ext::touched_mask: Gaussians the backward blend did not reach have exactly-zero parameter gradients
     (that is what lets the multi-GPU exchange skip them); touched ones are a small part of the scene."""
     import torch
     from gsraster_b200 import capi
@@ -460,11 +460,7 @@ def test_touched_mask_marks_exactly_the_nonzero_gradient_rows():
     cam = scenes.make_camera(W, H, 1)
     grads = scenes.make_upstream_grads(W, H, 16)
     mask = torch.zeros(P, dtype=torch.uint8, device="cuda")
-    capi.set_touched_mask(mask)
-    try:
-        mine = h.run_mine(sc, cam, grads)
-    finally:
-        capi.set_touched_mask(None)
+    mine = h.run_mine(sc, cam, grads, ext=capi.Ext(touched_mask=mask))
     m = mask.bool()
     assert 0 < int(m.sum()) < P
     for k in h.GRAD_KEYS:
@@ -530,10 +526,10 @@ def test_sparse_exchange_with_overlapped_flag_exchange_single_rank_nccl():
                                 device_id=torch.device("cuda", 0))
     try:
         worst, rows, fb = gx.run_check(P=50000, W=320, H=256, steps=3)
-        assert worst <= 1e-6 and rows > 0 and fb <= 1, (worst, rows, fb)
+        assert worst <= 1e-5 and rows > 0 and fb <= 1, (worst, rows, fb)   # (two backward runs: atomic order differs)
+        # two views per rank accumulated into the sparse rows of one bucket (gsr_ext::accumulate)
+        worst, rows, fb = gx.run_check(P=50000, W=320, H=256, steps=3, V=2)
+        assert worst <= 1e-5 and rows > 0 and fb <= 1, (worst, rows, fb)
     finally:
-        from gsraster_b200 import capi
-        capi.set_touched_mask(None)
-        capi.set_blend_done_event(None)
         if created:
             dist.destroy_process_group()
