@@ -994,10 +994,14 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback")
     torch.cuda.set_device(local_rank)
+    # stdout of rank 0 carries exactly ONE JSON line: libraries (NCCL's version / INFO lines) write to file descriptor 1
+    # behind Python's back, so fd 1 is pointed at stderr for the run and the line goes to the saved descriptor
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if world > 1:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        # NCCL writes its version / INFO lines to stdout by default; stdout of rank 0 carries exactly one JSON line
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     r = run_mine(args, rank, world, local_rank)
@@ -1103,7 +1107,8 @@ def main():
         cb = cpu_baseline(args)
         out["cpu_baseline"] = {k: (round(cb[k], 5) if k == "value" else cb[k])
                                for k in ("value", "unit", "cores", "kind", "sample", "sample_scale")}
-    print(json.dumps(out), flush=True)
+    real_stdout.write(json.dumps(out) + "\n")
+    real_stdout.flush()
     if world > 1:
         torch.distributed.destroy_process_group()
     return 0

@@ -69,6 +69,7 @@ struct DevCtx {
 constexpr int MAX_DEVICES = 64;
 thread_local DevCtx g_dev[MAX_DEVICES];
 const bool g_no_side_sort = getenv("GSR_NO_SIDE_SORT") != nullptr;  // diagnostics: everything on the caller's stream
+const bool g_fwd_v1 = getenv("GSR_FWD_V1") != nullptr;              // A/B: first-generation forward blend (render_fwd.cu)
 const bool g_nvtx = getenv("GSR_NVTX") != nullptr;                  // NVTX range per stage (timeline tools)
 cudaError_t dev_ctx(DevCtx** out) {
   int dev = 0;
@@ -288,7 +289,8 @@ int gsr_forward(const gsr_params* p, gsr_alloc_fn geom_alloc, void* geom_ctx, gs
   STAGE_CHECK("binning");
   {
     StageTimer tm(p, 3, stream);
-    gsr::launch_render_forward(p->F, cam, g, b, img, sh_objs, out_depth, out_color, out_objects, stream);
+    if (g_fwd_v1) gsr::launch_render_forward(p->F, cam, g, b, img, sh_objs, out_depth, out_color, out_objects, stream);
+    else gsr::launch_render_forward2(p->F, cam, g, b, img, sh_objs, out_depth, out_color, out_objects, stream);
   }
   g_launches += 1;
   STAGE_CHECK("render_forward");

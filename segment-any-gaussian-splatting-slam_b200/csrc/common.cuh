@@ -216,6 +216,9 @@ struct BwdOpts {
   int* touched_idx;      // sparse rows: list of the Gaussians written (first touch), may be NULL
   int* touched_count;
 };
+// second-generation forward blend (render_fwd2.cu: two pixels per thread, packed FFMA2): the default
+void launch_render_forward2(int F, const Cam& cam, const GeomState& g, const BinState& b, ImageState& img,
+                            const float* sh_objs, float* out_depth, float* out_color, float* out_objects, cudaStream_t s);
 void launch_render_backward(int F, const Cam& cam, const GeomState& g, const BinState& b,
                             const ImageState& img, const float* sh_objs, const float* dL_dpix_depth,
                             const float* dL_dpix, const float* dL_dpix_obj, const BwdOpts& opt, cudaStream_t s);

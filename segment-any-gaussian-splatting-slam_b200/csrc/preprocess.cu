@@ -82,18 +82,28 @@ preprocess_kernel(const FwdInputs in, const Cam cam, float4* __restrict__ rec, u
   const int first = blockIdx.x * PF_THREADS;
   const int idx = first + threadIdx.x;
   const bool staged_sh = in.colors_precomp == nullptr && in.M == 16 && (((uintptr_t)in.shs & 15) == 0);
-  // Every thread fetches its own 192-byte SH row with one TMA bulk copy into its padded tile row; the copies complete
-  // on one mbarrier and are only waited for right before the colour evaluation, i.e. they fly underneath the geometry
-  // loads and the covariance projection (a plain load + barrier here exposed the full HBM latency up front).
+  // Every thread that survives the near-plane test fetches its own 192-byte SH row with one TMA bulk copy into its
+  // padded tile row; the copies complete on one mbarrier and are only waited for right before the colour evaluation,
+  // i.e. they fly underneath the remaining geometry loads and the covariance projection (a plain load + barrier here
+  // exposed the full HBM latency up front). The 12-byte mean and the cull come FIRST: a third of the headline scene's
+  // Gaussians are behind the camera or too near, and their rows (63 MB per view) used to be fetched and dropped.
   __shared__ uint64_t sh_bar;
   if (staged_sh) {
     if (threadIdx.x == 0) {
-      mbar_init(&sh_bar, 1);
+      mbar_init(&sh_bar, PF_THREADS);   // every thread arrives once, announcing the bytes of its own copy (0 or 192)
       mbar_fence_init();
     }
     __syncthreads();
-    if (threadIdx.x == 0) mbar_arrive_expect_tx(&sh_bar, (uint32_t)min(PF_THREADS, in.P - first) * 192u);
-    if (idx < in.P) tma_load_1d(&sh_tile[threadIdx.x * 13], in.shs + (size_t)idx * 48, 192, &sh_bar);
+  }
+  float3 p_orig = {0.f, 0.f, 0.f}, p_view = {0.f, 0.f, 0.f};
+  if (idx < in.P) {
+    p_orig = {in.means3D[3 * idx], in.means3D[3 * idx + 1], in.means3D[3 * idx + 2]};
+    p_view = xform4x3(p_orig, cs.V);
+  }
+  if (staged_sh) {
+    const bool fetch = idx < in.P && !(p_view.z <= 0.2f);
+    mbar_arrive_expect_tx(&sh_bar, fetch ? 192u : 0u);
+    if (fetch) tma_load_1d(&sh_tile[threadIdx.x * 13], in.shs + (size_t)idx * 48, 192, &sh_bar);
   }
   if (idx >= in.P) return;  // (these threads issued no copy; the block lives on through the threads that wait below)
 
@@ -101,8 +111,6 @@ preprocess_kernel(const FwdInputs in, const Cam cam, float4* __restrict__ rec, u
   uint32_t touched = 0;
   uint64_t key = (0xFFFFFFFFull << 32) | (uint32_t)idx;  // culled Gaussians sort last
 
-  const float3 p_orig = {in.means3D[3 * idx], in.means3D[3 * idx + 1], in.means3D[3 * idx + 2]};
-  const float3 p_view = xform4x3(p_orig, cs.V);
   do {
     if (p_view.z <= 0.2f) {  // auxiliary.h:159 -- near plane only, no lateral test
       if (in.prefiltered) flags[1] = 1;

@@ -355,10 +355,17 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
     // ---- sparse rows: this thread's rows only; first touch of the step writes, later views of the step add ----
     const bool acc = opt.accumulate && opt.touched_ext[idx] != 0;
     auto put = [acc](float* p, float v) { *p = acc ? *p + v : v; };
+    auto put4 = [acc](float* p, float a, float b, float c, float d) {  // 16-byte aligned rows: one 128-bit access
+      float4* q = reinterpret_cast<float4*>(p);
+      float4 v = make_float4(a, b, c, d);
+      if (acc) { const float4 o = *q; v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w; }
+      *q = v;
+    };
     put(out.dL_dopacity + idx, g[7]);
     put(out.dL_ddepths + idx, g[8]);
 #pragma unroll
-    for (int k = 0; k < F; k++) put(out.dL_dobjects + (size_t)idx * F + k, g[12 + k]);
+    for (int k = 0; k < F; k += 4)
+      put4(out.dL_dobjects + (size_t)idx * F + k, g[12 + k], g[13 + k], g[14 + k], g[15 + k]);
     put(out.dL_dmean2D + 3 * (size_t)idx, g[0]);
     put(out.dL_dmean2D + 3 * (size_t)idx + 1, g[1]);
     put(out.dL_dmean2D + 3 * (size_t)idx + 2, 0.f);
@@ -374,11 +381,15 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
       put(out.dL_dmean3D + 3 * (size_t)idx + k, dmean[k]);
       if (out.dL_dscale) put(out.dL_dscale + 3 * (size_t)idx + k, dscale[k]);
     }
-    if (out.dL_drot) {
+    if (out.dL_drot) put4(out.dL_drot + 4 * (size_t)idx, drot[0], drot[1], drot[2], drot[3]);
+    if (out.dL_dsh != nullptr && M == 16 && ((uintptr_t)out.dL_dsh & 15) == 0) {
+      float d48[48];
 #pragma unroll
-      for (int k = 0; k < 4; k++) put(out.dL_drot + 4 * (size_t)idx + k, drot[k]);
-    }
-    if (out.dL_dsh != nullptr) {
+      for (int k = 0; k < 16; k++) { d48[3 * k] = basis[k] * dRGB[0]; d48[3 * k + 1] = basis[k] * dRGB[1]; d48[3 * k + 2] = basis[k] * dRGB[2]; }
+#pragma unroll
+      for (int q4 = 0; q4 < 12; q4++)
+        put4(out.dL_dsh + (size_t)idx * 48 + 4 * q4, d48[4 * q4], d48[4 * q4 + 1], d48[4 * q4 + 2], d48[4 * q4 + 3]);
+    } else if (out.dL_dsh != nullptr) {
 #pragma unroll
       for (int k = 0; k < 16; k++)
         if (k < M) {

@@ -205,15 +205,20 @@ class _Resizer:
     def _alloc(self, _ctx, n):
         n = int(n) + 256
         pool = _Resizer._pools.setdefault(self.key, [])
+        best = None
         for i in range(len(pool)):
             t = pool[i]
             # free <=> only the pool list and the local name refer to it, and no autograd node saved it
-            if sys.getrefcount(t) <= 3 and t._use_count() <= 1:
-                if n <= t.numel() <= n + n // 2 + (1 << 20):
-                    self.t = t
-                    return t.data_ptr()
+            if sys.getrefcount(t) <= 3 and t._use_count() <= 1 and t.numel() >= n:
+                if best is None or t.numel() < best.numel():
+                    best = t   # the smallest free buffer that fits: a mapping loop cycles through keyframes whose R differ,
+                               # and the pool settles on buffers large enough for all of them instead of re-allocating
         t = None
-        self.t = torch.empty(n + n // 16, dtype=torch.uint8, device=self.device)  # head-room: R varies a little per view
+        if best is not None and best.numel() <= 4 * n + (64 << 20):
+            self.t = best
+            return best.data_ptr()
+        best = None
+        self.t = torch.empty(n + n // 4, dtype=torch.uint8, device=self.device)  # head-room: R varies from view to view
         pool.append(self.t)
         if len(pool) > _Resizer._POOL_MAX:
             for i in range(len(pool)):  # drop the oldest unreferenced buffer
