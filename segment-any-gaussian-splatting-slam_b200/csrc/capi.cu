@@ -70,6 +70,7 @@ constexpr int MAX_DEVICES = 64;
 thread_local DevCtx g_dev[MAX_DEVICES];
 const bool g_no_side_sort = getenv("GSR_NO_SIDE_SORT") != nullptr;  // diagnostics: everything on the caller's stream
 const bool g_fwd_v1 = getenv("GSR_FWD_V1") != nullptr;              // A/B: first-generation forward blend (render_fwd.cu)
+const bool g_bwd_v1 = getenv("GSR_BWD_V1") != nullptr;              // A/B: first-generation backward blend (render_bwd.cu)
 const bool g_nvtx = getenv("GSR_NVTX") != nullptr;                  // NVTX range per stage (timeline tools)
 cudaError_t dev_ctx(DevCtx** out) {
   int dev = 0;
@@ -375,7 +376,8 @@ static int backward_impl(const gsr_params* p, int num_rendered, const float* bac
     if (!opt.clean_rows)  // rows + internal touched flags
       CUDA_TRY(cudaMemsetAsync(opt.rows, 0, (size_t)P * gsr::grad_row_floats(p->F) * sizeof(float) + (size_t)P, stream));
     if (num_rendered > 0) {
-      gsr::launch_render_backward(p->F, cam, g, b, img, sh_objs, dL_dpix_depth, dL_dpix, dL_dpix_obj, opt, stream);
+      if (g_bwd_v1) gsr::launch_render_backward(p->F, cam, g, b, img, sh_objs, dL_dpix_depth, dL_dpix, dL_dpix_obj, opt, stream);
+      else gsr::launch_render_backward2(p->F, cam, g, b, img, sh_objs, dL_dpix_depth, dL_dpix, dL_dpix_obj, opt, stream);
       g_launches += 1;
     }
   }

@@ -222,6 +222,10 @@ void launch_render_forward2(int F, const Cam& cam, const GeomState& g, const Bin
 void launch_render_backward(int F, const Cam& cam, const GeomState& g, const BinState& b,
                             const ImageState& img, const float* sh_objs, const float* dL_dpix_depth,
                             const float* dL_dpix, const float* dL_dpix_obj, const BwdOpts& opt, cudaStream_t s);
+// second-generation backward blend (render_bwd2.cu: two pixels per lane, packed FFMA2 dot product): the default
+void launch_render_backward2(int F, const Cam& cam, const GeomState& g, const BinState& b,
+                             const ImageState& img, const float* sh_objs, const float* dL_dpix_depth,
+                             const float* dL_dpix, const float* dL_dpix_obj, const BwdOpts& opt, cudaStream_t s);
 void launch_count_pairs(const Cam& cam, const GeomState& g, const BinState& b, const ImageState& img,
                         unsigned long long* counts, cudaStream_t s);
 struct BwdOutputs {
