@@ -17,6 +17,7 @@
 //   * TRACK (gsr_ext::tracking): the F feature-channel columns are not reduced at all.
 // Pixel k-index of the products: p = 2 * lane + h (h = 0: upper pixel, 1: lower), so a lane stores its (w_A, w_B) and
 // (q_A, q_B) as two 8-byte shared-memory stores per hit.
+#include <cstdlib>
 #include "common.cuh"
 #include "tma.cuh"
 
@@ -28,10 +29,10 @@ constexpr int WSTRIDE2 = 68;   // slot-row stride (floats), == 4 mod 32: A-fragm
 constexpr int BWD2_THREADS = 128;
 constexpr unsigned FULL2 = 0xffffffffu;
 
-template <int F, bool TRACK>
+template <int F, bool TRACK, int NSTG>
 struct Bwd2Cfg {
   static constexpr int BB = 32;                              // instances per staged batch (one mask group)
-  static constexpr int NST = 3;                              // staging ring depth
+  static constexpr int NST = NSTG;                           // staging ring depth (3: 3 CTAs/SM at F = 16; 6: 2 CTAs/SM)
   static constexpr int NTW = TRACK ? 1 : 1 + F / 8;          // 8-column output tiles of the w side
   static constexpr int NT = 1 + NTW;                         // + the q side
   static constexpr int NC = 8 * NT;                          // output columns
@@ -44,9 +45,9 @@ struct Bwd2Row {  // one staged instance: 64-byte record + feature row
   float4 rec[REC4];
   float4 feat[F / 4];
 };
-template <int F, bool TRACK>
+template <int F, bool TRACK, int NSTG>
 struct Bwd2Smem {
-  using Cfg = Bwd2Cfg<F, TRACK>;
+  using Cfg = Bwd2Cfg<F, TRACK, NSTG>;
   Bwd2Row<F> row[Cfg::NST][Cfg::BB];
   float4 meta[4][SLOTS2];                     // per warp, per slot: {Gaussian index bits, gx', gy', -}
   float wq[4][2 * SLOTS2 * WSTRIDE2];         // per warp: w rows, then q rows; re-used for the result tile
@@ -55,7 +56,7 @@ struct Bwd2Smem {
   uint64_t empty[Cfg::NST];  // empty: all 4 warps are done with the batch in this stage
   uint32_t max_contrib;
 };
-static_assert(SLOTS2 * Bwd2Cfg<32, false>::DSTRIDE <= 2 * SLOTS2 * WSTRIDE2, "result tile must fit");
+static_assert(SLOTS2 * Bwd2Cfg<32, false, 3>::DSTRIDE <= 2 * SLOTS2 * WSTRIDE2, "result tile must fit");
 
 __device__ __forceinline__ float rcp_approx2(float x) {
   float r;
@@ -85,7 +86,7 @@ __device__ __forceinline__ void flush_slots2(float* __restrict__ wbuf, const flo
                                              const float (&vb)[4], bool qzero, int ns, int lane,
                                              float* __restrict__ grad_rows, uint8_t* __restrict__ touched,
                                              uint8_t* __restrict__ touched_ext) {
-  using Cfg = Bwd2Cfg<F, TRACK>;
+  using Cfg = Bwd2Cfg<F, TRACK, 3>;
   constexpr int NT = Cfg::NT, NC = Cfg::NC, DS = Cfg::DSTRIDE, ROW = Cfg::ROW;
   const int gid = lane >> 2, tig = lane & 3;
   const float* qbuf = wbuf + SLOTS2 * WSTRIDE2;
@@ -191,8 +192,8 @@ __device__ __forceinline__ void flush_slots2(float* __restrict__ wbuf, const flo
 
 }  // namespace
 
-template <int F, bool TRACK>
-__global__ void __launch_bounds__(BWD2_THREADS, (F == 16 ? 3 : 2))
+template <int F, bool TRACK, int NSTG>
+__global__ void __launch_bounds__(BWD2_THREADS, (F == 16 && NSTG == 3 ? 3 : 2))
 render_bwd2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
                    const uint32_t* __restrict__ hitw, const float4* __restrict__ rec,
                    const float* __restrict__ feats, int W, int H, const float* __restrict__ bg,
@@ -200,10 +201,10 @@ render_bwd2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict_
                    const float* __restrict__ dL_dpix_depth, const float* __restrict__ dL_dpix,
                    const float* __restrict__ dL_dpix_obj, float* __restrict__ grad_rows,
                    uint8_t* __restrict__ touched, uint8_t* __restrict__ touched_ext) {
-  using Cfg = Bwd2Cfg<F, TRACK>;
-  constexpr int BB = Cfg::BB, NST = Cfg::NST;
+  using Cfg = Bwd2Cfg<F, TRACK, NSTG>;
+  constexpr int BB = Cfg::BB, NST = Cfg::NST, AHEAD = NST - 1;   // batches in flight ahead of the one being walked
   extern __shared__ __align__(128) unsigned char smem_raw2[];
-  Bwd2Smem<F, TRACK>& sm = *reinterpret_cast<Bwd2Smem<F, TRACK>*>(smem_raw2);
+  Bwd2Smem<F, TRACK, NSTG>& sm = *reinterpret_cast<Bwd2Smem<F, TRACK, NSTG>*>(smem_raw2);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int bx0 = blockIdx.x * TILE_X + (warp & 1) * 8, by0 = blockIdx.y * TILE_Y + (warp >> 1) * 8;
   const int px = bx0 + (lane & 7), pyA = by0 + (lane >> 3), pyB = pyA + 4;
@@ -237,14 +238,23 @@ render_bwd2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict_
   const int thrA = todo - (int)lastA, thrB = todo - (int)lastB;
 
   constexpr uint32_t ROW_BYTES = 16 * REC4 + 4 * F;
-  auto issue = [&](int b) {
+  // Staging: lanes 0..7 of every warp issue the bulk copies of rows 8 warp + lane (the work is spread over the four
+  // warps), and the Gaussian index of a row is fetched ONE BATCH AHEAD of its copies, so the dependent global load
+  // (point_list -> record address) never sits in front of a TMA issue (ncu: that load and the wait for the copies it
+  // delayed were 15 % of the stall samples of the first version).
+  const bool issuer = lane < BB / 4;
+  const int myrow = warp * (BB / 4) + lane;
+  auto load_id = [&](int b) -> uint32_t {
+    const int wi = b * BB + myrow;
+    return (issuer && wi < todo) ? point_list[list_end - 1 - (uint32_t)wi] : 0u;
+  };
+  auto issue = [&](int b, uint32_t id) {
     const int st = b % NST;
     const int cnt = min(BB, todo - b * BB);
     if (tid == 0) mbar_arrive_expect_tx(&sm.bar[st], (uint32_t)cnt * ROW_BYTES);
-    if (tid < cnt) {
-      const uint32_t id = point_list[list_end - 1 - (uint32_t)(b * BB + tid)];
-      tma_load_1d(&sm.row[st][tid].rec[0], rec + REC4 * (size_t)id, 16 * REC4, &sm.bar[st]);
-      tma_load_1d(&sm.row[st][tid].feat[0], feats + (size_t)id * F, 4 * F, &sm.bar[st]);
+    if (issuer && myrow < cnt) {
+      tma_load_1d(&sm.row[st][myrow].rec[0], rec + REC4 * (size_t)id, 16 * REC4, &sm.bar[st]);
+      tma_load_1d(&sm.row[st][myrow].feat[0], feats + (size_t)id * F, 4 * F, &sm.bar[st]);
     }
   };
   // Forward blend masks of this warp's two halves (BinState::hitw): batch b walks list positions p_top, p_top - 1, ...;
@@ -256,8 +266,15 @@ render_bwd2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict_
     return __ldg(hw + (size_t)g * 8) | __ldg(hw + (size_t)g * 8 + 2);
   };
   uint32_t wv_next = load_masks(0);
-  if (nbatch > 0) issue(0);
-  if (nbatch > 1) issue(1);
+  {
+    uint32_t ids[AHEAD];
+#pragma unroll
+    for (int i = 0; i < AHEAD; i++) ids[i] = load_id(i);
+#pragma unroll
+    for (int i = 0; i < AHEAD; i++)
+      if (nbatch > i) issue(i, ids[i]);
+  }
+  uint32_t id_next = load_id(AHEAD);
 
   // ---- per-pixel upstream gradients (lane = pixels A and B); feature channels in pairs for the packed FMAs ----
   const float TfA = insideA ? final_T[pidA] : 0.f, TfB = insideB ? final_T[pidB] : 0.f;
@@ -399,9 +416,10 @@ render_bwd2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict_
     }
     __syncwarp();
     if (lane == 0) mbar_arrive(&sm.empty[st]);  // this warp is done with stage st
-    if (b + 2 < nbatch) {
+    if (b + AHEAD < nbatch) {  // batch b + AHEAD goes into the stage batch b - 1 used: wait until all warps left it
       if (b >= 1) mbar_wait(&sm.empty[(b - 1) % NST], (uint32_t)((b - 1) / NST) & 1u);
-      issue(b + 2);
+      issue(b + AHEAD, id_next);
+      id_next = load_id(b + AHEAD + 1);
     }
   }
   if (ns > 0)
@@ -414,16 +432,22 @@ void launch_render_backward2(int F, const Cam& cam, const GeomState& g, const Bi
   dim3 grid(cam.gx, cam.gy), block(BWD2_THREADS);
   // with opt.accumulate the per-Gaussian backward maintains the external flags (it has to see their previous value)
   uint8_t* const ext = opt.accumulate ? nullptr : opt.touched_ext;
-  static std::atomic<unsigned long long> done[4] = {{0}, {0}, {0}, {0}};  // per-device opt-in bitmaps (common.cuh)
-#define GSR_BWD2(FF, TT, SLOT)                                                                                     \
+  static std::atomic<unsigned long long> done[5] = {{0}, {0}, {0}, {0}, {0}};  // per-device opt-in bitmaps (common.cuh)
+  static const bool deep = getenv("GSR_BWD_NST6") != nullptr;   // A/B: 6-deep staging ring at 2 CTAs/SM (F = 16)
+#define GSR_BWD2(FF, TT, NS, SLOT)                                                                                 \
   do {                                                                                                             \
-    ensure_dyn_smem(render_bwd2_kernel<FF, TT>, (int)sizeof(Bwd2Smem<FF, TT>), done[SLOT]);                        \
-    render_bwd2_kernel<FF, TT><<<grid, block, sizeof(Bwd2Smem<FF, TT>), s>>>(                                      \
+    ensure_dyn_smem(render_bwd2_kernel<FF, TT, NS>, (int)sizeof(Bwd2Smem<FF, TT, NS>), done[SLOT]);                \
+    render_bwd2_kernel<FF, TT, NS><<<grid, block, sizeof(Bwd2Smem<FF, TT, NS>), s>>>(                              \
         img.ranges, b.point_list, b.hitw, g.rec, sh_objs, cam.W, cam.H, cam.bg, img.final_T, img.n_contrib,        \
         dL_dpix_depth, dL_dpix, dL_dpix_obj, opt.rows, opt.touched, ext);                                          \
   } while (0)
-  if (F == 16) { if (opt.tracking) GSR_BWD2(16, true, 0); else GSR_BWD2(16, false, 1); }
-  else         { if (opt.tracking) GSR_BWD2(32, true, 2); else GSR_BWD2(32, false, 3); }
+  if (F == 16) {
+    if (opt.tracking) GSR_BWD2(16, true, 3, 0);
+    else if (deep) GSR_BWD2(16, false, 6, 4);
+    else GSR_BWD2(16, false, 3, 1);
+  } else {
+    if (opt.tracking) GSR_BWD2(32, true, 4, 2); else GSR_BWD2(32, false, 4, 3);
+  }
 #undef GSR_BWD2
 }
 
