@@ -115,8 +115,10 @@ __device__ __forceinline__ void flush_slots2(float* __restrict__ wbuf, const flo
 #pragma unroll
     for (int nt = 1; nt < NT; nt++) {
       uint32_t b0h, b0l, b1h, b1l;
-      tf32_split2(bfrag[(nt - 1) * 16 + ks * 2 + 0][lane], b0h, b0l);
-      tf32_split2(bfrag[(nt - 1) * 16 + ks * 2 + 1][lane], b1h, b1l);
+      // (columns are XOR-swizzled with the register row so that the one-off fill below is 2-way instead of 16-way
+      // bank-conflicted; a row is still read by 32 distinct lanes -> conflict-free)
+      tf32_split2(bfrag[(nt - 1) * 16 + ks * 2 + 0][lane ^ (((ks * 2 + 0) & 7) << 2)], b0h, b0l);
+      tf32_split2(bfrag[(nt - 1) * 16 + ks * 2 + 1][lane ^ (((ks * 2 + 1) & 7) << 2)], b1h, b1l);
       mma_tf32_2(acc[nt], ah, b0h, b1h);
       mma_tf32_2(acc[nt], al, b0h, b1h);
       mma_tf32_2(acc[nt], ah, b0l, b1l);
@@ -312,13 +314,14 @@ render_bwd2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict_
       const float vv = (float)((lane >> 3) + 4 * h) - 3.5f;
       const float2 dc = h ? dcB : dcA, gb = h ? gbB : gbA;
       const float col8[8] = {dc.x, dc.x * uu, dc.x * vv, dc.y, gb.x, gb.y, 0.f, 0.f};
+      const int sw = (rbase & 7) << 2;   // swizzle, see flush_slots2
 #pragma unroll
-      for (int c = 0; c < 8; c++) bf[rbase][4 * c + lbase] = col8[c];
+      for (int c = 0; c < 8; c++) bf[rbase][(4 * c + lbase) ^ sw] = col8[c];
       if (!TRACK) {
 #pragma unroll
         for (int c = 0; c < F; c++) {
           const float2 d2 = h ? doB[c >> 1] : doA[c >> 1];
-          bf[(1 + c / 8) * 16 + rbase][4 * (c % 8) + lbase] = (c & 1) ? d2.y : d2.x;
+          bf[(1 + c / 8) * 16 + rbase][(4 * (c % 8) + lbase) ^ sw] = (c & 1) ? d2.y : d2.x;
         }
       }
     }
