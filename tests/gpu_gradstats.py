@@ -29,7 +29,7 @@ def stats(a, b1, b2):
     spread = np.abs(b1 - b2)
     rel = err[sel] / np.abs(ref[sel])
     rel_ref = spread[sel] / np.abs(ref[sel])
-    excess = err[sel] - (1e-2 * np.abs(ref[sel]) + 2.0 * spread[sel])
+    excess = err[sel] - (1e-2 * np.abs(ref[sel]) + 2.0 * spread[sel] + spread.max())
     return dict(maxnorm=err.max() / mx, ref_maxnorm=spread.max() / mx, l2=np.linalg.norm(a - ref) / np.linalg.norm(ref),
                 ref_l2=np.linalg.norm(b1 - b2) / np.linalg.norm(ref), n=int(sel.sum()), elem_max=rel.max(),
                 elem_p999=np.quantile(rel, 0.999), ref_elem_max=rel_ref.max(), viol=int((excess > 0).sum()),

@@ -208,9 +208,11 @@ def grad_rel_l2(a, b):
 
 def grad_elementwise_violations(a, b1, b2, rel=1e-2, floor=1e-4):
     """Per-element check against the MEAN of two reference runs b1, b2, on the entries with |ref| >= floor * max|ref|:
-    |a - ref| <= rel * |ref| + 2 |b1 - b2| + 1e-6 max|ref|. The second term is the reference's own run-to-run spread at
-    that element (its float atomics reorder sums: measured up to 8 % on single small entries of dL_dcov3D,
-    tests/gpu_gradstats.py), the third its rounding floor. -> (violations, entries checked, worst relative error)."""
+    |a - ref| <= rel * |ref| + 2 |b1 - b2| + max|b1 - b2| + 1e-6 max|ref|. The second and third terms are the reference's
+    own run-to-run spread, at that element and over the tensor (its float atomics reorder sums: measured up to 8 % on
+    single small entries of dL_dcov3D, tests/gpu_gradstats.py; two runs only sample that spread, so the tensor-wide
+    maximum backs the per-element difference up -- no entry can be demanded to be more accurate than the reference
+    reproduces itself), the last its rounding floor. -> (violations, entries checked, worst relative error)."""
     a, b1, b2 = [npy(x).astype(np.float64).reshape(-1) for x in (a, b1, b2)]
     ref = 0.5 * (b1 + b2)
     mx = np.abs(ref).max() if ref.size else 0.0
@@ -218,7 +220,7 @@ def grad_elementwise_violations(a, b1, b2, rel=1e-2, floor=1e-4):
         return 0, 0, 0.0
     sel = np.abs(ref) >= floor * mx
     err = np.abs(a - ref)[sel]
-    allowed = rel * np.abs(ref[sel]) + 2.0 * np.abs(b1 - b2)[sel] + 1e-6 * mx
+    allowed = rel * np.abs(ref[sel]) + 2.0 * np.abs(b1 - b2)[sel] + np.abs(b1 - b2).max() + 1e-6 * mx
     return int((err > allowed).sum()), int(sel.sum()), float((err / np.abs(ref[sel])).max())
 
 

@@ -41,7 +41,8 @@ def _compare_on_device(name, sc, cam, grads):
         assert e_l2 <= 1e-3 + 3 * spread_l2, (k, "rel-L2", e_l2, spread_l2)
         refm = 0.5 * (b1 + b2)
         sel = refm.abs() >= 1e-4 * mx
-        viol = int((((a - refm).abs() > 1e-2 * refm.abs() + 2.0 * (b1 - b2).abs() + 1e-6 * mx) & sel).sum())
+        noise = (b1 - b2).abs()   # the reference's own run-to-run spread (helpers.grad_elementwise_violations)
+        viol = int((((a - refm).abs() > 1e-2 * refm.abs() + 2.0 * noise + noise.max() + 1e-6 * mx) & sel).sum())
         assert viol == 0, (k, "per-element", viol, int(sel.sum()))
         nz_a = a.view(P, -1).abs().sum(1) > 0
         nz_b = (b1.view(P, -1).abs().sum(1) > 0) | (b2.view(P, -1).abs().sum(1) > 0)
