@@ -8,15 +8,17 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB = os.path.join(HERE, "_build", "liboracle.so")
+LIB64 = os.path.join(HERE, "_build", "liboracle_f64.so")   # the same source with -DORC_REAL=double (pose-gradient FD checks)
 
 
-def build(force=False):
+def build(force=False, f64=False):
     src = os.path.join(HERE, "oracle.cpp")
-    if force or not os.path.exists(LIB) or os.path.getmtime(LIB) < os.path.getmtime(src):
-        os.makedirs(os.path.dirname(LIB), exist_ok=True)
-        subprocess.check_call(["g++", "-O2", "-std=c++17", "-fopenmp", "-ffp-contract=off", "-shared", "-fPIC",
-                               src, "-o", LIB])
-    return LIB
+    out = LIB64 if f64 else LIB
+    if force or not os.path.exists(out) or os.path.getmtime(out) < os.path.getmtime(src):
+        os.makedirs(os.path.dirname(out), exist_ok=True)
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-fopenmp", "-ffp-contract=off", "-shared", "-fPIC"] +
+                              (["-DORC_REAL=double"] if f64 else []) + [src, "-o", out])
+    return out
 
 
 class _Scene(C.Structure):
@@ -42,17 +44,17 @@ class _Grads(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in _GRAD_FIELDS]
 
 
-_lib = None
+_lib = {}
 
 
-def lib():
-    global _lib
-    if _lib is None:
-        _lib = C.CDLL(build())
-        _lib.orc_preprocess.restype = C.c_int64
-        _lib.orc_bin.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
-        _lib.orc_higher_msb.restype = C.c_uint32
-    return _lib
+def lib(f64=False):
+    if f64 not in _lib:
+        L = C.CDLL(build(f64=f64))
+        L.orc_preprocess.restype = C.c_int64
+        L.orc_bin.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
+        L.orc_higher_msb.restype = C.c_uint32
+        _lib[f64] = L
+    return _lib[f64]
 
 
 def _p(a):
@@ -66,7 +68,12 @@ def _f32(a):
 class Problem:
     """Holds contiguous host arrays + the C struct (keeps them alive)."""
 
-    def __init__(self, scene, cam, colors_precomp=None, cov3D_precomp=None, prefiltered=False):
+    def __init__(self, scene, cam, colors_precomp=None, cov3D_precomp=None, prefiltered=False, f64=False):
+        """f64: double-precision build of the oracle; the camera arrays of `cam` are then taken as float64 as given
+        (a finite-difference step of 1e-6 must survive), everything else is widened from the fp32 scene."""
+        self.f64 = bool(f64)
+        rt = np.float64 if f64 else np.float32
+        _f32 = lambda a: None if a is None else np.ascontiguousarray(a, dtype=rt)   # noqa: F811 (shadows the module helper)
         self.P = scene.means3D.shape[0]
         self.F = scene.sh_objs.shape[-1]
         self.W, self.H = cam.W, cam.H
@@ -91,16 +98,17 @@ class Problem:
 
 def forward(prob):
     """Runs K1..K4 of the oracle. Returns dict of numpy arrays (state + outputs) and R."""
-    L = lib()
+    L = lib(prob.f64)
+    rt = np.float64 if prob.f64 else np.float32
     P, W, H, F = prob.P, prob.W, prob.H, prob.F
     T = ((W + 15) // 16) * ((H + 15) // 16)
-    st = dict(depths=np.zeros(P, np.float32), clamped=np.zeros(3 * P, np.uint8), radii=np.zeros(P, np.int32),
-              means2D=np.zeros((P, 2), np.float32), cov3D=np.zeros((P, 6), np.float32),
-              conic_opacity=np.zeros((P, 6), np.float32), rgb=np.zeros((P, 3), np.float32),
+    st = dict(depths=np.zeros(P, rt), clamped=np.zeros(3 * P, np.uint8), radii=np.zeros(P, np.int32),
+              means2D=np.zeros((P, 2), rt), cov3D=np.zeros((P, 6), rt),
+              conic_opacity=np.zeros((P, 6), rt), rgb=np.zeros((P, 3), rt),
               tiles_touched=np.zeros(P, np.uint32), point_offsets=np.zeros(P, np.uint32),
-              is_used=np.zeros(P, np.uint8), final_T=np.zeros(H * W, np.float32),
-              n_contrib=np.zeros(H * W, np.uint32), out_depth=np.zeros((1, H, W), np.float32),
-              out_color=np.zeros((3, H, W), np.float32), out_objects=np.zeros((F, H, W), np.float32),
+              is_used=np.zeros(P, np.uint8), final_T=np.zeros(H * W, rt),
+              n_contrib=np.zeros(H * W, np.uint32), out_depth=np.zeros((1, H, W), rt),
+              out_color=np.zeros((3, H, W), rt), out_objects=np.zeros((F, H, W), rt),
               ranges=np.zeros((T, 2), np.uint32), keys=np.zeros(0, np.uint64), point_list=np.zeros(0, np.uint32))
     cs = _State(*[_p(st[k]) for k in _STATE_FIELDS])
     R = int(L.orc_preprocess(C.byref(prob.c), C.byref(cs)))
@@ -117,14 +125,16 @@ def forward(prob):
 
 
 def backward(prob, st, dL_ddepth, dL_dcolor, dL_dobjects):
-    L = lib()
+    L = lib(prob.f64)
+    rt = np.float64 if prob.f64 else np.float32
+    _f32 = lambda a: None if a is None else np.ascontiguousarray(a, dtype=rt)   # noqa: F811
     P, F, M = prob.P, prob.F, prob.M
-    g = dict(dL_dmean2D=np.zeros((P, 3), np.float32), dL_dconic=np.zeros((P, 6), np.float32),
-             dL_dopacity=np.zeros((P, 1), np.float32), dL_ddepths=np.zeros((P, 1), np.float32),
-             dL_dcolors=np.zeros((P, 3), np.float32), dL_dobjects=np.zeros((P, F), np.float32),
-             dL_dmean3D=np.zeros((P, 3), np.float32), dL_dcov3D=np.zeros((P, 6), np.float32),
-             dL_dsh=np.zeros((P, max(M, 0), 3), np.float32), dL_dscale=np.zeros((P, 3), np.float32),
-             dL_drot=np.zeros((P, 4), np.float32))
+    g = dict(dL_dmean2D=np.zeros((P, 3), rt), dL_dconic=np.zeros((P, 6), rt),
+             dL_dopacity=np.zeros((P, 1), rt), dL_ddepths=np.zeros((P, 1), rt),
+             dL_dcolors=np.zeros((P, 3), rt), dL_dobjects=np.zeros((P, F), rt),
+             dL_dmean3D=np.zeros((P, 3), rt), dL_dcov3D=np.zeros((P, 6), rt),
+             dL_dsh=np.zeros((P, max(M, 0), 3), rt), dL_dscale=np.zeros((P, 3), rt),
+             dL_drot=np.zeros((P, 4), rt))
     cg = _Grads(*[_p(g[k]) for k in _GRAD_FIELDS])
     if prob.arr["shs"] is None:
         cg.dL_dsh = None

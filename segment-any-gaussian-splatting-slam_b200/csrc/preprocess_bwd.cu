@@ -87,6 +87,7 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
       touched[idx] = 0;
     }
   }
+  float covyz_true = 0.f, conicy_true = 0.f;
   if (visible) {
     // K5 accumulates raw per-pixel moments (render_bwd.cu header); apply the per-Gaussian coefficients:
     // reference backward.cu:653-677 with dL_dG = opacity * dL_dalpha, G-gradients and depth partials.
@@ -101,6 +102,12 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
     g[4] = -0.5f * op * Qyy - covyz * Wy;
     g[5] = -ca * Wx - cb2 * Wy;  // d/dcov_zx
     g[6] = -cb2 * Wx;            // d/dcov_yz (sic, backward.cu:629)
+    // The camera gradient (extension) is the TRUE derivative of the forward pass; two entries of the row differ from
+    // what the reference accumulates: the partial of depth_c w.r.t. cov_yz is -b dx - c dy (backward.cu:629 leaves
+    // the c dy term out), and the depth part of dL/dconic.y is stored at full weight although .y holds HALF of dL/db
+    // everywhere else (backward.cu:631 vs :671; computeCov2DCUDA doubles it, :211-213).
+    covyz_true = -cb2 * Wx - cc * Wy;
+    conicy_true = -0.5f * op * Qxy - 0.5f * (covyz * Wx + covzx * Wy);
   }
   // scalar / float4 outputs of K5 are written directly (coalesced as they are)
   if (MODE == 0 && valid) {
@@ -180,11 +187,25 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
     const float dL_dT10 = 2 * TV(1, 0) * dL_dc + TV(0, 0) * dL_db + TV(2, 0) * dL_dcovyz;
     const float dL_dT11 = 2 * TV(1, 1) * dL_dc + TV(0, 1) * dL_db;  // reference drops the dL_dcovyz term (backward.cu:263-265)
     const float dL_dT12 = 2 * TV(1, 2) * dL_dc + TV(0, 2) * dL_db;  // idem (backward.cu:266-268)
-    // full dL/dA (A = Jm * R_cw) for the pose gradient: row 1 with the dL_dcovyz terms the reference's mean path
-    // drops, row 2 (constant-Jacobian row, only reaches cov_zx / cov_yz)
-    float dA1[3] = {dL_dT10, dL_dT11 + TV(2, 1) * dL_dcovyz, dL_dT12 + TV(2, 2) * dL_dcovyz};
-    float dA2[3] = {dL_dcovzx * TV(0, 0) + dL_dcovyz * TV(1, 0), dL_dcovzx * TV(0, 1) + dL_dcovyz * TV(1, 1),
-                    dL_dcovzx * TV(0, 2) + dL_dcovyz * TV(1, 2)};
+    // ---- camera gradient: the same chain once more with the TRUE partials (it has no reference to stay compatible
+    // with; pinned by finite differences over a 6-dof twist, tests/test_pose_fd_gpu.py): dL/dA rows 0..2 with
+    // A = Jm * R_cw, row 1 including the dL_dcovyz terms the reference's mean path drops (backward.cu:263-268), row 2
+    // (constant-Jacobian row, only reaches cov_zx / cov_yz) which the reference never needs ----
+    float dA0[3] = {0.f, 0.f, 0.f}, dA1[3] = {0.f, 0.f, 0.f}, dA2[3] = {0.f, 0.f, 0.f};
+    if (want_pose) {
+      float da_t = 0, db_t = 0, dc_t = 0;
+      if (denom2inv != 0) {
+        da_t = denom2inv * (-c * c * dL_dconic.x + 2 * b * c * conicy_true + (denom - a * c) * dL_dconic.z);
+        dc_t = denom2inv * (-a * a * dL_dconic.z + 2 * a * b * conicy_true + (denom - a * c) * dL_dconic.x);
+        db_t = denom2inv * 2 * (b * c * dL_dconic.x - (denom + 2 * b * b) * conicy_true + a * b * dL_dconic.z);
+      }
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        dA0[k] = 2 * TV(0, k) * da_t + TV(1, k) * db_t + TV(2, k) * dL_dcovzx;
+        dA1[k] = 2 * TV(1, k) * dc_t + TV(0, k) * db_t + TV(2, k) * covyz_true;
+        dA2[k] = dL_dcovzx * TV(0, k) + covyz_true * TV(1, k);
+      }
+    }
 #undef TV
 #undef TT
     const float* V = cs.V;
@@ -200,9 +221,16 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
                          (2 * h_y * c2.ty) * tz3 * dL_dJ12;
     if (want_pose) {
       const float p4[4] = {mean.x, mean.y, mean.z, 1.f};
-      const float dA0[3] = {dL_dT00, dL_dT01, dL_dT02};
       const float Jm00 = h_x * tz, Jm11 = h_y * tz, Jm02 = -h_x * c2.tx * tz2, Jm12 = -h_y * c2.ty * tz2;
-      const float dtr[3] = {dL_dtx, dL_dty, dL_dtz + g[8]};  // g[8] = dL/d(depth), depth = t.z
+      const float dJ00p = V[0] * dA0[0] + V[4] * dA0[1] + V[8] * dA0[2];
+      const float dJ02p = V[2] * dA0[0] + V[6] * dA0[1] + V[10] * dA0[2];
+      const float dJ11p = V[1] * dA1[0] + V[5] * dA1[1] + V[9] * dA1[2];
+      const float dJ12p = V[2] * dA1[0] + V[6] * dA1[1] + V[10] * dA1[2];
+      const float dtx_p = x_grad_mul * -h_x * tz2 * dJ02p;
+      const float dty_p = y_grad_mul * -h_y * tz2 * dJ12p;
+      const float dtz_p = -h_x * tz2 * dJ00p - h_y * tz2 * dJ11p + (2 * h_x * c2.tx) * tz3 * dJ02p +
+                          (2 * h_y * c2.ty) * tz3 * dJ12p;
+      const float dtr[3] = {dtx_p, dty_p, dtz_p + g[8]};  // g[8] = dL/d(depth), depth = t.z
 #pragma unroll
       for (int c = 0; c < 4; c++) {
         pv[0 + c] = dtr[0] * p4[c];

@@ -164,3 +164,41 @@ def test_cls3d_oracle_matches_golden_vectors_from_the_reference_loss_code():
         assert abs(loss - z["loss"]) <= 1e-4 * abs(z["loss"]), (f, loss, z["loss"])
         d = np.abs(grad - z["grad"]).max(1)
         assert (d > 1e-5 * np.abs(z["grad"]).max()).mean() <= 2e-3, f
+
+
+def test_pose_fd_machinery_against_the_double_oracles_own_backward():
+    """tests/pose_fd.py (double-precision oracle + central differences over a camera twist, the pin of the camera-pose
+    gradient) checked on the CPU against the double oracle's own analytic gradients through the rigid-motion identity:
+    moving the camera by exp(eps G^) equals moving every Gaussian by V0^-1 exp(eps G^) V0 (SH degree 0, no depth
+    upstream gradient: the reference's mean path drops two dL_dcovyz terms there, backward.cu:263-268)."""
+    from oracle import pyoracle as po
+    from pose_fd import PoseFD, twist_matrix, drop_clamped
+    W, H, P, F = 96, 64, 300, 16
+    cam = scenes.make_camera(W, H, 1)
+    sc = drop_clamped(scenes.make_scene(P, sh_degree=0, F=F, seed=77, W=W, H=H, scale_mul=4.0, behind_frac=0.0), cam)
+    gd, gc, go = [g * (W * H) for g in scenes.make_upstream_grads(W, H, F, seed=3)]
+    grads = (np.zeros_like(gd), gc, go)
+    fd = PoseFD(sc, cam, grads)
+    pr = po.Problem(sc, cam, f64=True)
+    st = po.forward(pr)
+    g = po.backward(pr, st, *grads)
+    dmean, dcov = g["dL_dmean3D"], g["dL_dcov3D"]
+    q = sc.rotations.astype(np.float64)
+    x, y, z, w = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+    Rm = np.stack([1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y),
+                   2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x),
+                   2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)], 1).reshape(-1, 3, 3)
+    Sigma = np.einsum("nij,nj,nkj->nik", Rm, sc.scales.astype(np.float64) ** 2, Rm)
+    dS = np.zeros_like(Sigma)
+    dS[:, 0, 0], dS[:, 1, 1], dS[:, 2, 2] = dcov[:, 0], dcov[:, 3], dcov[:, 5]
+    dS[:, 0, 1] = dS[:, 1, 0] = 0.5 * dcov[:, 1]
+    dS[:, 0, 2] = dS[:, 2, 0] = 0.5 * dcov[:, 2]
+    dS[:, 1, 2] = dS[:, 2, 1] = 0.5 * dcov[:, 4]
+    p = sc.means3D.astype(np.float64)
+    for xi in ((0, 0, 0, 1, 0, 0), (0, 0, 0, 0.2, -0.4, 1.0), (0.5, 0.3, -0.8, 0, 0, 0), (0.2, -0.1, 0.4, 0.3, 0.3, -0.2)):
+        d_fd, rich = fd.derivative(xi)
+        Gw = fd.V0inv @ twist_matrix(xi) @ fd.V0          # the same motion on the world side
+        K, t = Gw[:3, :3], Gw[:3, 3]
+        d_an = (dmean * (p @ K.T + t)).sum() + (dS * (K @ Sigma + Sigma @ K.T)).sum()
+        assert rich <= 1e-5 * max(abs(d_fd), 1.0), (xi, rich)
+        assert abs(d_fd - d_an) <= 1e-5 * max(abs(d_fd), abs(d_an), 1e-3), (xi, d_fd, d_an)
