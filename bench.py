@@ -631,6 +631,39 @@ def pose_backward_leg(args, wl, steps=32):
                      "per-Gaussian outputs) vs the full mapping backward + the 27 camera sums" % wl.P)
 
 
+def libtorch_cpp_leg(args, wl, steps=32):
+    """north_star: "host code stays C++ with LibTorch tensors": the same keyframes driven by bin/mapping_harness, a pure
+    C++ / LibTorch process (csrc/mapping_harness.cpp -> csrc/torch_binding.cpp, the reference's operator signatures ->
+    the C ABI); dense reference output contract, its own CUDA-event timing."""
+    import struct
+    import tempfile
+    import numpy as np
+    exe = os.path.join(PKG, "bin", "mapping_harness")
+    if not os.path.exists(exe):
+        return dict(error="bin/mapping_harness not built")
+    sc, a = wl.scene, args
+    with tempfile.NamedTemporaryFile(suffix=".bin", delete=False) as f:
+        path = f.name
+        f.write(struct.pack("<7i2f", wl.P, wl.M, a.F, a.width, a.height, a.deg, wl.K, wl.cams[0].tanfovx, wl.cams[0].tanfovy))
+        for arr in (sc.bg, sc.means3D, sc.shs, sc.sh_objs, sc.opacities, sc.scales, sc.rotations):
+            f.write(np.ascontiguousarray(arr, np.float32).tobytes())
+        for c in wl.cams:
+            for arr in (c.viewmatrix, c.projmatrix, c.campos):
+                f.write(np.ascontiguousarray(arr, np.float32).tobytes())
+        for g in wl.g:
+            f.write(g.detach().cpu().numpy().astype(np.float32).tobytes())
+    try:
+        r = subprocess.run([exe, path, str(steps), "6"], capture_output=True, text=True, timeout=300)
+    finally:
+        os.unlink(path)
+    if r.returncode != 0:
+        return dict(error=("rc %d: " % r.returncode) + r.stderr[-200:])
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    out["note"] = "bin/mapping_harness: C++ / LibTorch host (no Python in the process), reference operator signatures, " \
+                  "dense outputs, same keyframes"
+    return out
+
+
 def knn_leg(hbm_gbs, P=5_000_000):
     """BASELINE config 5 / metric (iv): simple-knn distCUDA2 over 5M LiDAR points; the reference build
     (oracle/_ref/libref_knn.so: KNN/simple_knn.cu:185-221) timed beside it when it was shipped."""
@@ -1089,6 +1122,7 @@ def main():
 
         leg("render_fps", lambda: render_fps_leg(wl))
         leg("dropin_dense", lambda: dropin_dense_leg(args, wl))
+        leg("libtorch_cpp", lambda: libtorch_cpp_leg(args, wl))
         leg("pose_backward", lambda: pose_backward_leg(args, wl))
         out["pose_backward_ms"] = out["pose_backward"].get("tracking_mode_ms")
         leg("optimizer_n1", lambda: optimizer_leg(args, int(r["stats"]["touched_rows"]), pk["hbm_gbs"]))

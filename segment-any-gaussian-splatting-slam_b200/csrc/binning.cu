@@ -10,6 +10,7 @@
 //
 // Radix passes are an in-house stable 8-bit LSD pass: per-block digit histogram -> per-digit
 // scan over blocks -> ranked scatter (warp match_any ranking, no atomics on the data path).
+#include <cstdlib>
 #include "common.cuh"
 
 namespace gsr {
@@ -294,10 +295,168 @@ offsets_kernel(int gx, int gy, SuperGrid sg, int use_smem, int* __restrict__ sat
   }
 }
 
+// =================================================================================================
+// Single-pass ("onesweep") radix sort of the depth keys: one upfront kernel builds the digit histograms of all four
+// passes, then every pass is ONE kernel whose tiles chain their per-digit prefixes with decoupled look-back
+// (Merrill & Garland's single-pass scan, as CUB's onesweep -- the reference's sort, rasterizer_impl.cu:312-317 -- does):
+// a tile publishes its local digit counts, walks back over its predecessors' status words until it meets one that
+// already holds an inclusive prefix, and publishes its own. 5 launches + 1 memset instead of 12 launches; every key is
+// read once per pass instead of twice. Tiles take their index from an atomic counter, so every predecessor of a
+// running tile is itself running or done: the look-back cannot deadlock. A status word carries value and state in one
+// 32-bit store (top two bits: 0 empty, 1 local count, 2 inclusive prefix), so no further ordering is needed.
+// Stable: items keep their order inside a tile (warp-striped ranking below), tiles keep the order of the input.
+// =================================================================================================
+constexpr uint32_t OS_LOCAL = 1u << 30, OS_INCL = 2u << 30, OS_MASK = (1u << 30) - 1;
+
+__global__ void __launch_bounds__(SORT_THREADS)
+onesweep_hist_kernel(const uint64_t* __restrict__ in, int64_t n, uint32_t* __restrict__ hist /* [4][256] */) {
+  __shared__ uint32_t h[4][RADIX];
+  for (int i = threadIdx.x; i < 4 * RADIX; i += SORT_THREADS) (&h[0][0])[i] = 0;
+  __syncthreads();
+  const int64_t base = (int64_t)blockIdx.x * SORT_TILE;
+#pragma unroll 2
+  for (int k = 0; k < SORT_IPT; k++) {
+    const int64_t i = base + (int64_t)k * SORT_THREADS + threadIdx.x;
+    const bool ok = i < n;
+    const uint32_t key = ok ? (uint32_t)(in[i] >> 32) : 0u;
+#pragma unroll
+    for (int p = 0; p < 4; p++) {
+      // depth digits are heavily skewed: aggregate equal digits inside the warp first (one shared atomic per value)
+      const uint32_t d = ok ? (key >> (8 * p)) & 255u : 0xffffffffu;
+      const unsigned peers = __match_any_sync(0xffffffffu, d);
+      if (ok && (threadIdx.x & 31) == (unsigned)__ffs(peers) - 1) atomicAdd(&h[p][d], (uint32_t)__popc(peers));
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 4 * RADIX; i += SORT_THREADS) {
+    const uint32_t v = (&h[0][0])[i];
+    if (v) atomicAdd(&hist[i], v);
+  }
+}
+
+__global__ void __launch_bounds__(SORT_THREADS)
+onesweep_pass_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out, int64_t n, int pass,
+                     const uint32_t* __restrict__ hist, uint32_t* __restrict__ counters,
+                     volatile uint32_t* __restrict__ status) {
+  constexpr int NWARP = SORT_THREADS / 32;
+  __shared__ uint32_t wc[NWARP][RADIX + 1];
+  __shared__ uint32_t digit_base[RADIX];
+  __shared__ uint32_t warp_sums[NWARP];
+  __shared__ uint32_t tile_s;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int shift = 32 + 8 * pass;
+  if (threadIdx.x == 0) tile_s = atomicAdd(&counters[pass], 1u);
+  for (int i = threadIdx.x; i < NWARP * (RADIX + 1); i += SORT_THREADS) (&wc[0][0])[i] = 0;
+  __syncthreads();
+  const uint32_t tile = tile_s;
+
+  // exclusive scan of this pass's 256 digit totals (one per thread): where every digit's run starts in the output
+  uint32_t gbase;
+  {
+    const uint32_t v = hist[pass * RADIX + threadIdx.x];
+    uint32_t incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    if (lane == 31) warp_sums[warp] = incl;
+    __syncthreads();
+    uint32_t woff = 0;
+    for (int w = 0; w < warp; w++) woff += warp_sums[w];
+    gbase = woff + incl - v;
+  }
+
+  // Item order inside a tile is warp-striped: item = base + warp*256 + k*32 + lane, so (warp, k, lane) lexicographic
+  // order == memory order and the ranking below is stable.
+  const int64_t base = (int64_t)tile * SORT_TILE + warp * (32 * SORT_IPT);
+  uint64_t item[SORT_IPT];
+  uint32_t rank[SORT_IPT];
+#pragma unroll
+  for (int k = 0; k < SORT_IPT; k++) {
+    const int64_t i = base + k * 32 + lane;
+    item[k] = i < n ? in[i] : 0;
+  }
+#pragma unroll
+  for (int k = 0; k < SORT_IPT; k++) {
+    const int64_t i = base + k * 32 + lane;
+    const uint32_t d = i < n ? ((uint32_t)(item[k] >> shift) & 255u) : RADIX;  // RADIX = "invalid" bin
+    const unsigned peers = __match_any_sync(0xffffffffu, d);
+    const int leader = __ffs(peers) - 1;
+    uint32_t prior = 0;
+    if (lane == leader) {
+      prior = wc[warp][d];
+      wc[warp][d] = prior + __popc(peers);
+    }
+    prior = __shfl_sync(0xffffffffu, prior, leader);
+    rank[k] = prior + __popc(peers & ((1u << lane) - 1));
+    __syncwarp();
+  }
+  __syncthreads();
+  // thread d: exclusive prefix of digit d over the warps, local count, then the chained scan over the tiles
+  {
+    const int d = threadIdx.x;
+    uint32_t run = 0;
+#pragma unroll
+    for (int w = 0; w < NWARP; w++) {
+      const uint32_t t = wc[w][d];
+      wc[w][d] = run;
+      run += t;
+    }
+    volatile uint32_t* mine = status + (size_t)tile * RADIX + d;
+    *mine = (tile == 0 ? OS_INCL : OS_LOCAL) | run;
+    // Look-back in windows of LB predecessors whose status words are loaded together (LB independent L2 reads in
+    // flight per thread, coalesced over the 256 digits): when all tiles are resident at once -- 489 tiles at 1 M keys
+    // -- a one-word-at-a-time walk is a chain of up to hundreds of dependent L2 round trips (measured: 23 us per pass).
+    constexpr int LB = 16;
+    uint32_t excl = 0;
+    int64_t t = (int64_t)tile - 1;
+    bool done = t < 0;
+    while (!done) {
+      uint32_t v[LB];
+#pragma unroll
+      for (int i = 0; i < LB; i++) v[i] = t - i >= 0 ? status[(size_t)(t - i) * RADIX + d] : 0x80000000u /* OS_INCL */;  // before tile 0: prefix 0
+#pragma unroll
+      for (int i = 0; i < LB; i++) {
+        if (done) break;
+        if (v[i] & OS_INCL) { excl += v[i] & OS_MASK; done = true; }
+        else if (v[i] & OS_LOCAL) { excl += v[i] & OS_MASK; t--; }
+        else break;  // predecessor t has not published yet (it holds a lower ticket, so it is running): look again from t
+      }
+    }
+    if (tile != 0) *mine = OS_INCL | (excl + run);
+    digit_base[d] = gbase + excl;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < SORT_IPT; k++) {
+    const int64_t i = base + k * 32 + lane;
+    if (i < n) {
+      const uint32_t d = (uint32_t)(item[k] >> shift) & 255u;
+      out[digit_base[d] + wc[warp][d] + rank[k]] = item[k];
+    }
+  }
+}
+
 void launch_depth_sort(int P, GeomState& g, cudaStream_t s, int& launches) {
   // 4 stable 8-bit passes over the depth bits (item bits 32..63); a -> b -> a -> b -> a
   uint64_t* a = g.dkeys_a;
   uint64_t* b = g.dkeys_b;
+  static const bool v1 = getenv("GSR_SORT_V1") != nullptr;   // A/B: three kernels per pass (histogram, scan, scatter)
+  if (!v1 && (uint32_t)P <= OS_MASK) {
+    const int nblk = sort_blocks(P);
+    uint32_t* hist = g.onesweep;
+    uint32_t* counters = hist + 4 * RADIX;
+    uint32_t* status = counters + 16;
+    cudaMemsetAsync(g.onesweep, 0, onesweep_words(P) * sizeof(uint32_t), s);   // histograms, tickets, 4 status regions
+    onesweep_hist_kernel<<<nblk, SORT_THREADS, 0, s>>>(a, P, hist);
+    for (int pass = 0; pass < 4; pass++) {
+      onesweep_pass_kernel<<<nblk, SORT_THREADS, 0, s>>>(a, b, P, pass, hist, counters, status + (size_t)pass * RADIX * nblk);
+      uint64_t* t = a; a = b; b = t;
+    }
+    launches += 5;
+    return;
+  }
   for (int pass = 0; pass < 4; pass++) {
     radix_pass(a, b, P, 32 + 8 * pass, 8, g.block_hist, g.digit_total, s, launches);
     uint64_t* t = a; a = b; b = t;

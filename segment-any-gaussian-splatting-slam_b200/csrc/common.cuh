@@ -50,6 +50,7 @@ constexpr int EMIT_THREADS = 256;
 __host__ __device__ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 inline int sort_blocks(int64_t n) { return (int)((n + SORT_TILE - 1) / SORT_TILE); }
 inline int emit_blocks(int64_t n) { return (int)((n + EMIT_THREADS - 1) / EMIT_THREADS); }
+inline size_t onesweep_words(int64_t n) { return 4 * RADIX + 16 + 4 * (size_t)RADIX * sort_blocks(n); }
 
 struct GeomState {
   float4* rec;
@@ -62,6 +63,7 @@ struct GeomState {
   uint32_t* block_hist;   // 256 * sort_blocks(P)
   uint32_t* digit_total;  // 256
   uint32_t* block_sums;   // emit_blocks(P) + 8
+  uint32_t* onesweep;     // single-pass depth sort: [4][256] digit histograms, [16] tile counters, [4][tiles][256] tile status
   int* flags;             // [0] num_rendered, [1] prefiltered-cull error, [2..3] L1 list total (u64)
   float* grad_rows;       // P * 32 (F=16) or P * 64 (F=32): backward intermediate, see render_bwd.cu
   uint8_t* touched;       // P (directly behind grad_rows, one memset): 1 = the backward blend wrote this Gaussian's row
@@ -121,6 +123,7 @@ inline size_t geom_from_chunk(char* chunk, size_t P, GeomState& g, int F = 32) {
   carve(p, g.block_hist, (size_t)RADIX * sort_blocks((int64_t)P));
   carve(p, g.digit_total, RADIX);
   carve(p, g.block_sums, (size_t)emit_blocks((int64_t)P) + 8);
+  carve(p, g.onesweep, onesweep_words((int64_t)P));
   carve(p, g.flags, 8);
   carve(p, g.pose_acc, 32);
   carve(p, g.grad_rows, P * (size_t)grad_row_floats(F));

@@ -195,6 +195,10 @@ class _Resizer:
 
     _pools = {}
     _POOL_MAX = 8
+    # Diagnostics (tests/gpu_sanitize.py; compute-sanitizer is closed on the GPU pool): the slack behind the requested
+    # size is filled with a pattern before the kernels run and verified in take(): a write past the end of a scratch
+    # buffer raises instead of corrupting a neighbour.
+    debug_canary = False
 
     def __init__(self, device, role=""):
         self.device = device
@@ -203,6 +207,13 @@ class _Resizer:
         self.cb = ALLOC_FN(self._alloc)
 
     def _alloc(self, _ctx, n):
+        p = self._alloc_impl(n)
+        if _Resizer.debug_canary:
+            self.req = int(n)
+            self.t[self.req:].fill_(0xA5)
+        return p
+
+    def _alloc_impl(self, n):
         n = int(n) + 256
         pool = _Resizer._pools.setdefault(self.key, [])
         best = None
@@ -233,6 +244,11 @@ class _Resizer:
         """Hand the buffer to the caller and break the self -> callback -> bound method -> self cycle, so that the
         buffer's life ends with the caller's reference and not at the next cyclic-GC run."""
         t, self.t, self.cb = self.t, None, None
+        if _Resizer.debug_canary and getattr(self, "req", None) is not None and t is not None and t.numel():
+            torch.cuda.synchronize(t.device)
+            if not bool((t[self.req:] == 0xA5).all()):
+                raise RuntimeError("gsraster_b200: a kernel wrote past the end of the %s scratch buffer (%d bytes requested)"
+                                   % (self.key[1], self.req))
         return t
 
 
