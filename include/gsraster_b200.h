@@ -179,7 +179,11 @@ int gsr_export_state(const gsr_params* params, int num_rendered, const char* geo
 /* Sizes of the three scratch buffers (what the allocators will be asked for). */
 size_t gsr_geom_bytes(int P);
 size_t gsr_image_bytes(int width, int height);
-size_t gsr_binning_bytes(int64_t num_rendered);
+size_t gsr_binning_bytes(int64_t num_rendered);   /* point list + blend masks: what gsr_backward reads */
+/* Safe upper bound of what the binning allocator of gsr_forward can be asked for (point list, blend masks, supertile
+ * lists of at most min(R, P x supertiles) entries, per-(supertile, block) counters): for hosts that pre-size a fixed
+ * buffer. The `bytes` argument of the allocator callback remains the authoritative figure of a call. */
+size_t gsr_binning_bytes_bound(int64_t num_rendered, int P, int width, int height);
 
 /* Per-stage device timing for the roofline report (bench.py): a forward / backward call that is handed a timer
  * (gsr_ext::timer) brackets each of its stages with CUDA events on params->stream. gsr_timer_read synchronises those

@@ -194,6 +194,15 @@ size_t gsr_binning_bytes(int64_t R) {
   return gsr::bin_from_chunk(nullptr, (size_t)(R > 0 ? R : 1), 0, 0, b);
 }
 
+size_t gsr_binning_bytes_bound(int64_t R, int P, int width, int height) {
+  gsr::BinState b;
+  const int gx = (width + gsr::TILE_X - 1) / gsr::TILE_X, gy = (height + gsr::TILE_Y - 1) / gsr::TILE_Y;
+  const size_t NS = (size_t)gsr::super_grid(gx > 0 ? gx : 1, gy > 0 ? gy : 1).NS;
+  const size_t r = (size_t)(R > 0 ? R : 1), pp = (size_t)(P > 0 ? P : 1);
+  const size_t l1 = r < pp * NS ? r : pp * NS;   // every overlapped supertile holds at least one covered tile
+  return gsr::bin_from_chunk(nullptr, r, l1, ((pp + 255) / 256) * NS, b);
+}
+
 int gsr_forward(const gsr_params* p, gsr_alloc_fn geom_alloc, void* geom_ctx, gsr_alloc_fn binning_alloc,
                 void* binning_ctx, gsr_alloc_fn image_alloc, void* image_ctx, const float* background,
                 const float* means3D, const float* shs, const float* sh_objs, const float* colors_precomp,

@@ -166,6 +166,12 @@ def test_stage_timer_and_stats_are_per_call():
                                  d["viewmatrix"], d["projmatrix"], cam.tanfovx, cam.tanfovy, cam.H, cam.W, d["shs"],
                                  d["sh_objs"], sc.sh_degree, d["campos"], False, False, ext=ext)
     assert ext.stats.num_rendered == r[0] > 0 and ext.stats.launches >= 5 and ext.stats.l1_total > 0
+    import ctypes as C
+    L = capi.lib()
+    L.gsr_binning_bytes_bound.restype = C.c_size_t
+    L.gsr_binning_bytes_bound.argtypes = [C.c_int64, C.c_int, C.c_int, C.c_int]
+    # the pre-sizing bound covers point list + blend masks + the supertile lists this call really built
+    assert L.gsr_binning_bytes_bound(r[0], sc.P, cam.W, cam.H) >= L.gsr_binning_bytes(r[0]) + 8 * ext.stats.l1_total
     ms, gaps = t.read()
     assert all(ms[k] > 0 for k in ("preprocess", "depth_sort_offsets", "binning", "render_fwd"))
     assert ms["render_bwd"] == 0 and ms["preprocess_bwd"] == 0

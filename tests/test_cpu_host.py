@@ -43,6 +43,13 @@ def test_scratch_sizes_are_pure_functions_and_monotonic():
     assert L.gsr_image_bytes(1280, 1024) >= 1280 * 1024 * 8 + 5120 * 8
     assert L.gsr_binning_bytes(10**6) >= 10**6 * 4
     assert L.gsr_binning_bytes(0) > 0
+    L.gsr_binning_bytes_bound.restype = C.c_size_t
+    L.gsr_binning_bytes_bound.argtypes = [C.c_int64, C.c_int, C.c_int, C.c_int]
+    # the bound covers the supertile lists (<= min(R, P * supertiles) entries of 8 B) on top of point list + masks
+    assert L.gsr_binning_bytes_bound(10**6, 10**5, 1280, 1024) >= L.gsr_binning_bytes(10**6) + 8 * 10**6
+    assert L.gsr_binning_bytes_bound(10**9, 1000, 1280, 1024) <= L.gsr_binning_bytes(10**9) + 8 * 1000 * 80 + 4 * 4 * 80 + 4096
+    L.gsr_row_workspace_bytes.restype = C.c_size_t
+    assert L.gsr_row_workspace_bytes(1000, 16) >= 1000 * (32 * 4 + 1) and L.gsr_row_workspace_bytes(1000, 32) >= 1000 * (64 * 4 + 1)
     assert L.gsr_knn_scratch_bytes(5_000_000) >= 5_000_000 * 32
 
 
