@@ -3,7 +3,7 @@
 // render_bwd.cu (one scalar suffix sum per pixel, raw moments reduced on the tensor cores, per-Gaussian coefficients
 // applied in K7) -- see the header of render_bwd.cu. render_bwd.cu stays as the A/B baseline (GSR_BWD_V1=1).
 //
-// Why (ncu, profiles/r02_ncu_render_base.csv): render_bwd_kernel issues ~90 instructions per (warp, Gaussian) hit of
+// Why (ncu, profiles/r02_ncu_render_kernels.txt, first block): render_bwd_kernel issues ~90 instructions per (warp, Gaussian) hit of
 // which 8 LDS.128 + the walk / slot bookkeeping are per-Gaussian overhead paid once per 32 pixels, 40 are the scalar
 // FFMAs of the 20-term dot product E, and every (warp, Gaussian) pair ends in a result-tile transpose, a centre shift
 // and 8 red.global.add.v4 (1 433 per touched row on the headline scene); 111 registers and 108 KB of shared memory

@@ -2,7 +2,7 @@
 // Behaviour: reference forward.cu:280-436 (checklist 11-14), identical to render_fwd.cu (which stays
 // as the A/B baseline, GSR_FWD_V1=1).
 //
-// Why: ncu on render_fwd_kernel (profiles/r02_ncu_render_base.csv) shows 87 % of the issue slots busy with the FMA pipe
+// Why: ncu on render_fwd_kernel (profiles/r02_ncu_render_kernels.txt, first block) shows 87 % of the issue slots busy with the FMA pipe
 // at 48 %: the kernel is bound by ISSUED INSTRUCTIONS, ~95 per (warp, Gaussian) iteration of which only ~50 are the
 // per-pixel arithmetic; the rest (8 LDS.128 of the staged record, candidate selection, votes, mask bookkeeping, loop
 // control) is per-Gaussian overhead that one pixel per thread pays for every 32 pixels. Here
