@@ -282,7 +282,10 @@ int gsr_photometric_loss(const float* img, const float* gt, int H, int W, float 
  * gt (H*W) int64 labels, a label outside [0, C) contributes neither loss nor gradient (torch's ignore_index = -100)
  * while the mean still runs over all H*W pixels; dL_dobjects (F, H, W) = grad_weight * d loss_obj / d objects (may be
  * NULL: value only); pred (H*W) int32 (may be NULL); out2 (device float[2]) = {loss_obj, mean cross-entropy};
- * scratch: gsr_feature_loss_scratch_bytes() bytes. F in {16, 32}, 2 <= C <= 256. The logits never reach HBM.
+ * scratch: gsr_feature_loss_scratch_bytes() bytes. F in {16, 32}, 2 <= C <= 256; weight 16-byte aligned. The logits
+ * never reach HBM. C <= 112 (the reference's 100 classes) runs on the 5th-generation tensor cores (tcgen05.mma
+ * kind::tf32 with a 3xTF32 split, accumulators and the softmax gradient operand in TMEM: csrc/featloss_tc.cu); larger C,
+ * or GSR_FEATLOSS_MMA_SYNC=1 in the environment, takes the mma.sync kernel (csrc/featloss.cu).
  * The classifier's own gradient is not produced (the reference never steps cls_optimizer, :217). */
 size_t gsr_feature_loss_scratch_bytes(void);
 int gsr_feature_loss(const float* objects, const long long* gt, int H, int W, int F, int C, const float* weight,

@@ -582,6 +582,8 @@ int gsr_feature_loss(const float* objects, const long long* gt, int H, int W, in
                      void* stream_) {
   if (!objects || !gt || !weight || !bias || !out2 || !scratch || H <= 0 || W <= 0)
     return fail(GSR_ERR_INVALID_ARGUMENT, "feature_loss: bad argument");
+  if (reinterpret_cast<uintptr_t>(weight) & 15)
+    return fail(GSR_ERR_INVALID_ARGUMENT, "feature_loss: weight must be 16-byte aligned");
   if (!gsr::launch_feature_loss(objects, gt, H * W, F, C, weight, bias, grad_weight, dL_dobjects, pred, out2, scratch,
                                 (cudaStream_t)stream_))
     return fail(GSR_ERR_INVALID_ARGUMENT, "feature_loss: F must be 16 or 32 and 2 <= C <= 256 (got F=%d C=%d)", F, C);

@@ -267,6 +267,10 @@ void launch_fl(const float* obj, const long long* gt, int HW, int C, const float
 
 }  // namespace
 
+int launch_feature_loss_tc(const float* obj, const long long* gt, int HW, int F, int C, const float* weight,
+                           const float* bias, float gscale, float* dobj, int* pred, float* partial, int max_grid,
+                           cudaStream_t s);  // featloss_tc.cu
+
 size_t feature_loss_scratch_bytes() { return FL_MAX_GRID * sizeof(float); }
 
 // objects (F, H*W), gt (H*W) int64, weight (C, F), bias (C); dobj = grad_weight * d loss / d objects (or null);
@@ -279,6 +283,13 @@ bool launch_feature_loss(const float* obj, const long long* gt, int HW, int F, i
   int grid = (ntile + 7) / 8;
   if (grid > FL_MAX_GRID) grid = FL_MAX_GRID;
   const float gscale = (float)((double)grad_weight / ((double)HW * log((double)C)));
+  // default for C <= 112: the tcgen05 / TMEM kernel (featloss_tc.cu); GSR_FEATLOSS_MMA_SYNC=1 keeps the mma.sync one
+  const bool mma_sync_only = getenv("GSR_FEATLOSS_MMA_SYNC") != nullptr;
+  if (C <= 112 && !mma_sync_only) {
+    grid = launch_feature_loss_tc(obj, gt, HW, F, C, weight, bias, gscale, dobj, pred, partial, FL_MAX_GRID, s);
+    feature_loss_finalize_kernel<<<1, 256, 0, s>>>(partial, grid, HW, C, out2);
+    return true;
+  }
 #define GSR_FL(F_, NT_) launch_fl<F_, NT_>(obj, gt, HW, C, weight, bias, gscale, dobj, pred, partial, grid, s)
   if (F == 16) {
     if (C <= 104) GSR_FL(16, 13);

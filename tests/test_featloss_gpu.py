@@ -76,3 +76,31 @@ def test_feature_loss_rejects_bad_arguments():
     with pytest.raises(RuntimeError):
         _run(torch.zeros(8, 8, 8, device=dev), torch.zeros(8, 8, dtype=torch.int64, device=dev),
              torch.zeros(100, 8, device=dev), b)
+
+
+@pytest.mark.parametrize("F,C,H,W", [(16, 100, 480, 640), (32, 100, 123, 77), (16, 112, 64, 65), (32, 7, 33, 129),
+                                     (16, 19, 1, 1), (16, 100, 1, 127)])
+def test_tcgen05_kernel_matches_mma_sync_kernel(F, C, H, W):
+    """featloss_tc.cu (tcgen05.mma kind::tf32, accumulators and the d operand in TMEM; default for C <= 112) against
+    featloss.cu (mma.sync; GSR_FEATLOSS_MMA_SYNC=1) on the same inputs: same 3xTF32 split, so the two agree far inside
+    the reference tolerance; ragged tiles (H*W not a multiple of 128), ignored labels, one-pixel images."""
+    torch.manual_seed(7 * F + C)
+    dev = "cuda"
+    objects = 1.5 * torch.randn(F, H, W, device=dev)
+    gt = torch.randint(0, C, (H, W), device=dev)
+    gt[torch.rand(H, W, device=dev) < 0.1] = -100
+    w, b = 0.3 * torch.randn(C, F, device=dev), 0.5 * torch.randn(C, device=dev)
+    a = _run(objects, gt, w, b, grad_weight=1.3)
+    os.environ["GSR_FEATLOSS_MMA_SYNC"] = "1"
+    try:
+        m = _run(objects, gt, w, b, grad_weight=1.3)
+    finally:
+        del os.environ["GSR_FEATLOSS_MMA_SYNC"]
+    assert abs(float(a[0][0]) - float(m[0][0])) <= 2e-6 * max(1.0, abs(float(m[0][0])))
+    assert abs(float(a[0][1]) - float(m[0][1])) <= 1e-5 * max(1.0, abs(float(m[0][1])))
+    gmax = float(m[1].abs().max())
+    assert float((a[1] - m[1]).abs().max()) <= 2e-5 * gmax + 1e-12
+    assert float((a[2] == m[2]).float().mean()) >= 0.999
+    # deterministic: a second call returns the same bits
+    a2 = _run(objects, gt, w, b, grad_weight=1.3)
+    assert torch.equal(a[1], a2[1]) and float(a[0][0]) == float(a2[0][0])
