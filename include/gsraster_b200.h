@@ -140,10 +140,16 @@ int gsr_backward(const gsr_params* params, int num_rendered,
 /* EXTENSION (no reference equivalent: the reference never differentiates w.r.t. the camera):
  * gsr_backward plus the gradients w.r.t. the three camera inputs of gsr_forward, each treated as an independent
  * input: dL_dviewmatrix[16] and dL_dprojmatrix[16] (column-major flat like the inputs; the unused rows -- row 3 of
- * the view matrix, row 2 of the projection matrix -- are zero) and dL_dcampos[3]. The t = V p path reuses the
- * reference's per-Gaussian intermediates (including its dropped dL_dcovyz terms, backward.cu:263-268), so that at SH
- * degree 0 the rigid-motion identity "moving the camera == moving every Gaussian the other way" holds exactly
- * against dL_dmean3D / dL_dcov3D. The 27 sums are reduced warp -> block -> double-precision atomics. */
+ * the view matrix, row 2 of the projection matrix -- are zero) and dL_dcampos[3]. The camera side carries the TRUE
+ * derivative of the forward pass: three shortcuts of the reference's world-space backward (the dL_dcovyz terms it
+ * drops from T, backward.cu:263-268; the -c dy term missing from its cov_yz partial; the depth part of dL_dconic.y
+ * counted twice) are corrected on this path only -- the 11 reference outputs keep the reference's values bit for
+ * bit. Pinned by central differences of the double-precision oracle over a 6-dof twist (tests/test_pose_fd_gpu.py:
+ * SH degree 3, colour + depth + features, ~1e-6 relative on every degree of freedom); parity unpinned by the
+ * reference by construction. With a zero depth upstream gradient the rigid-motion identity "moving the camera ==
+ * moving every Gaussian the other way" holds against dL_dmean3D / dL_dcov3D at SH degree 0. Gaussians outside the
+ * +-1.3 tan(fov) clamp of the EWA Jacobian follow the reference's masked derivative (backward.cu:170-178).
+ * The 27 sums are reduced warp -> block -> double-precision atomics. gsr_ext::tracking skips everything but them. */
 int gsr_backward_pose(const gsr_params* params, int num_rendered,
                       const float* background, const float* means3D, const float* shs, const float* sh_objs,
                       const float* colors_precomp, const float* scales, const float* rotations,

@@ -100,10 +100,20 @@ preprocess_kernel(const FwdInputs in, const Cam cam, float4* __restrict__ rec, u
     p_orig = {in.means3D[3 * idx], in.means3D[3 * idx + 1], in.means3D[3 * idx + 2]};
     p_view = xform4x3(p_orig, cs.V);
   }
+  // ... and a Gaussian whose centre projects well outside the image only needs its row if its footprint still reaches
+  // a tile: those decide after the tile-rectangle test below (a quarter of the headline scene never fetches).
+  float4 p_hom = {0.f, 0.f, 0.f, 1.f};
+  bool arrived = !staged_sh;   // this thread has announced its copy (or its absence) on sh_bar
+  if (idx < in.P) p_hom = xform4x4(p_orig, cs.PV);
   if (staged_sh) {
-    const bool fetch = idx < in.P && !(p_view.z <= 0.2f);
-    mbar_arrive_expect_tx(&sh_bar, fetch ? 192u : 0u);
-    if (fetch) tma_load_1d(&sh_tile[threadIdx.x * 13], in.shs + (size_t)idx * 48, 192, &sh_bar);
+    const bool alive = idx < in.P && !(p_view.z <= 0.2f);
+    const float lim = 1.05f * (p_hom.w + 0.0000001f);
+    const bool early = alive && fabsf(p_hom.x) <= lim && fabsf(p_hom.y) <= lim;
+    if (early || !alive) {
+      mbar_arrive_expect_tx(&sh_bar, early ? 192u : 0u);
+      arrived = true;
+    }
+    if (early) tma_load_1d(&sh_tile[threadIdx.x * 13], in.shs + (size_t)idx * 48, 192, &sh_bar);
   }
   if (idx >= in.P) return;  // (these threads issued no copy; the block lives on through the threads that wait below)
 
@@ -116,7 +126,6 @@ preprocess_kernel(const FwdInputs in, const Cam cam, float4* __restrict__ rec, u
       if (in.prefiltered) flags[1] = 1;
       break;
     }
-    float4 p_hom = xform4x4(p_orig, cs.PV);
     float p_w = 1.0f / (p_hom.w + 0.0000001f);
     float3 p_proj = {p_hom.x * p_w, p_hom.y * p_w, p_hom.z * p_w};
 
@@ -153,6 +162,11 @@ preprocess_kernel(const FwdInputs in, const Cam cam, float4* __restrict__ rec, u
     float rgb[3];
     unsigned cbits = 0;
     if (staged_sh) {
+      if (!arrived) {   // centre outside the image, footprint inside: late fetch
+        mbar_arrive_expect_tx(&sh_bar, 192u);
+        tma_load_1d(&sh_tile[threadIdx.x * 13], in.shs + (size_t)idx * 48, 192, &sh_bar);
+        arrived = true;
+      }
       mbar_wait(&sh_bar, 0);
       float4 shl[12];
 #pragma unroll
@@ -193,7 +207,10 @@ preprocess_kernel(const FwdInputs in, const Cam cam, float4* __restrict__ rec, u
   dkeys[idx] = key;
   if (is_used) is_used[idx] = touched > 0;
   // culled threads never looked at the tile, but the block must not retire while bulk copies into it are in flight
-  if (staged_sh) mbar_wait(&sh_bar, 0);
+  if (staged_sh) {
+    if (!arrived) mbar_arrive_expect_tx(&sh_bar, 0u);
+    mbar_wait(&sh_bar, 0);
+  }
 }
 
 void launch_preprocess(const FwdInputs& in, const Cam& cam, GeomState& g, ImageState& img, int* radii,
