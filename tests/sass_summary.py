@@ -2,7 +2,7 @@
   python tests/sass_summary.py > profiles/r02_sass_opcodes.txt
 Per kernel: registers, static instruction count, and the counts of the opcodes that show what the kernel is built on
 (B200_PROFILING.md "What proves a Blackwell-native kernel"): UBLKCP / SYNCS (TMA bulk copies completing on mbarriers),
-FFMA2 (Blackwell packed fp32 FMA), HMMA (warp-level mma.sync), REDG (vector red.global.add), REDUX, MATCH, LDSM, ..."""
+UTCHMMA / LDTM / STTM (tcgen05.mma, tcgen05.ld / st: TMEM), FFMA2 (Blackwell packed fp32 FMA), HMMA (warp-level mma.sync), REDG (vector red.global.add), REDUX, MATCH, LDSM, ..."""
 import collections
 import os
 import re
@@ -11,7 +11,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "segment-any-gaussian-splatting-slam_b200", "lib", "libgsraster_b200.so")
-KEY = ("UBLKCP", "SYNCS", "UTMALDG", "UTCHMMA", "LDTM", "FFMA2", "FMUL2", "FADD2", "HMMA", "REDG", "RED", "REDUX", "MATCH",
+KEY = ("UBLKCP", "SYNCS", "UTMALDG", "UTCHMMA", "UTCBAR", "LDTM", "STTM", "FFMA2", "FMUL2", "FADD2", "HMMA", "REDG", "RED", "REDUX", "MATCH",
        "VOTE", "SHFL", "LDSM", "LDS", "STS", "LDG", "STG", "ATOMG", "ATOMS", "MUFU", "FFMA", "FMUL", "FADD", "BAR", "LDL", "STL")
 
 
@@ -35,7 +35,7 @@ def main():
     print("# %s (sm_100a), cuobjdump -sass: static opcode counts per kernel" % os.path.relpath(LIB, ROOT))
     for (fn, c), name in zip(ops.items(), demangle):
         r = regs.get(fn, (0, 0, 0, 0))
-        short = re.sub(r"\(.*", "", name).replace("gsr::", "").replace("(anonymous namespace)::", "")
+        short = re.sub(r"\(.*", "", name.replace("(anonymous namespace)::", "")).replace("gsr::", "").replace("void ", "")
         keys = " ".join("%s=%d" % (k, c[k]) for k in KEY if c.get(k))
         print("%-52s regs %3d stack %3d  inst %5d | %s" % (short[:52], r[0], r[1], sum(c.values()), keys))
 
