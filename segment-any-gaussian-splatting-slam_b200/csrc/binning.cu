@@ -313,18 +313,21 @@ onesweep_hist_kernel(const uint64_t* __restrict__ in, int64_t n, uint32_t* __res
   __shared__ uint32_t h[4][RADIX];
   for (int i = threadIdx.x; i < 4 * RADIX; i += SORT_THREADS) (&h[0][0])[i] = 0;
   __syncthreads();
-  const int64_t base = (int64_t)blockIdx.x * SORT_TILE;
+  // grid-stride over the 2048-key tiles: at most two blocks per SM flush their 1024 bins into the 32 cache lines of the
+  // global histograms (489 blocks x ~520 non-empty bins serialised in L2 for longer than the counting itself took)
+  for (int64_t base = (int64_t)blockIdx.x * SORT_TILE; base < n; base += (int64_t)gridDim.x * SORT_TILE) {
 #pragma unroll 2
-  for (int k = 0; k < SORT_IPT; k++) {
-    const int64_t i = base + (int64_t)k * SORT_THREADS + threadIdx.x;
-    const bool ok = i < n;
-    const uint32_t key = ok ? (uint32_t)(in[i] >> 32) : 0u;
+    for (int k = 0; k < SORT_IPT; k++) {
+      const int64_t i = base + (int64_t)k * SORT_THREADS + threadIdx.x;
+      const bool ok = i < n;
+      const uint32_t key = ok ? (uint32_t)(in[i] >> 32) : 0u;
 #pragma unroll
-    for (int p = 0; p < 4; p++) {
-      // depth digits are heavily skewed: aggregate equal digits inside the warp first (one shared atomic per value)
-      const uint32_t d = ok ? (key >> (8 * p)) & 255u : 0xffffffffu;
-      const unsigned peers = __match_any_sync(0xffffffffu, d);
-      if (ok && (threadIdx.x & 31) == (unsigned)__ffs(peers) - 1) atomicAdd(&h[p][d], (uint32_t)__popc(peers));
+      for (int p = 0; p < 4; p++) {
+        // depth digits are heavily skewed: aggregate equal digits inside the warp first (one shared atomic per value)
+        const uint32_t d = ok ? (key >> (8 * p)) & 255u : 0xffffffffu;
+        const unsigned peers = __match_any_sync(0xffffffffu, d);
+        if (ok && (threadIdx.x & 31) == (unsigned)__ffs(peers) - 1) atomicAdd(&h[p][d], (uint32_t)__popc(peers));
+      }
     }
   }
   __syncthreads();
@@ -334,11 +337,16 @@ onesweep_hist_kernel(const uint64_t* __restrict__ in, int64_t n, uint32_t* __res
   }
 }
 
-__global__ void __launch_bounds__(SORT_THREADS)
+// IPT keys per thread (tile = 256 IPT keys), look-back window LB. Measured on the headline (1 M keys, sort + offsets
+// serialised on one stream, tests/gpu_sort_time.py): IPT 8 / LB 16: 0.146 ms, LB 64: 0.170, IPT 16 / LB 16: 0.141,
+// IPT 16 / LB 8 at two blocks per SM (245 tiles, all resident): 0.139 -- the default.
+template <int IPT, int LB, int MINB>
+__global__ void __launch_bounds__(SORT_THREADS, MINB)
 onesweep_pass_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out, int64_t n, int pass,
                      const uint32_t* __restrict__ hist, uint32_t* __restrict__ counters,
                      volatile uint32_t* __restrict__ status) {
   constexpr int NWARP = SORT_THREADS / 32;
+  constexpr int TILE = SORT_THREADS * IPT;
   __shared__ uint32_t wc[NWARP][RADIX + 1];
   __shared__ uint32_t digit_base[RADIX];
   __shared__ uint32_t warp_sums[NWARP];
@@ -367,18 +375,18 @@ onesweep_pass_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out
     gbase = woff + incl - v;
   }
 
-  // Item order inside a tile is warp-striped: item = base + warp*256 + k*32 + lane, so (warp, k, lane) lexicographic
+  // Item order inside a tile is warp-striped: item = base + warp*32*IPT + k*32 + lane, so (warp, k, lane) lexicographic
   // order == memory order and the ranking below is stable.
-  const int64_t base = (int64_t)tile * SORT_TILE + warp * (32 * SORT_IPT);
-  uint64_t item[SORT_IPT];
-  uint32_t rank[SORT_IPT];
+  const int64_t base = (int64_t)tile * TILE + warp * (32 * IPT);
+  uint64_t item[IPT];
+  uint32_t rank[IPT];
 #pragma unroll
-  for (int k = 0; k < SORT_IPT; k++) {
+  for (int k = 0; k < IPT; k++) {
     const int64_t i = base + k * 32 + lane;
     item[k] = i < n ? in[i] : 0;
   }
 #pragma unroll
-  for (int k = 0; k < SORT_IPT; k++) {
+  for (int k = 0; k < IPT; k++) {
     const int64_t i = base + k * 32 + lane;
     const uint32_t d = i < n ? ((uint32_t)(item[k] >> shift) & 255u) : RADIX;  // RADIX = "invalid" bin
     const unsigned peers = __match_any_sync(0xffffffffu, d);
@@ -408,7 +416,6 @@ onesweep_pass_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out
     // Look-back in windows of LB predecessors whose status words are loaded together (LB independent L2 reads in
     // flight per thread, coalesced over the 256 digits): when all tiles are resident at once -- 489 tiles at 1 M keys
     // -- a one-word-at-a-time walk is a chain of up to hundreds of dependent L2 round trips (measured: 23 us per pass).
-    constexpr int LB = 16;
     uint32_t excl = 0;
     int64_t t = (int64_t)tile - 1;
     bool done = t < 0;
@@ -429,7 +436,7 @@ onesweep_pass_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out
   }
   __syncthreads();
 #pragma unroll
-  for (int k = 0; k < SORT_IPT; k++) {
+  for (int k = 0; k < IPT; k++) {
     const int64_t i = base + k * 32 + lane;
     if (i < n) {
       const uint32_t d = (uint32_t)(item[k] >> shift) & 255u;
@@ -449,9 +456,11 @@ void launch_depth_sort(int P, GeomState& g, cudaStream_t s, int& launches) {
     uint32_t* counters = hist + 4 * RADIX;
     uint32_t* status = counters + 16;
     cudaMemsetAsync(g.onesweep, 0, onesweep_words(P) * sizeof(uint32_t), s);   // histograms, tickets, 4 status regions
-    onesweep_hist_kernel<<<nblk, SORT_THREADS, 0, s>>>(a, P, hist);
+    onesweep_hist_kernel<<<nblk < 2 * 148 ? nblk : 2 * 148, SORT_THREADS, 0, s>>>(a, P, hist);
+    constexpr int PASS_IPT = 2 * SORT_IPT;   // 4096-key tiles (the status regions are sized for the 2048-key tiles of the histogram kernel)
+    const int npass_blk = (int)(((int64_t)P + SORT_THREADS * PASS_IPT - 1) / (SORT_THREADS * PASS_IPT));
     for (int pass = 0; pass < 4; pass++) {
-      onesweep_pass_kernel<<<nblk, SORT_THREADS, 0, s>>>(a, b, P, pass, hist, counters, status + (size_t)pass * RADIX * nblk);
+      onesweep_pass_kernel<PASS_IPT, 8, 2><<<npass_blk, SORT_THREADS, 0, s>>>(a, b, P, pass, hist, counters, status + (size_t)pass * RADIX * nblk);
       uint64_t* t = a; a = b; b = t;
     }
     launches += 5;
