@@ -308,6 +308,23 @@ offsets_kernel(int gx, int gy, SuperGrid sg, int use_smem, int* __restrict__ sat
 // =================================================================================================
 constexpr uint32_t OS_LOCAL = 1u << 30, OS_INCL = 2u << 30, OS_MASK = (1u << 30) - 1;
 
+// Lanes of the warp that hold the same NBITS-bit value, from NBITS ballots. __match_any_sync gives the same mask but
+// its cost grows with the number of DISTINCT values in the warp: ~170 cycles on the uniformly distributed low depth
+// bytes (ncu: 65 % of the histogram kernel's stall samples sat on the instruction behind MATCH.ANY), against ~3 issue
+// slots per bit here. Measured neutral on the 1 M-key headline: there the sort is a chain of dependent global round
+// trips (stage 1 serialised = 0.082 ms fixed + 0.058 ms per million keys, tests/gpu_sort_time.py at 62 k ... 4 M keys).
+template <int NBITS>
+__device__ __forceinline__ uint32_t warp_peers(uint32_t v) {
+  uint32_t peers = 0xffffffffu;
+#pragma unroll
+  for (int b = 0; b < NBITS; b++) {
+    const bool bit = (v >> b) & 1u;
+    const uint32_t bal = __ballot_sync(0xffffffffu, bit);
+    peers &= bit ? bal : ~bal;
+  }
+  return peers;
+}
+
 __global__ void __launch_bounds__(SORT_THREADS)
 onesweep_hist_kernel(const uint64_t* __restrict__ in, int64_t n, uint32_t* __restrict__ hist /* [4][256] */) {
   __shared__ uint32_t h[4][RADIX];
@@ -321,19 +338,22 @@ onesweep_hist_kernel(const uint64_t* __restrict__ in, int64_t n, uint32_t* __res
       const int64_t i = base + (int64_t)k * SORT_THREADS + threadIdx.x;
       const bool ok = i < n;
       const uint32_t key = ok ? (uint32_t)(in[i] >> 32) : 0u;
+      const uint32_t okm = __ballot_sync(0xffffffffu, ok);
 #pragma unroll
       for (int p = 0; p < 4; p++) {
         // depth digits are heavily skewed: aggregate equal digits inside the warp first (one shared atomic per value)
-        const uint32_t d = ok ? (key >> (8 * p)) & 255u : 0xffffffffu;
-        const unsigned peers = __match_any_sync(0xffffffffu, d);
+        const uint32_t d = (key >> (8 * p)) & 255u;
+        const unsigned peers = warp_peers<8>(d) & okm;
         if (ok && (threadIdx.x & 31) == (unsigned)__ffs(peers) - 1) atomicAdd(&h[p][d], (uint32_t)__popc(peers));
       }
     }
   }
   __syncthreads();
+  // ~520 non-empty bins per block: all blocks on one copy of the histograms serialise on its 32 cache lines in L2
+  uint32_t* const copy = hist + (size_t)(blockIdx.x % OS_HIST_COPIES) * (4 * RADIX);
   for (int i = threadIdx.x; i < 4 * RADIX; i += SORT_THREADS) {
     const uint32_t v = (&h[0][0])[i];
-    if (v) atomicAdd(&hist[i], v);
+    if (v) atomicAdd(&copy[i], v);
   }
 }
 
@@ -361,7 +381,9 @@ onesweep_pass_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out
   // exclusive scan of this pass's 256 digit totals (one per thread): where every digit's run starts in the output
   uint32_t gbase;
   {
-    const uint32_t v = hist[pass * RADIX + threadIdx.x];
+    uint32_t v = 0;
+#pragma unroll
+    for (int c = 0; c < OS_HIST_COPIES; c++) v += hist[(size_t)c * (4 * RADIX) + pass * RADIX + threadIdx.x];
     uint32_t incl = v;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -389,7 +411,7 @@ onesweep_pass_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out
   for (int k = 0; k < IPT; k++) {
     const int64_t i = base + k * 32 + lane;
     const uint32_t d = i < n ? ((uint32_t)(item[k] >> shift) & 255u) : RADIX;  // RADIX = "invalid" bin
-    const unsigned peers = __match_any_sync(0xffffffffu, d);
+    const unsigned peers = warp_peers<9>(d);
     const int leader = __ffs(peers) - 1;
     uint32_t prior = 0;
     if (lane == leader) {
@@ -453,7 +475,7 @@ void launch_depth_sort(int P, GeomState& g, cudaStream_t s, int& launches) {
   if (!v1 && (uint32_t)P <= OS_MASK) {
     const int nblk = sort_blocks(P);
     uint32_t* hist = g.onesweep;
-    uint32_t* counters = hist + 4 * RADIX;
+    uint32_t* counters = hist + (size_t)OS_HIST_COPIES * 4 * RADIX;
     uint32_t* status = counters + 16;
     cudaMemsetAsync(g.onesweep, 0, onesweep_words(P) * sizeof(uint32_t), s);   // histograms, tickets, 4 status regions
     onesweep_hist_kernel<<<nblk < 2 * 148 ? nblk : 2 * 148, SORT_THREADS, 0, s>>>(a, P, hist);

@@ -50,7 +50,8 @@ constexpr int EMIT_THREADS = 256;
 __host__ __device__ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 inline int sort_blocks(int64_t n) { return (int)((n + SORT_TILE - 1) / SORT_TILE); }
 inline int emit_blocks(int64_t n) { return (int)((n + EMIT_THREADS - 1) / EMIT_THREADS); }
-inline size_t onesweep_words(int64_t n) { return 4 * RADIX + 16 + 4 * (size_t)RADIX * sort_blocks(n); }
+constexpr int OS_HIST_COPIES = 8;   // the histogram blocks spread their flushes over this many copies (32 hot L2 lines otherwise)
+inline size_t onesweep_words(int64_t n) { return (size_t)OS_HIST_COPIES * 4 * RADIX + 16 + 4 * (size_t)RADIX * sort_blocks(n); }
 
 struct GeomState {
   float4* rec;
