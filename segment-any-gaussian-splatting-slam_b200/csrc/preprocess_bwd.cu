@@ -13,6 +13,7 @@
 namespace gsr {
 
 constexpr int PB_THREADS = 128;
+constexpr int PB_SUBS = 8;      // sparse / tracking modes: 128-Gaussian groups per block
 constexpr int PB_TILE = PB_THREADS * 49;  // floats: SH rows of up to 48 floats at an odd stride
 
 // thread-private K values -> (P, K) row-major tensor, coalesced through the tile
@@ -42,19 +43,60 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
                       const BwdOutputs out, const BwdOpts opt) {
   constexpr int ROW = (F == 16) ? 32 : 64;
   __shared__ CamS cs;
-  __shared__ float4 tile4[PB_THREADS * 13];  // M == 16: SH rows of 12 float4 at a 13-float4 stride
+  // M == 16: SH rows of 12 float4 at a 13-float4 stride. The sparse / tracking modes only keep the 27 camera sums here:
+  // 26 KB less per block, and most of their blocks leave at the flag test below before touching anything else.
+  __shared__ float4 tile4[MODE == 0 ? PB_THREADS * 13 : 8];
   float* tile = reinterpret_cast<float*>(tile4);
   static_assert(PB_THREADS * 13 * 4 >= PB_TILE, "tile too small for the scalar layout");
+  // Dense mode: block b owns Gaussians [128 b, 128 b + 128), thread t Gaussian 128 b + t. Sparse / tracking modes: a
+  // block owns PB_SUBS such groups, reads their 1024 flags with one 8-byte load per thread, compacts the touched
+  // indices (in order: results do not depend on the schedule) into shared memory and hands them to its threads, 128 at
+  // a time. ncu on the headline (1 796 touched rows of 1 M): 61 % of the stall samples of the one-group-per-block
+  // version sat in the flag test of its 7 813 blocks, 13 waves at 4 blocks per SM.
+  __shared__ int s_list[MODE == 0 ? 1 : PB_SUBS * PB_THREADS];
+  __shared__ int s_warp[PB_THREADS / 32];
+  int count = 0;
+  if (MODE != 0) {
+    const size_t g0 = ((size_t)blockIdx.x * PB_SUBS * PB_THREADS) + 8 * (size_t)threadIdx.x;
+    uint64_t w = 0;
+    if (g0 + 8 <= (size_t)in.P && ((uintptr_t)touched & 7) == 0) {
+      w = *reinterpret_cast<const uint64_t*>(touched + g0);
+    } else {
+      for (int k = 0; k < 8; k++)
+        if (g0 + k < (size_t)in.P) w |= (uint64_t)touched[g0 + k] << (8 * k);
+    }
+    int mine = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) mine += ((w >> (8 * k)) & 0xffu) != 0;
+    int incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, o);
+      if ((threadIdx.x & 31) >= o) incl += t;
+    }
+    if ((threadIdx.x & 31) == 31) s_warp[threadIdx.x >> 5] = incl;
+    __syncthreads();
+    int pos = incl - mine;
+#pragma unroll
+    for (int q = 0; q < PB_THREADS / 32; q++) {
+      if (q < (int)(threadIdx.x >> 5)) pos += s_warp[q];
+      count += s_warp[q];
+    }
+    if (count == 0) return;
+#pragma unroll
+    for (int k = 0; k < 8; k++)
+      if (((w >> (8 * k)) & 0xffu) != 0) s_list[pos++] = (int)(g0 + k);
+    __syncthreads();
+  }
   load_cam(cam, cs);
-  const int first = blockIdx.x * PB_THREADS;
-  const int idx = first + threadIdx.x;
-  const bool valid = idx < in.P;
   const int M = in.M, D = in.D;
+  auto group = [&](const int first, const int idx) {
+  const bool valid = idx < in.P;
   // Gaussians the backward blend never reached have all-zero rows, hence all-zero gradients: only zeros are written
   // (a touched Gaussian was rendered, so radii > 0 is implied: the sparse modes do not read radii)
   const bool visible = valid && touched[idx] != 0 && (MODE != 0 || radii[idx] > 0);
   const bool any_visible = __syncthreads_or(visible);
-  if (MODE != 0 && !any_visible) return;  // sparse / tracking: nothing to write for this block
+  if (MODE != 0 && !any_visible) return;  // sparse / tracking: nothing to write for this group
   const int SS = (3 * M) | 1;  // odd row stride -> conflict-free per-thread rows
   // SH coefficients of the block's Gaussians: coalesced load into the tile
   const bool sh16 = MODE == 0 && in.shs != nullptr && M == 16 && (((uintptr_t)in.shs | (uintptr_t)out.dL_dsh) & 15) == 0;
@@ -482,6 +524,15 @@ preprocess_bwd_kernel(const FwdInputs in, const Cam cam, const uint32_t* __restr
     __syncthreads();
     if (threadIdx.x < 27 && tile[threadIdx.x] != 0.f) atomicAdd(&pose_acc[threadIdx.x], (double)tile[threadIdx.x]);
   }
+  };  // group
+  if (MODE == 0) {
+    group(blockIdx.x * PB_THREADS, blockIdx.x * PB_THREADS + threadIdx.x);
+  } else {
+    for (int base = 0; base < count; base += PB_THREADS) {
+      const int j = base + threadIdx.x;
+      group(0, j < count ? s_list[j] : in.P);
+    }
+  }
 }
 
 // pose accumulators (double) -> the three camera-gradient outputs (column-major flat matrices like the inputs)
@@ -499,10 +550,11 @@ __global__ void pose_finalize_kernel(const double* __restrict__ acc, float* __re
 
 void launch_preprocess_backward(const FwdInputs& in, const Cam& cam, const GeomState& g, const int* radii,
                                 const BwdOutputs& out, const BwdOpts& opt, cudaStream_t s) {
-  const int nb = (in.P + PB_THREADS - 1) / PB_THREADS;
+  const int nb_dense = (in.P + PB_THREADS - 1) / PB_THREADS;
+  const int nb_sparse = (in.P + PB_SUBS * PB_THREADS - 1) / (PB_SUBS * PB_THREADS);
   if (out.dL_dviewmatrix) cudaMemsetAsync(g.pose_acc, 0, 32 * sizeof(double), s);
 #define GSR_LAUNCH_PB(FF, PP, MM)                                                                                        \
-  preprocess_bwd_kernel<FF, PP, MM><<<nb, PB_THREADS, 0, s>>>(in, cam, g.tiles_touched, g.clamped, radii, opt.rows, opt.touched, \
+  preprocess_bwd_kernel<FF, PP, MM><<<(MM) == 0 ? nb_dense : nb_sparse, PB_THREADS, 0, s>>>(in, cam, g.tiles_touched, g.clamped, radii, opt.rows, opt.touched, \
                                                               g.rec, g.pose_acc, out, opt)
   const bool pose = out.dL_dviewmatrix != nullptr;
   const int mode = opt.tracking ? 2 : (opt.sparse_rows ? 1 : 0);
