@@ -116,6 +116,19 @@ preprocess_kernel(const FwdInputs in, const Cam cam, float4* __restrict__ rec, u
     if (early) tma_load_1d(&sh_tile[threadIdx.x * 13], in.shs + (size_t)idx * 48, 192, &sh_bar);
   }
   if (idx >= in.P) return;  // (these threads issued no copy; the block lives on through the threads that wait below)
+  // every remaining per-Gaussian input is requested NOW, next to the SH copy: loads issued where they are consumed sit
+  // behind data-dependent branches the compiler cannot hoist them over, one exposed HBM latency each
+  const bool alive0 = !(p_view.z <= 0.2f);
+  float opac = 0.f, sc0 = 0.f, sc1 = 0.f, sc2 = 0.f;
+  float4 q = {0.f, 0.f, 0.f, 0.f};
+  if (alive0) {
+    opac = in.opacities[idx];
+    if (in.cov3D_precomp == nullptr) {
+      const float* sc = in.scales + 3 * (size_t)idx;
+      sc0 = sc[0], sc1 = sc[1], sc2 = sc[2];
+      q = reinterpret_cast<const float4*>(in.rotations)[idx];
+    }
+  }
 
   int my_radius_i = 0;
   uint32_t touched = 0;
@@ -134,9 +147,7 @@ preprocess_kernel(const FwdInputs in, const Cam cam, float4* __restrict__ rec, u
 #pragma unroll
       for (int k = 0; k < 6; k++) cov3D[k] = in.cov3D_precomp[6 * (size_t)idx + k];
     } else {
-      const float* sc = in.scales + 3 * (size_t)idx;
-      const float4 q = reinterpret_cast<const float4*>(in.rotations)[idx];
-      cov3d_from_scale_rot(sc[0], sc[1], sc[2], cam.scale_modifier, q.x, q.y, q.z, q.w, cov3D);
+      cov3d_from_scale_rot(sc0, sc1, sc2, cam.scale_modifier, q.x, q.y, q.z, q.w, cov3D);
     }
     Cov2D c2 = project_cov(p_orig, cam.focal_x, cam.focal_y, cam.tan_fovx, cam.tan_fovy, cov3D, cs.V);
     // low-pass filter, forward.cu:114-115
@@ -185,7 +196,6 @@ preprocess_kernel(const FwdInputs in, const Cam cam, float4* __restrict__ rec, u
     // sqrt(tau * cov_xx), |dy| by sqrt(tau * cov_yy). Margins (0.01 on tau, 0.1 % + 0.01 px on the extents) cover
     // the float rounding of the blend's own power / exp evaluation, so skipping outside the box never changes a
     // result. Opacities that can never reach 1/255 get a negative box.
-    const float opac = in.opacities[idx];
     const float tau = 2.0f * logf(255.0f * opac) + 0.01f;
     float hx = -1.f, hy = -1.f;
     if (tau > 0.f) {
