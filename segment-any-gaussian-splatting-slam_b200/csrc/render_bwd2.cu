@@ -220,7 +220,7 @@ render_bwd2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict_
   const uint32_t lastA = insideA ? n_contrib[pidA] : 0, lastB = insideB ? n_contrib[pidB] : 0;
   if (tid == 0) {
     for (int i = 0; i < NST; i++) {
-      mbar_init(&sm.bar[i], 1);
+      mbar_init(&sm.bar[i], BWD2_THREADS);   // one deferred arrival per thread and batch
       mbar_init(&sm.empty[i], 4);
     }
     mbar_fence_init();
@@ -239,11 +239,15 @@ render_bwd2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict_
   // a pair is live for a pixel iff its list position < n_contrib  <=>  walk index >= thr
   const int thrA = todo - (int)lastA, thrB = todo - (int)lastB;
 
-  constexpr uint32_t ROW_BYTES = 16 * REC4 + 4 * F;
-  // Staging: lanes 0..7 of every warp issue the bulk copies of rows 8 warp + lane (the work is spread over the four
-  // warps), and the Gaussian index of a row is fetched ONE BATCH AHEAD of its copies, so the dependent global load
-  // (point_list -> record address) never sits in front of a TMA issue (ncu: that load and the wait for the copies it
-  // delayed were 15 % of the stall samples of the first version).
+  // Staging: every warp gathers rows 8 warp .. 8 warp + 7 of a batch with 16-byte cp.async (LDGSTS), granule g = lane +
+  // 32 k of the warp's 8 rows x GPR granules (record first, then features): 2 (F = 16) or 3 copy instructions per warp
+  // and batch. (cp.async.bulk takes uniform-register operands: per-lane bulk copies are issued by a compiler-generated
+  // loop that elects one lane at a time -- 8 % of this kernel's stall samples, 17 % of the forward blend's.) The
+  // Gaussian index of a row is fetched ONE BATCH AHEAD of its copies (lanes 0..7), so the dependent global load
+  // (point_list -> record address) never sits in front of the copies (ncu: that load and the wait for the copies it
+  // delayed were 15 % of the stall samples of the first version). Every thread's arrival on the stage's full barrier
+  // is deferred until its copies have landed (cp.async.mbarrier.arrive.noinc).
+  constexpr int GPR = REC4 + F / 4;
   const bool issuer = lane < BB / 4;
   const int myrow = warp * (BB / 4) + lane;
   auto load_id = [&](int b) -> uint32_t {
@@ -253,11 +257,18 @@ render_bwd2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict_
   auto issue = [&](int b, uint32_t id) {
     const int st = b % NST;
     const int cnt = min(BB, todo - b * BB);
-    if (tid == 0) mbar_arrive_expect_tx(&sm.bar[st], (uint32_t)cnt * ROW_BYTES);
-    if (issuer && myrow < cnt) {
-      tma_load_1d(&sm.row[st][myrow].rec[0], rec + REC4 * (size_t)id, 16 * REC4, &sm.bar[st]);
-      tma_load_1d(&sm.row[st][myrow].feat[0], feats + (size_t)id * F, 4 * F, &sm.bar[st]);
+#pragma unroll
+    for (int k = 0; k < (BB / 4) * GPR / 32; k++) {
+      const int g = lane + 32 * k;
+      const int rl = g / GPR, part = g - rl * GPR;      // row within the warp's slice, 16-byte part of the row
+      const uint32_t rid = __shfl_sync(FULL2, id, rl);
+      const int r = warp * (BB / 4) + rl;
+      if (r < cnt) {
+        if (part < REC4) cp_async16(&sm.row[st][r].rec[part], rec + REC4 * (size_t)rid + part);
+        else cp_async16(&sm.row[st][r].feat[part - REC4], reinterpret_cast<const float4*>(feats + (size_t)rid * F) + (part - REC4));
+      }
     }
+    cp_async_mbar_arrive(&sm.bar[st]);
   };
   // Forward blend masks of this warp's two halves (BinState::hitw): batch b walks list positions p_top, p_top - 1, ...;
   // lane l holds the word of group (p_top >> 5) - l.

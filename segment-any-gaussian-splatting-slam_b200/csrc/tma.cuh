@@ -43,4 +43,14 @@ __device__ __forceinline__ void tma_load_1d(void* smem_dst, const void* gmem_src
                : "memory");
 }
 
+// 16-byte global -> shared copy per thread (LDGSTS, L2 only); completion is observed through an mbarrier:
+// cp_async_mbar_arrive makes the calling thread's arrival on `bar` fire once all its earlier cp.async have landed
+// (.noinc: the arrival is one of the barrier's expected count).
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_mbar_arrive(uint64_t* bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
 }  // namespace gsr
