@@ -171,6 +171,18 @@ int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const
 size_t gsr_knn_scratch_bytes(int P);
 int gsr_knn(int P, const float* points, float* mean_dists, char* scratch, void* stream);
 
+/* Allocation-free variant of gsr_knn. It has NO counterpart in the reference: it was added
+ * for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc). Same kernels and bit-identical results as gsr_knn, but the scratch is a
+ * file-scope `static __device__` array inside the library (9 MiB, held by every GPU that loads the library until the
+ * process exits), so the caller passes only inputs and outputs and the call performs no cudaMalloc / cudaFree / any
+ * allocating routine. Limit: P <= GSR_KNN_STATIC_MAX_POINTS; a larger P is refused with GSR_ERR_UNSUPPORTED (use
+ * gsr_knn with caller scratch). All calls on a GPU share the one array: calls that overlap on the GPU (two streams,
+ * two host threads on one device) RACE on it -- serialise them. The array keeps the previous call's contents; the
+ * only part that must start at zero (the bounding box) is cleared by every call. */
+#define GSR_KNN_STATIC_MAX_POINTS 262144
+int gsr_knn_static(int P, const float* points, float* mean_dists, void* stream);
+
 /* Parity/diagnostic export (no reference equivalent; the reference's private scratch layout is
  * rasterizer_impl.h:30-70). Any output may be NULL. All device pointers:
  * tiles_touched u32[P], depths f32[P], means2D f32[2P], conic_opacity f32[6P] (float6 order),

@@ -674,6 +674,18 @@ int gsr_knn(int P, const float* points, float* mean_dists, char* scratch, void* 
   return GSR_OK;
 }
 
+int gsr_knn_static(int P, const float* points, float* mean_dists, void* stream_) {
+  g_launches = 0;
+  if (P < 0 || (P > 0 && (!points || !mean_dists))) return fail(GSR_ERR_INVALID_ARGUMENT, "knn_static: bad argument");
+  if (P > gsr::knn_static_max_points())
+    return fail(GSR_ERR_UNSUPPORTED, "knn_static: P = %d exceeds the static scratch limit of %d points (use gsr_knn)", P,
+                gsr::knn_static_max_points());
+  if (P == 0) return GSR_OK;
+  cudaError_t e = gsr::launch_knn_static(P, points, mean_dists, (cudaStream_t)stream_, g_launches);
+  if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "knn_static: %s", cudaGetErrorString(e));
+  return GSR_OK;
+}
+
 int gsr_export_state(const gsr_params* p, int num_rendered, const char* geom_buffer, const char* binning_buffer,
                      const char* image_buffer, uint32_t* tiles_touched, float* depths, float* means2D,
                      float* conic_opacity, float* rgb, uint8_t* clamped, uint32_t* point_list, uint64_t* sorted_keys,

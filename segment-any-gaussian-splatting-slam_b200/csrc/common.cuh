@@ -245,5 +245,7 @@ void launch_export(int P, int64_t R, const Cam& cam, const GeomState& g, const B
                    uint64_t* sorted_keys, cudaStream_t s);
 size_t knn_scratch_bytes(int P);
 void launch_knn(int P, const float* points, float* mean_dists, char* scratch, cudaStream_t s, int& launches);
+int knn_static_max_points();   // allocation-free variant on a file-scope device array (knn.cu)
+cudaError_t launch_knn_static(int P, const float* points, float* mean_dists, cudaStream_t s, int& launches);
 
 }  // namespace gsr

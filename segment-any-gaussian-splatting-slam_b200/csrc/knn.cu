@@ -240,4 +240,37 @@ void launch_knn(int P, const float* points, float* mean_dists, char* scratch, cu
   launches += 2;
 }
 
+// ---- allocation-free variant (gsr_knn_static, include/gsraster_b200.h) ------------------------------------------
+// Same kernels, same carve, but the scratch is a file-scope device array instead of caller memory: for callers that
+// cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc). Every GPU that loads the
+// library holds the 9 MiB until exit. All calls share the array: calls that overlap on one GPU race on it.
+// Nothing in it has to survive or be zero between calls except the bounding box, which launch_knn clears per call.
+constexpr int KNN_STATIC_MAX_P = 262144;
+constexpr size_t KNN_STATIC_BYTES = (size_t)9 << 20;   // >= knn_scratch_bytes(KNN_STATIC_MAX_P) = 8 553 984
+static __device__ __align__(256) unsigned char knn_static_scratch[KNN_STATIC_BYTES];
+
+int knn_static_max_points() { return KNN_STATIC_MAX_P; }
+
+// In host code `knn_static_scratch` is only the host-side stand-in of the symbol: the device address is resolved once
+// per device (with that device current) and cached. -> cudaSuccess or the failing call's code.
+cudaError_t launch_knn_static(int P, const float* points, float* mean_dists, cudaStream_t s, int& launches) {
+  static std::atomic<char*> dev_ptr[64];
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+  if (P > KNN_STATIC_MAX_P || knn_scratch_bytes(P) > KNN_STATIC_BYTES) return cudaErrorInvalidValue;
+  char* ptr = dev_ptr[dev].load(std::memory_order_acquire);
+  if (!ptr) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, knn_static_scratch);
+    if (e != cudaSuccess) return e;
+    if (!p) return cudaErrorInvalidSymbol;
+    ptr = static_cast<char*>(p);
+    dev_ptr[dev].store(ptr, std::memory_order_release);
+  }
+  launch_knn(P, points, mean_dists, ptr, s, launches);
+  return cudaGetLastError();
+}
+
 }  // namespace gsr
