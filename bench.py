@@ -447,7 +447,18 @@ def run_e2e(args, wl, bucket, ex, world, peer, dense, my_views, sync_all):
     h_loss = [torch.zeros(8 * max(V, 1) + 8).pin_memory() for _ in range(2)]
     d_loss = [torch.zeros(8 * max(V, 1) + 8, device=dev) for _ in range(2)]
     ev_loss = [torch.cuda.Event() for _ in range(2)]
-    state = dict(i=0, slot=0, last=0.0)
+    state = dict(i=0, slot=0, last=0.0, pref=None)
+
+    def issue_copy(p):
+        k = state["slot"] % NB
+        state["slot"] += 1
+        copy_stream.wait_event(ev_free[k])
+        with torch.cuda.stream(copy_stream):
+            gt[k].copy_(h_gt, non_blocking=True)
+            for name in cam_d[k]:
+                cam_d[k][name].copy_(h_cam[p][name], non_blocking=True)
+            ev_in[k].record(copy_stream)
+        return k
 
     def step():
         i = state["i"]
@@ -459,15 +470,15 @@ def run_e2e(args, wl, bucket, ex, world, peer, dense, my_views, sync_all):
         else:
             ext_b = None
         for j, p in enumerate(views):
-            k = state["slot"] % NB
-            state["slot"] += 1
-            # keyframe: pinned host -> device on the copy stream, concurrent with the previous view's kernels
-            copy_stream.wait_event(ev_free[k])
-            with torch.cuda.stream(copy_stream):
-                gt[k].copy_(h_gt, non_blocking=True)
-                for name in cam_d[k]:
-                    cam_d[k][name].copy_(h_cam[p][name], non_blocking=True)
-                ev_in[k].record(copy_stream)
+            # keyframe: pinned host -> device on the copy stream. The copy of the NEXT view (of this step or the next)
+            # is queued before this view's forward, so it runs under this view's kernels: queued after the backward
+            # it only had the backward's 0.6 ms to hide 15.7 MB in, and e2e moved with the box's PCIe rate (650..775).
+            if state["pref"] is not None and state["pref"][0] == p:
+                k = state["pref"][1]
+            else:
+                k = issue_copy(p)
+            nxt = views[j + 1] if j + 1 < len(views) else my_views(i + 1)[0]
+            state["pref"] = (nxt, issue_copy(nxt))
             main.wait_event(ev_in[k])
             res = wl.fwd(p, cam_t=cam_d[k])
             # masked L1 photometric loss (loss_utils.py:17-20), value and dL/dcolour in one fused pass
