@@ -11,7 +11,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "segment-any-gaussian-splatting-slam_b200", "lib", "libgsraster_b200.so")
-KEY = ("UBLKCP", "SYNCS", "UTMALDG", "UTCHMMA", "UTCBAR", "LDTM", "STTM", "FFMA2", "FMUL2", "FADD2", "HMMA", "REDG", "RED", "REDUX", "MATCH",
+KEY = ("UBLKCP", "LDGSTS", "SYNCS", "UTMALDG", "UTCHMMA", "UTCBAR", "LDTM", "STTM", "FFMA2", "FMUL2", "FADD2", "HMMA", "REDG", "RED", "REDUX", "MATCH",
        "VOTE", "SHFL", "LDSM", "LDS", "STS", "LDG", "STG", "ATOMG", "ATOMS", "MUFU", "FFMA", "FMUL", "FADD", "BAR", "LDL", "STL")
 
 
