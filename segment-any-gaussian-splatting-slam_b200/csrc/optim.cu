@@ -19,7 +19,7 @@ namespace gsr {
 struct AdamArgs {
   gsr_adam_tensors t;
   float lr[7];
-  float beta1, beta2, eps, bc1, bc2_sqrt;  // bc1 = 1 - beta1^t, bc2_sqrt = sqrt(1 - beta2^t)
+  float beta1, beta2, eps, inv_bc1, inv_bc2_sqrt;  // 1 / (1 - beta1^t), 1 / sqrt(1 - beta2^t)
   int P, M, F;
   const int* idx;    // sparse mode: rows to step (NULL = dense)
   const int* count;  // sparse mode: number of valid rows (device scalar)
@@ -28,13 +28,26 @@ struct AdamArgs {
 };
 
 // torch/optim/adam.py (_single_tensor_adam): exp_avg.lerp_(grad, 1 - beta1); exp_avg_sq = beta2 v + (1 - beta2) g g;
-// denom = sqrt(v) / sqrt(bc2) + eps; p -= (lr / bc1) * m / denom
-__device__ __forceinline__ float adam_update(float* p, float* m, float* v, size_t i, float g, float lr, const AdamArgs& a) {
-  float mi = m[i], vi = v[i];
+// denom = sqrt(v) / sqrt(bc2) + eps; p -= (lr / bc1) * m / denom.
+// The two per-step constants are folded on the host (step_k = lr_k / bc1, inv_bc2_sqrt) and the square root and the
+// quotient use the hardware approximations (sqrt.approx, __fdividef: <= 2 ulp each): with IEEE sqrt and two IEEE
+// divisions per element the dense kernel issued 160 instructions per parameter and ran at 63 % issue utilisation and
+// 57 % of DRAM bandwidth (ncu) -- bound by arithmetic, not by its 32 B per parameter. The result stays within 1e-6
+// relative of torch's update (tests: 2e-5 of the tensor maximum after four steps).
+__device__ __forceinline__ float adam_sqrt(float x) {
+  float r;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ float adam_core(float& mi, float& vi, float pi, float g, float step, const AdamArgs& a) {
   mi = mi + (g - mi) * (1.f - a.beta1);
   vi = a.beta2 * vi + (1.f - a.beta2) * g * g;
-  const float denom = sqrtf(vi) / a.bc2_sqrt + a.eps;
-  const float pn = p[i] - (lr / a.bc1) * (mi / denom);
+  const float denom = fmaf(adam_sqrt(vi), a.inv_bc2_sqrt, a.eps);
+  return pi - step * __fdividef(mi, denom);
+}
+__device__ __forceinline__ float adam_update(float* p, float* m, float* v, size_t i, float g, float lr, const AdamArgs& a) {
+  float mi = m[i], vi = v[i];
+  const float pn = adam_core(mi, vi, p[i], g, lr * a.inv_bc1, a);
   m[i] = mi; v[i] = vi; p[i] = pn;
   return pn;
 }
@@ -109,14 +122,9 @@ __device__ __forceinline__ void adam_update4(float* p, float* m, float* v, size_
   const float4 p4 = *reinterpret_cast<const float4*>(p + i);
   float mi[4] = {m4.x, m4.y, m4.z, m4.w}, vi[4] = {v4.x, v4.y, v4.z, v4.w};
   const float pi[4] = {p4.x, p4.y, p4.z, p4.w};
-  const float step = lr / a.bc1;
+  const float step = lr * a.inv_bc1;
 #pragma unroll
-  for (int k = 0; k < 4; k++) {
-    mi[k] = mi[k] + (g[k] - mi[k]) * (1.f - a.beta1);
-    vi[k] = a.beta2 * vi[k] + (1.f - a.beta2) * g[k] * g[k];
-    const float denom = sqrtf(vi[k]) / a.bc2_sqrt + a.eps;
-    pn[k] = pi[k] - step * (mi[k] / denom);
-  }
+  for (int k = 0; k < 4; k++) pn[k] = adam_core(mi[k], vi[k], pi[k], g[k], step, a);
   *reinterpret_cast<float4*>(m + i) = make_float4(mi[0], mi[1], mi[2], mi[3]);
   *reinterpret_cast<float4*>(v + i) = make_float4(vi[0], vi[1], vi[2], vi[3]);
   *reinterpret_cast<float4*>(p + i) = make_float4(pn[0], pn[1], pn[2], pn[3]);
@@ -139,11 +147,17 @@ adam_flat_kernel(const AdamArgs a) {
     // SH rows: element e of f_dc (grp 1) / f_rest (grp 2) lives at g_sh / a_shs [gauss * 3M + (grp 1: c, grp 2: 3 + c)]
     uint32_t sh[4] = {0, 0, 0, 0};
     if (grp == 1 || grp == 2) {
+      // one division per chunk; the following elements step through the row (and into the next Gaussian's)
       const uint32_t w = grp == 1 ? 3u : R, add = grp == 1 ? 0u : 3u;
+      uint32_t gi = grp == 1 ? __umulhi(i, 0xAAAAAAABu) >> 1 : i / w;
+      uint32_t r = i - gi * w;
+      uint32_t pos = gi * M3 + add + r;
 #pragma unroll
       for (int k = 0; k < 4; k++) {
-        const uint32_t e = min(i + k, n - 1), gi = e / w;
-        sh[k] = gi * M3 + add + (e - gi * w);
+        sh[k] = pos;
+        const bool wrap = ++r == w;
+        pos += wrap ? M3 - w + 1u : 1u;
+        r = wrap ? 0u : r;
       }
     }
     if (i + 4u <= n) {
@@ -227,8 +241,8 @@ void launch_adam(const gsr_adam_tensors& t, int P, int M, int F, const float* lr
   a.t = t;
   for (int i = 0; i < 7; i++) a.lr[i] = lr[i];
   a.beta1 = beta1; a.beta2 = beta2; a.eps = eps;
-  a.bc1 = (float)(1.0 - pow((double)beta1, (double)step));
-  a.bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, (double)step));
+  a.inv_bc1 = (float)(1.0 / (1.0 - pow((double)beta1, (double)step)));
+  a.inv_bc2_sqrt = (float)(1.0 / sqrt(1.0 - pow((double)beta2, (double)step)));
   a.P = P; a.M = M; a.F = F; a.idx = idx; a.count = count; a.cap = cap;
   a.dense_grad_rows = (flags & GSR_ADAM_DENSE_GRAD_ROWS) ? 1 : 0;
   if (idx) {  // sparse: a warp per listed row
@@ -245,7 +259,7 @@ void launch_adam(const gsr_adam_tensors& t, int P, int M, int F, const float* lr
     adam_step_kernel<<<(P + 7) / 8, 256, 0, s>>>(a);
     return;
   }
-  adam_flat_kernel<<<148 * 16, 256, 0, s>>>(a);
+  adam_flat_kernel<<<148 * 8, 256, 0, s>>>(a);   // one resident wave (8 blocks of 256 threads per SM), grid-stride
   adam_geom_kernel<<<(P + 255) / 256, 256, 0, s>>>(a);
 }
 void launch_activate(const gsr_adam_tensors& t, int P, int M, cudaStream_t s) {
