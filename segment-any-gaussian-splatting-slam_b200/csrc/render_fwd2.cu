@@ -231,6 +231,9 @@ render_fwd2_kernel(const uint2* __restrict__ ranges, uint32_t* __restrict__ poin
           const bool blendA = okA && !stopA, blendB = okB && !stopB;
           doneA = doneA || stopA;
           doneB = doneB || stopB;
+          // (voted here, not at the end of the iteration: the loop branch depends on it, and behind the packed FMAs its
+          // latency was exposed on every iteration)
+          all_done = __all_sync(FULLM, doneA && doneB);
           // colour / feature / depth sums need 1e-4, not bit-exactness: w = alpha * T, one packed FMA per channel pair
           const float wA = blendA ? alphaA * TA : 0.f, wB = blendB ? alphaB * TB : 0.f;
           // depth of the splat at the pixel: z - (zx a + zy b) dx - (zx b + zy c) dy   (forward.cu:403-405)
@@ -258,7 +261,6 @@ render_fwd2_kernel(const uint2* __restrict__ ranges, uint32_t* __restrict__ poin
           lastB = blendB ? pos : lastB;
           hitA |= blendA ? bit : 0u;
           hitB |= blendB ? bit : 0u;
-          all_done = __all_sync(FULLM, doneA && doneB);
         }
         // blend masks of the two 8x4 halves (lanes 0..31 all hold pixels of both halves: A = upper, B = lower)
         const uint32_t rA = __reduce_or_sync(FULLM, hitA), rB = __reduce_or_sync(FULLM, hitB);
