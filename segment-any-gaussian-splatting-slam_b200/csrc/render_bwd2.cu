@@ -370,13 +370,20 @@ render_bwd2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict_
       const uint32_t W1 = __shfl_sync(FULL2, wv, 0), W0 = __shfl_sync(FULL2, wv, 1);
       // bit l of m = mask bit of position p_hi - l
       uint32_t m = __brev(__funnelshift_rc(W0, W1, (p_hi & 31) + 1));
-      while (m) {
+      // the mask walk is one step ahead of the arithmetic: the bit scan of the NEXT hit is issued before this hit's
+      // work, so the next iteration starts with its row address in hand (index only: prefetching the record as well
+      // cost more registers than the exposed chain was worth)
+      int j = __ffs(m) - 1;
+      bool have = m != 0;
+      m &= m - 1;
+      while (have) {
         if (ns == SLOTS2) {
           flush_slots2<F, TRACK>(wbuf, sm.meta[warp], sm.bfrag[warp], ua, vb, qzero, ns, lane, grad_rows, touched, touched_ext);
           ns = 0;
           wp = reinterpret_cast<float2*>(wbuf) + lane;
         }
-        const int j = __ffs(m) - 1;
+        const int j_n = __ffs(m) - 1;
+        const bool have_n = m != 0;
         m &= m - 1;
         const Bwd2Row<F>& R = sm.row[st][j];
         const float4 r0 = R.rec[0];                                        // px, py, conic a, conic b
@@ -426,6 +433,8 @@ render_bwd2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict_
         if (lane == 0) sm.meta[warp][ns] = make_float4(r3.z, r0.x - cx, r0.y - cy, 0.f);
         ns++;
         wp += WSTRIDE2 / 2;
+        j = j_n;
+        have = have_n;
       }
     }
     __syncwarp();

@@ -205,10 +205,17 @@ render_fwd2_kernel(const uint2* __restrict__ ranges, uint32_t* __restrict__ poin
       for (int k = 0; k < NG; k++) {
         uint32_t m = candw[k];
         uint32_t hitA = 0, hitB = 0;   // per lane: bit i = this lane's pixel blended instance 32 k + i
-        while (m && !all_done) {
-          const uint32_t bit = m & (0u - m);
-          const int j = 32 * k + __ffs(m) - 1;
-          m ^= bit;
+        // the candidate walk is one step ahead of the blend: the bit scan of the NEXT candidate is issued before this
+        // candidate's arithmetic, so the next iteration starts with its record address in hand
+        uint32_t bit = m & (0u - m);
+        int j = 32 * k + __ffs(m) - 1;
+        bool have = m != 0;
+        m ^= bit;
+        while (have && !all_done) {
+          const uint32_t bit_n = m & (0u - m);
+          const int j_n = 32 * k + __ffs(m) - 1;
+          const bool have_n = m != 0;
+          m ^= bit_n;
           const float4* rp = &sm.rec[st][j][0];
           const float4 r0 = rp[0];                                       // px, py, conic a, conic b
           const float2 r1 = *reinterpret_cast<const float2*>(&rp[1]);    // conic c, opacity
@@ -261,6 +268,9 @@ render_fwd2_kernel(const uint2* __restrict__ ranges, uint32_t* __restrict__ poin
           lastB = blendB ? pos : lastB;
           hitA |= blendA ? bit : 0u;
           hitB |= blendB ? bit : 0u;
+          bit = bit_n;
+          j = j_n;
+          have = have_n;
         }
         // blend masks of the two 8x4 halves (lanes 0..31 all hold pixels of both halves: A = upper, B = lower)
         const uint32_t rA = __reduce_or_sync(FULLM, hitA), rB = __reduce_or_sync(FULLM, hitB);
