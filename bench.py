@@ -18,6 +18,7 @@ sm_100a) on the same keyframes on GPU 0 (the reference has no CPU path and no mu
 absent it falls back to timing the CPU oracle port. Prints ONE JSON line on rank 0.
 """
 import argparse
+import contextlib
 import json
 import os
 import subprocess
@@ -60,6 +61,8 @@ def parse_args():
                     help="secondary figure (scaling_same_pose): every rank renders keyframe 0 of the single-frustum "
                          "SURVEY 8d scene, as the round-1 scaling run did")
     ap.add_argument("--no-lpt", action="store_true", help="contiguous view blocks instead of the LPT assignment")
+    ap.add_argument("--no-view-pipeline", action="store_true",
+                    help="all views of a step on one stream (default: mapping.ViewPipeline, two alternating streams)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-legs", action="store_true", help="skip the secondary legs (workloads, render FPS, kNN, ...)")
@@ -267,10 +270,16 @@ def run_mine(args, rank, world, local_rank):
 
     # ---- view costs (device time of one forward + backward per pose, measured on rank 0, identical everywhere) and
     #      the LPT assignment of every distinct batch ----
-    def one_view(pose, ext_b=None):
+    vp = None if args.no_view_pipeline else mapping.ViewPipeline(dev)
+
+    def one_view(pose, ext_b=None, pipe=None):
         res = wl.fwd(pose, ext=capi.Ext(timer=timer[0]) if timer[0] else None)
         launches[0] += capi.last_launch_count()
+        if pipe is not None:
+            pipe.before_backward()
         wl.bwd(pose, res, out=bucket.views, ext=ext_b)
+        if pipe is not None:
+            pipe.after_backward()
         launches[0] += capi.last_launch_count()
         if timer[0]:
             rendered[pose] = rendered.get(pose, 0) + 1
@@ -317,8 +326,16 @@ def run_mine(args, rank, world, local_rank):
         else:
             ext_b = capi.Ext(timer=timer[0]) if timer[0] else None
         res = None
-        for p in views:
-            res = one_view(p, ext_b)
+        if vp is not None and timer[0] is None and len(views) > 1:
+            # the views of the step alternate between two streams: forward of view j + 1 beside backward of view j
+            vp.begin()
+            for p in views:
+                with vp.view():
+                    res = one_view(p, ext_b, vp)
+            vp.end()
+        else:   # (the instrumented pass stays on one stream: its stage events would measure the overlap, not the stages)
+            for p in views:
+                res = one_view(p, ext_b)
         if world > 1:
             if ar_events[0] is not None:
                 a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -394,7 +411,7 @@ def run_mine(args, rank, world, local_rank):
     # ---- timed region 2: end to end with host buffers ----
     e2e = None
     if not args.no_e2e:
-        e2e = run_e2e(args, wl, bucket, ex, world, peer, dense, my_views, sync_all)
+        e2e = run_e2e(args, wl, bucket, ex, world, peer, dense, my_views, sync_all, vp)
     clk = clocks.stop()
     # workload statistics of the views this rank rendered in the instrumented pass (outside the timed regions)
     per_pose = {p: wl.view_stats(p) for p in sorted(rendered)} if rendered else {0: wl.view_stats(0)}
@@ -417,7 +434,7 @@ def run_mine(args, rank, world, local_rank):
                 views_rendered=views_rendered, per_pose=per_pose)
 
 
-def run_e2e(args, wl, bucket, ex, world, peer, dense, my_views, sync_all):
+def run_e2e(args, wl, bucket, ex, world, peer, dense, my_views, sync_all, vp=None):
     """The same step through the public API with HOST buffers: per view the keyframe (view matrix, projection matrix,
     camera centre, ground-truth RGB image) is copied from pinned host memory, the reference's masked L1 photometric
     loss (gsr_photometric_loss, lambda_dssim = 0) on the rendered colour produces dL/dcolour on the device, and the
@@ -451,7 +468,8 @@ def run_e2e(args, wl, bucket, ex, world, peer, dense, my_views, sync_all):
               for kname in cam_keys} for q in range(NB)]
     gt = [torch.empty(3, H, W, device=dev) for _ in range(NB)]
     h2d_view = sum(cam_off[kname][1] for kname in cam_keys) * 4 + h_gt.numel() * 4
-    ploss = losses.PhotometricLoss(H, W, 0.0, device=dev)  # lambda_dssim = 0: masked L1 (the SSIM kernels are measured in loss_n2)
+    # lambda_dssim = 0: masked L1 (the SSIM kernels are measured in loss_n2); one object (scratch) per alternating stream
+    ploss2 = [losses.PhotometricLoss(H, W, 0.0, device=dev) for _ in range(2)]
     loss3 = [torch.empty(3, device=dev) for _ in range(NB)]
     grad_buf = [torch.empty(3, H, W, device=dev) for _ in range(2)]
     copy_stream = torch.cuda.Stream(device=dev)
@@ -486,6 +504,9 @@ def run_e2e(args, wl, bucket, ex, world, peer, dense, my_views, sync_all):
             ext_b = ex.ext(accumulate=len(views) > 1, overlap=True)
         else:
             ext_b = None
+        pipe = vp if (vp is not None and len(views) > 1) else None
+        if pipe:
+            pipe.begin()
         for j, p in enumerate(views):
             # keyframe: pinned host -> device on the copy stream. The copy of the NEXT view (of this step or the next)
             # is queued before this view's forward, so it runs under this view's kernels: queued after the backward
@@ -496,12 +517,20 @@ def run_e2e(args, wl, bucket, ex, world, peer, dense, my_views, sync_all):
                 k = issue_copy(p)
             nxt = views[j + 1] if j + 1 < len(views) else my_views(i + 1)[0]
             state["pref"] = (nxt, issue_copy(nxt))
-            main.wait_event(ev_in[k])
-            res = wl.fwd(p, cam_t=cam_d[k])
-            # masked L1 photometric loss (loss_utils.py:17-20), value and dL/dcolour in one fused pass
-            out3, grad_c = ploss(res[2], gt[k], out=d_loss3[k2][j], grad_out=grad_buf[j & 1])   # {loss, L1, -} of view j
-            wl.bwd(p, res, out=bucket.views, ext=ext_b, cam_t=cam_d[k], grads=(wl.g[0], grad_c, wl.g[2]))
-            ev_free[k].record(main)
+            with (pipe.view() if pipe else contextlib.nullcontext()):
+                cur = torch.cuda.current_stream()
+                cur.wait_event(ev_in[k])
+                res = wl.fwd(p, cam_t=cam_d[k])
+                # masked L1 photometric loss (loss_utils.py:17-20), value and dL/dcolour in one fused pass
+                out3, grad_c = ploss2[j & 1](res[2], gt[k], out=d_loss3[k2][j], grad_out=grad_buf[j & 1])   # {loss, L1, -} of view j
+                if pipe:
+                    pipe.before_backward()
+                wl.bwd(p, res, out=bucket.views, ext=ext_b, cam_t=cam_d[k], grads=(wl.g[0], grad_c, wl.g[2]))
+                if pipe:
+                    pipe.after_backward()
+                ev_free[k].record(cur)
+        if pipe:
+            pipe.end()
         if world > 1:
             if dense:
                 dist.all_reduce(bucket.flat)

@@ -202,7 +202,10 @@ class _Resizer:
 
     def __init__(self, device, role=""):
         self.device = device
-        self.key = (str(device), role)
+        # keyed by the stream of the call as well: "nothing references it any more" only says that the work using a
+        # buffer has been ENQUEUED, which orders it with later work on the same stream only (views of a step that
+        # alternate between two streams, mapping.ViewPipeline, must not inherit each other's buffers)
+        self.key = (str(device), role, torch.cuda.current_stream(device).cuda_stream)
         self.t = torch.empty(0, dtype=torch.uint8, device=device)
         self.cb = ALLOC_FN(self._alloc)
 

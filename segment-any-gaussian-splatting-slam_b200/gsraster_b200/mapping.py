@@ -344,3 +344,62 @@ class SparseGradExchange:
         for k, n in self.sizes:
             b.views[k].view(b.P, n).index_copy_(0, idx.to(torch.int64), views[k])
         return b
+
+
+class ViewPipeline:
+    """The views of one mapping step alternate between two CUDA streams, so that the forward pass of view j + 1 -- its
+    latency-bound preprocess / depth sort / binning stages and its host read-back of num_rendered -- runs beside the
+    backward pass of view j (both blend kernels leave issue slots free). Backward passes are chained by an event: they
+    share the step's flags, the gradient bucket and the row workspace. The step still begins and ends on the caller's
+    stream (begin() / end()), so nothing of step s + 1 overlaps step s: the optimiser step sits between them.
+
+        vp.begin()
+        for pose in views:
+            with vp.view():                 # torch.cuda.stream(next stream)
+                res = forward(pose)
+                vp.before_backward()
+                backward(pose, res, ext=accumulating ext)
+                vp.after_backward()
+        vp.end()
+    """
+
+    def __init__(self, device, nstreams: int = 2):
+        import torch
+        self.torch = torch
+        self.device = device
+        self.streams = [torch.cuda.Stream(device=device) for _ in range(max(1, nstreams))]
+        self.ev_start = torch.cuda.Event()
+        self.ev_bwd = [torch.cuda.Event() for _ in range(4)]
+        self.ev_end = [torch.cuda.Event() for _ in self.streams]
+        self.k = 0
+
+    def begin(self):
+        self.main = self.torch.cuda.current_stream(self.device)
+        self.ev_start.record(self.main)
+        self.joined = [False] * len(self.streams)
+        self.prev = None
+        self.k = 0
+
+    def view(self):
+        i = self.k % len(self.streams)
+        self.cur, self.cur_i = self.streams[i], i
+        if not self.joined[i]:
+            self.cur.wait_event(self.ev_start)
+            self.joined[i] = True
+        return self.torch.cuda.stream(self.cur)
+
+    def before_backward(self):
+        if self.prev is not None:
+            self.cur.wait_event(self.prev)
+
+    def after_backward(self):
+        ev = self.ev_bwd[self.k % len(self.ev_bwd)]
+        ev.record(self.cur)
+        self.prev = ev
+        self.k += 1
+
+    def end(self):
+        for i, s in enumerate(self.streams):
+            if self.joined[i]:
+                self.ev_end[i].record(s)
+                self.main.wait_event(self.ev_end[i])

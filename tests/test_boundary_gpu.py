@@ -244,3 +244,56 @@ def test_debug_flag_writes_the_reference_snapshots(tmp_path, monkeypatch):
     monkeypatch.setattr(dgr._C, "rasterize_gaussians_backward", orig)
     assert os.path.exists("snapshot_bw.dump")
     assert len(torch.load("snapshot_bw.dump")) == 24
+
+
+def test_view_pipeline_two_streams_matches_one_stream():
+    """mapping.ViewPipeline: the views of a step alternate between two streams (forward of view j + 1 beside backward of
+    view j, backward passes chained by an event). Four views accumulated through the pipeline equal the same four views
+    accumulated on one stream (same flags, rows equal up to the order of the float atomics), repeatedly, and the
+    scratch pool never hands a buffer of one stream to a call on another."""
+    import torch
+    from gsraster_b200 import capi, mapping
+    P, W, H, F, deg = 60_000, 640, 512, 16, 3
+    sc = scenes.make_trajectory_scene(P, 4, sh_degree=deg, F=F, seed=47, W=W, H=H)
+    grads = scenes.make_upstream_grads(W, H, F)
+    gd, gc, go = [torch.from_numpy(g).cuda() for g in grads]
+    e = torch.empty(0, device="cuda")
+    cams = [scenes.make_camera(W, H, v) for v in range(4)]
+    ds = [h.to_torch(sc, c) for c in cams]
+    M = (deg + 1) ** 2
+
+    def run(pipe):
+        mask = torch.zeros(P, dtype=torch.uint8, device="cuda")
+        ws = capi.new_row_workspace(P, F, "cuda")
+        ext = capi.Ext(touched_mask=mask, sparse_rows=True, accumulate=True, row_workspace=ws)
+        o = dict(device="cuda", dtype=torch.float32)
+        out = dict(means3D=torch.zeros((P, 3), **o), sh=torch.zeros((P, M, 3), **o), objects=torch.zeros((P, F), **o),
+                   opacity=torch.zeros((P, 1), **o), scales=torch.zeros((P, 3), **o), rotations=torch.zeros((P, 4), **o))
+        if pipe:
+            pipe.begin()
+        for cam, d in zip(cams, ds):
+            with (pipe.view() if pipe else torch.cuda.stream(torch.cuda.current_stream())):
+                r = capi.rasterize_gaussians(d["bg"], d["means3D"], e, d["opacities"], d["scales"], d["rotations"], 1.0, e,
+                                             d["viewmatrix"], d["projmatrix"], cam.tanfovx, cam.tanfovy, H, W, d["shs"],
+                                             d["sh_objs"], deg, d["campos"], False, False)
+                if pipe:
+                    pipe.before_backward()
+                capi.rasterize_gaussians_backward(d["bg"], d["means3D"], r[4], e, d["scales"], d["rotations"], 1.0, e,
+                                                  d["viewmatrix"], d["projmatrix"], cam.tanfovx, cam.tanfovy, gd, gc, d["shs"],
+                                                  go, d["sh_objs"], deg, d["campos"], r[6], r[0], r[7], r[8], False, out=out,
+                                                  ext=ext)
+                if pipe:
+                    pipe.after_backward()
+        if pipe:
+            pipe.end()
+        torch.cuda.synchronize()
+        assert int(ws.count_nonzero()) == 0
+        return mask.bool(), out
+
+    m0, ref = run(None)
+    vp = mapping.ViewPipeline(torch.device("cuda"))
+    for _ in range(3):
+        m1, got = run(vp)
+        assert torch.equal(m0, m1) and int(m0.sum()) > 0
+        for k in ref:
+            assert h.grad_rel_err(got[k].reshape(P, -1)[m0], ref[k].reshape(P, -1)[m0]) < 2e-5, k
