@@ -52,7 +52,7 @@ struct Bwd2Smem {
   float4 meta[4][SLOTS2];                     // per warp, per slot: {Gaussian index bits, gx', gy', -}
   float wq[4][2 * SLOTS2 * WSTRIDE2];         // per warp: w rows, then q rows; re-used for the result tile
   float bfrag[4][Cfg::NTW * 16][32];          // per warp: w-side B fragments [register][lane]
-  uint64_t bar[Cfg::NST];    // full: the TMA copies of the batch in this stage have landed
+  uint64_t bar[Cfg::NST];    // full: the cp.async copies of the batch in this stage have landed
   uint64_t empty[Cfg::NST];  // empty: all 4 warps are done with the batch in this stage
   uint32_t max_contrib;
 };

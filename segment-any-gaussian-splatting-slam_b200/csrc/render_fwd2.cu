@@ -284,7 +284,7 @@ render_fwd2_kernel(const uint2* __restrict__ ranges, uint32_t* __restrict__ poin
     }
     const int num_done = __syncthreads_count(doneA && doneB);
     if (num_done == FWD2_THREADS) {
-      if (b + 1 < nbatch) mbar_wait(&sm.bar[(b + 1) & 1], (uint32_t)((b + 1) >> 1) & 1u);  // drain in-flight TMA
+      if (b + 1 < nbatch) mbar_wait(&sm.bar[(b + 1) & 1], (uint32_t)((b + 1) >> 1) & 1u);  // drain the in-flight cp.async copies
       break;
     }
   }
