@@ -9,7 +9,8 @@ N > 1 the ranks then sum their gradients (sparse exchange over peer memory). The
 keyframes of a fixed trajectory of `--pool` DISTINCT poses (5 degrees of yaw + 0.25 m per keyframe) over a map
 sampled on the union of their frusta -- the reference, too, steps on a different keyframe every iteration
 (scripts/gaussian_splatting.py:792-833, 887-935). Views are assigned to ranks longest-processing-time-first on their
-measured cost. value = view-iterations (one view forward + backward) per second over all ranks; N = 1 renders the same
+measured cost; the views of a rank's step alternate between two CUDA streams (mapping.ViewPipeline: forward of view j + 1
+beside backward of view j; --no-view-pipeline for one stream). value = view-iterations (one view forward + backward) per second over all ranks; N = 1 renders the same
 keyframes one after the other, so per-GPU work is the same at every N (weak scaling).
 
 Headline workload: 1M Gaussians, 1280x1024, SH degree 3 (M=16), 16-d feature (BASELINE.json metric).
@@ -1128,8 +1129,10 @@ def main():
                                if traffic.get(top, {}).get("work_executed") and stages[top]["bound"] == "fp32" else None),
                 per="one view (forward + backward) of the instrumented pass, mean over the keyframes rank 0 rendered",
                 peak_source=("MEASURED_PEAKS.json hbm_gbs (%s)" % pk["source"]) if stages[top]["bound"] == "hbm" else pk["fp32_source"])
+    vpn = ("" if (args.no_view_pipeline or args.views_per_rank < 2) else
+           ", the views of a step on two alternating streams (forward of view j+1 beside backward of view j)")
     if world == 1:
-        par = "single GPU, %d views per step" % nv
+        par = "single GPU, %d views per step%s" % (nv, vpn)
     else:
         xb = r["exchange_rows"] * (r["bucket_bytes"] // args.P)
         mode = ("1 NCCL all-reduce of the dense %d MB bucket per step" % (r["bucket_bytes"] // 1000000) if args.dense_allreduce else
@@ -1140,7 +1143,7 @@ def main():
                      r["exchange_rows"], args.P, xb / 1e6))
         par = "view-data-parallel x%d, %s, %d views per rank per step, %s, replicated Gaussians, %s" % (
             world, "same pose on every rank" if args.same_pose else "distinct keyframe poses on every rank (pose of view r on rank r)",
-            args.views_per_rank, "contiguous view blocks" if args.no_lpt else "views assigned longest-processing-time-first", mode)
+            args.views_per_rank, ("contiguous view blocks" if args.no_lpt else "views assigned longest-processing-time-first") + vpn, mode)
     out = dict(metric=METRIC, value=round(value, 4), unit=UNIT, n_gpus=world, steps=K, warmup=max(args.warmup, 3),
                ms_per_step=round(ms / K, 4), higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32",
                data="synthetic",
